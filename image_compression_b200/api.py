@@ -1,0 +1,418 @@
+"""ctypes binding of libimgcomp_b200.so plus a host-side mirror of the reference's
+four seams (same names, argument meaning and error behaviour as the Java statics;
+see package docstring).  The Java 21 FFM binding a maintainer would add is in
+INTEGRATION.md; this module is the same binding for the pytest harness / bench.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+from typing import Dict, MutableMapping, Optional, Tuple
+
+import numpy as np
+
+ICB_OK, ICB_NO_FIT = 0, 1
+ICB_ERR_INVALID, ICB_ERR_OOM, ICB_ERR_CUDA, ICB_ERR_UNSUPPORTED = -1, -2, -3, -4
+ICB_ERR_CAPACITY, ICB_ERR_NO_DEVICE, ICB_ERR_TICKET = -5, -6, -7
+FMT_RGB8, FMT_BGR8, FMT_RGBA8, FMT_ABGR8 = 0, 1, 2, 3
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libimgcomp_b200.so")
+
+# every symbol include/imgcomp_b200.h declares (checked by tests/test_abi.py)
+ABI_SYMBOLS = [
+    "icb_init", "icb_shutdown", "icb_device_count", "icb_last_error", "icb_set_profile",
+    "icb_alloc_pinned", "icb_free_pinned", "icb_jpg_fit", "icb_jpg_encode", "icb_jpg_sizes",
+    "icb_jpg_coefficients", "icb_resize_dims", "icb_resize_bilinear", "icb_png_fit",
+    "icb_submit_jpg_fit", "icb_wait", "icb_image_upload", "icb_image_free",
+    "icb_submit_jpg_fit_image", "icb_submit_resize_image", "icb_stats", "icb_profile_jpg_fit_image",
+]
+
+
+class IcbError(RuntimeError):
+    def __init__(self, code: int, msg: str = ""):
+        super().__init__(f"imgcomp_b200 status {code}: {msg}")
+        self.code = code
+
+
+class _Result(C.Structure):
+    _fields_ = [("status", C.c_int), ("out_len", C.c_size_t), ("best_q", C.c_float), ("scale", C.c_double),
+                ("used_cache", C.c_int), ("n_passes", C.c_int), ("device", C.c_int)]
+
+
+class _Stats(C.Structure):
+    _fields_ = [("images_done", C.c_uint64), ("kernels_launched", C.c_uint64), ("entropy_passes", C.c_uint64),
+                ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("last_transform_ms", C.c_float),
+                ("last_entropy_ms", C.c_float), ("last_total_ms", C.c_float),
+                ("last_transform_launches", C.c_int), ("last_entropy_launches", C.c_int)]
+
+
+def library_path() -> str:
+    return _LIB_PATH
+
+
+_lib = None
+
+
+def load_library(build_if_missing: bool = True):
+    """dlopen the CUDA library (building it in-tree with nvcc if it is absent).
+    Raises if it cannot be had -- there is no other implementation to fall back to."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH):
+        if not build_if_missing:
+            raise IcbError(ICB_ERR_NO_DEVICE, f"{_LIB_PATH} not built")
+        from . import build as _build
+        _build.build()
+    L = C.CDLL(_LIB_PATH)
+    u8p, vp = C.POINTER(C.c_uint8), C.c_void_p
+    L.icb_init.argtypes = [C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+    L.icb_shutdown.argtypes = [vp]
+    L.icb_shutdown.restype = None
+    L.icb_device_count.argtypes = [vp]
+    L.icb_last_error.argtypes = [vp]
+    L.icb_last_error.restype = C.c_char_p
+    L.icb_set_profile.argtypes = [vp, C.c_int, C.c_int]
+    L.icb_alloc_pinned.argtypes = [C.c_size_t]
+    L.icb_alloc_pinned.restype = vp
+    L.icb_free_pinned.argtypes = [vp]
+    L.icb_free_pinned.restype = None
+    L.icb_jpg_fit.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int64, C.c_int, C.c_float,
+                              C.c_double, vp, C.c_size_t, C.POINTER(C.c_size_t), C.POINTER(C.c_float),
+                              C.POINTER(C.c_double), C.POINTER(C.c_int)]
+    L.icb_jpg_encode.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, vp, C.c_size_t,
+                                 C.POINTER(C.c_size_t)]
+    L.icb_jpg_sizes.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float), C.c_int,
+                                C.POINTER(C.c_int64)]
+    L.icb_jpg_coefficients.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_size_t]
+    L.icb_resize_dims.argtypes = [C.c_int, C.c_int, C.c_double, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.icb_resize_dims.restype = None
+    L.icb_resize_bilinear.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int]
+    L.icb_png_fit.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_size_t,
+                              C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.icb_submit_jpg_fit.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int64, C.c_int,
+                                     C.c_float, C.c_double, vp, C.c_size_t, C.POINTER(C.c_int64)]
+    L.icb_wait.argtypes = [vp, C.c_int64, C.POINTER(_Result)]
+    L.icb_image_upload.argtypes = [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
+    L.icb_image_free.argtypes = [vp, vp]
+    L.icb_image_free.restype = None
+    L.icb_submit_jpg_fit_image.argtypes = [vp, vp, C.c_float, C.c_int64, C.c_int, C.c_float, C.c_double, vp,
+                                           C.c_size_t, C.POINTER(C.c_int64)]
+    L.icb_submit_resize_image.argtypes = [vp, vp, C.c_int, C.c_int, vp, C.c_int, C.POINTER(C.c_int64)]
+    L.icb_stats.argtypes = [vp, C.POINTER(_Stats)]
+    L.icb_profile_jpg_fit_image.argtypes = [vp, vp, C.c_float, C.c_int64, C.c_int, C.POINTER(C.c_float),
+                                            C.POINTER(C.c_float), C.POINTER(C.c_float)]
+    _lib = L
+    return L
+
+
+# ---- value types at the seam (report/CompressionParams.java:3, learn/LearnedParams.java:8,
+#      learn/jpg/SimilarityKey.java:9) ----
+@dataclass(frozen=True)
+class CompressionParams:
+    quality: float
+    min_size_bytes: int
+    min_width: int
+    min_height: int
+    target_max_size_bytes: int
+
+
+@dataclass(frozen=True)
+class LearnedParams:
+    quality: float
+    scale: float
+
+
+@dataclass(frozen=True)
+class SimilarityKey:
+    width_bucket: int
+    height_bucket: int
+    size_bucket: int
+
+
+def create_key(width: int, height: int, file_size: int) -> SimilarityKey:
+    """tools/CacheTools.java:14-21 -- buckets of 100 px / 100 px / 100 KiB on the DECODED dims."""
+    return SimilarityKey(width // 100, height // 100, file_size // 102400)
+
+
+@dataclass
+class FitResult:
+    status: int
+    data: Optional[bytes]
+    best_q: float
+    scale: float
+    used_cache: bool
+    n_passes: int
+    device: int
+    out_len: int = 0
+
+
+def _image_args(image: np.ndarray, fmt: Optional[int]) -> Tuple[np.ndarray, int, int, int, int]:
+    if image is None:
+        raise TypeError("image must not be None")         # Java: NullPointerException
+    if image.dtype != np.uint8 or image.ndim != 3 or image.shape[2] not in (3, 4):
+        raise ValueError("image must be uint8 (h, w, 3|4)")
+    if not image.flags["C_CONTIGUOUS"]:
+        image = np.ascontiguousarray(image)
+    h, w, c = image.shape
+    if fmt is None:
+        fmt = FMT_RGB8 if c == 3 else FMT_RGBA8
+    return image, w, h, image.strides[0], fmt
+
+
+class Engine:
+    """One handle = the GPU work queues that replace CompressionBatch's thread pool
+    (CompressionBatch.java:64-68).  Thread-safe: call from as many threads as slots."""
+
+    def __init__(self, devices=None, slots_per_gpu: int = 4, max_w: int = 0, max_h: int = 0):
+        self._L = load_library()
+        self._h = C.c_void_p()
+        arr, n = None, 0
+        if devices:
+            arr = (C.c_int * len(devices))(*devices)
+            n = len(devices)
+        rc = self._L.icb_init(arr, n, slots_per_gpu, max_w, max_h, C.byref(self._h))
+        if rc != ICB_OK:
+            self._h = C.c_void_p()
+            raise IcbError(rc, "icb_init failed (no CUDA device? this library has no CPU path)")
+        self._pinned = {}
+        self._inflight = {}
+
+    # ---- lifecycle ----
+    def close(self):
+        if getattr(self, "_h", None) and self._h.value:
+            for p in list(self._pinned.values()):
+                self._L.icb_free_pinned(p)
+            self._pinned.clear()
+            self._L.icb_shutdown(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _err(self, rc: int) -> IcbError:
+        return IcbError(rc, (self._L.icb_last_error(self._h) or b"").decode(errors="replace"))
+
+    @property
+    def device_count(self) -> int:
+        return self._L.icb_device_count(self._h)
+
+    def set_profile(self, table_mode: int = 0, jfif_minor: int = 2):
+        rc = self._L.icb_set_profile(self._h, table_mode, jfif_minor)
+        if rc:
+            raise self._err(rc)
+
+    def alloc_pinned(self, shape, dtype=np.uint8) -> np.ndarray:
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = self._L.icb_alloc_pinned(nbytes)
+        if not p:
+            raise IcbError(ICB_ERR_OOM, "pinned allocation failed")
+        buf = (C.c_uint8 * nbytes).from_address(p)
+        arr = np.frombuffer(buf, dtype=dtype).reshape(shape)
+        self._pinned[arr.ctypes.data] = p
+        return arr
+
+    # ---- core/ImageCompressionJpg.java:136-147 ----
+    def compress_jpg_to_stream(self, image: np.ndarray, quality: float, fmt: Optional[int] = None) -> bytes:
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        cap = w * h * 3 + 65536
+        while True:
+            out = np.empty(cap, np.uint8)
+            n = C.c_size_t(0)
+            rc = self._L.icb_jpg_encode(self._h, image.ctypes.data, w, h, pitch, fmt, C.c_float(quality),
+                                        out.ctypes.data, cap, C.byref(n))
+            if rc == ICB_ERR_CAPACITY and n.value > cap:
+                cap = n.value
+                continue
+            if rc:
+                raise self._err(rc)
+            return out[: n.value].tobytes()
+
+    # ---- core/ImageCompressionJpg.java:77-122 (+ :216-238, :158-200, :255-260) ----
+    def jpg_fit(self, image: np.ndarray, init_q: float, target: int, cached: Optional[LearnedParams] = None,
+                fmt: Optional[int] = None) -> FitResult:
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        cap = max(int(target), 0) + 16
+        out = np.empty(cap, np.uint8)
+        n, bq, sc, uc = C.c_size_t(0), C.c_float(0), C.c_double(0), C.c_int(0)
+        rc = self._L.icb_jpg_fit(self._h, image.ctypes.data, w, h, pitch, fmt, C.c_float(init_q), int(target),
+                                 1 if cached else 0, C.c_float(cached.quality if cached else 0.0),
+                                 C.c_double(cached.scale if cached else 1.0), out.ctypes.data, cap, C.byref(n),
+                                 C.byref(bq), C.byref(sc), C.byref(uc))
+        if rc < 0:
+            raise self._err(rc)
+        data = out[: n.value].tobytes() if rc == ICB_OK else None
+        return FitResult(rc, data, float(bq.value), float(sc.value), bool(uc.value), 0, 0, n.value)
+
+    def compress_jpg_with_target_size(self, original_image: np.ndarray, original_size: int, output_file,
+                                      params: CompressionParams,
+                                      cache: MutableMapping[SimilarityKey, LearnedParams],
+                                      fmt: Optional[int] = None) -> bool:
+        """Same contract as the Java static: returns True and writes output_file when a
+        (quality, scale) fits params.target_max_size_bytes, updating `cache` on a fresh search."""
+        if original_image is None or params is None or cache is None:
+            raise TypeError("null argument")
+        h, w = original_image.shape[:2]
+        key = create_key(w, h, original_size)                                   # :79
+        cached = cache.get(key)                                                 # :80
+        r = self.jpg_fit(original_image, params.quality, params.target_max_size_bytes, cached, fmt)
+        if r.status != ICB_OK:
+            return False                                                        # :120-121
+        if output_file is not None:
+            with open(output_file, "wb") as f:                                  # :258 / :229
+                f.write(r.data)
+        if not r.used_cache:
+            cache[key] = LearnedParams(r.best_q, r.scale)                       # :111
+        self.last_fit = r
+        return True
+
+    # ---- hooks ----
+    def jpg_sizes(self, image: np.ndarray, qualities, fmt: Optional[int] = None):
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        qs = np.ascontiguousarray(qualities, np.float32)
+        sizes = np.zeros(len(qs), np.int64)
+        rc = self._L.icb_jpg_sizes(self._h, image.ctypes.data, w, h, pitch, fmt,
+                                   qs.ctypes.data_as(C.POINTER(C.c_float)), len(qs),
+                                   sizes.ctypes.data_as(C.POINTER(C.c_int64)))
+        if rc:
+            raise self._err(rc)
+        return sizes
+
+    def jpg_coefficients(self, image: np.ndarray, fmt: Optional[int] = None) -> np.ndarray:
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        nblocks = 6 * ((w + 15) // 16) * ((h + 15) // 16)
+        out = np.zeros((nblocks, 64), np.int16)
+        rc = self._L.icb_jpg_coefficients(self._h, image.ctypes.data, w, h, pitch, fmt, out.ctypes.data, out.size)
+        if rc:
+            raise self._err(rc)
+        return out
+
+    # ---- tools/ImageTools.java:7-26 ----
+    def resize_dims(self, w: int, h: int, scale: float) -> Tuple[int, int]:
+        a, b = C.c_int(0), C.c_int(0)
+        self._L.icb_resize_dims(w, h, C.c_double(scale), C.byref(a), C.byref(b))
+        return a.value, b.value
+
+    def resize_image(self, original_image: np.ndarray, scale: float, fmt: Optional[int] = None) -> np.ndarray:
+        image, w, h, pitch, fmt = _image_args(original_image, fmt)
+        dw, dh = self.resize_dims(w, h, scale)
+        return self.resize_to(image, dw, dh, fmt)
+
+    def resize_to(self, image: np.ndarray, dw: int, dh: int, fmt: Optional[int] = None) -> np.ndarray:
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        c = image.shape[2]
+        dst = np.empty((dh, dw, c), np.uint8)
+        rc = self._L.icb_resize_bilinear(self._h, image.ctypes.data, w, h, pitch, fmt, dst.ctypes.data, dw, dh,
+                                         dw * c)
+        if rc:
+            raise self._err(rc)
+        return dst
+
+    # ---- core/ImageCompressionPng.java:37-75 (PNG file write stays with the caller) ----
+    def compress_png_with_target_size(self, original_image: np.ndarray, output_file, params: CompressionParams,
+                                      fmt: Optional[int] = None):
+        """-> (False, None) when the image already fits min_width x min_height (:49-53),
+        else (True, resized pixels).  None arguments raise TypeError (Java: NPE, :39-41)."""
+        if original_image is None:
+            raise TypeError("originalImage must not be null")
+        if output_file is None:
+            raise TypeError("outputFile must not be null")
+        if params is None:
+            raise TypeError("params must not be null")
+        image, w, h, pitch, fmt = _image_args(original_image, fmt)
+        c = image.shape[2]
+        dw, dh = C.c_int(0), C.c_int(0)
+        rc = self._L.icb_png_fit(self._h, image.ctypes.data, w, h, pitch, fmt, params.min_width, params.min_height,
+                                 None, 0, C.byref(dw), C.byref(dh))
+        if rc == ICB_NO_FIT:
+            return False, None
+        if rc:
+            raise self._err(rc)
+        dst = np.empty((dh.value, dw.value, c), np.uint8)
+        rc = self._L.icb_png_fit(self._h, image.ctypes.data, w, h, pitch, fmt, params.min_width, params.min_height,
+                                 dst.ctypes.data, dst.size, C.byref(dw), C.byref(dh))
+        if rc:
+            raise self._err(rc)
+        return True, dst
+
+    # ---- asynchronous queue (CompressionBatch.java:77-88 submit / :97-107 await) ----
+    def submit_jpg_fit(self, image: np.ndarray, init_q: float, target: int, out: np.ndarray,
+                       cached: Optional[LearnedParams] = None, fmt: Optional[int] = None) -> int:
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        t = C.c_int64(0)
+        rc = self._L.icb_submit_jpg_fit(self._h, image.ctypes.data, w, h, pitch, fmt, C.c_float(init_q), int(target),
+                                        1 if cached else 0, C.c_float(cached.quality if cached else 0.0),
+                                        C.c_double(cached.scale if cached else 1.0), out.ctypes.data, out.size,
+                                        C.byref(t))
+        if rc:
+            raise self._err(rc)
+        self._inflight[t.value] = (image, out)
+        return t.value
+
+    def submit_jpg_fit_image(self, img_handle, init_q: float, target: int, out: np.ndarray,
+                             cached: Optional[LearnedParams] = None) -> int:
+        t = C.c_int64(0)
+        rc = self._L.icb_submit_jpg_fit_image(self._h, img_handle, C.c_float(init_q), int(target),
+                                              1 if cached else 0, C.c_float(cached.quality if cached else 0.0),
+                                              C.c_double(cached.scale if cached else 1.0), out.ctypes.data, out.size,
+                                              C.byref(t))
+        if rc:
+            raise self._err(rc)
+        self._inflight[t.value] = (None, out)
+        return t.value
+
+    def submit_resize_image(self, img_handle, dw: int, dh: int, dst: np.ndarray) -> int:
+        t = C.c_int64(0)
+        rc = self._L.icb_submit_resize_image(self._h, img_handle, dw, dh, dst.ctypes.data, dst.strides[0],
+                                             C.byref(t))
+        if rc:
+            raise self._err(rc)
+        self._inflight[t.value] = (None, dst)
+        return t.value
+
+    def wait(self, ticket: int) -> FitResult:
+        r = _Result()
+        rc = self._L.icb_wait(self._h, ticket, C.byref(r))
+        self._inflight.pop(ticket, None)
+        if rc < 0:
+            raise self._err(rc)
+        return FitResult(rc, None, float(r.best_q), float(r.scale), bool(r.used_cache), int(r.n_passes),
+                         int(r.device), int(r.out_len))
+
+    # ---- resident images ----
+    def upload_image(self, image: np.ndarray, device_index: int = 0, fmt: Optional[int] = None):
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        p = C.c_void_p()
+        rc = self._L.icb_image_upload(self._h, device_index, image.ctypes.data, w, h, pitch, fmt, C.byref(p))
+        if rc:
+            raise self._err(rc)
+        return p
+
+    def free_image(self, img_handle):
+        self._L.icb_image_free(self._h, img_handle)
+
+    def profile_jpg_fit_image(self, img_handle, init_q: float, target: int, reps: int = 1):
+        a, b, c = C.c_float(0), C.c_float(0), C.c_float(0)
+        rc = self._L.icb_profile_jpg_fit_image(self._h, img_handle, C.c_float(init_q), int(target), reps,
+                                               C.byref(a), C.byref(b), C.byref(c))
+        if rc:
+            raise self._err(rc)
+        return float(a.value), float(b.value), float(c.value)
+
+    def stats(self) -> Dict[str, float]:
+        s = _Stats()
+        rc = self._L.icb_stats(self._h, C.byref(s))
+        if rc:
+            raise self._err(rc)
+        return {k: getattr(s, k) for k, _ in _Stats._fields_}

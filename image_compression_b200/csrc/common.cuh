@@ -1,0 +1,142 @@
+// common.cuh -- shared constants and device-side state for the sm_100a JPEG path.
+//
+// Arithmetic follows IJG libjpeg 6b as the JDK's JPEGImageWriter runs it
+// (reference call site: core/ImageCompressionJpg.java:137-143); section tags
+// a2.x refer to SURVEY.md section 8(a).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace icb {
+
+// ---- geometry (IJG jcmaster.c initial_setup, 3 components 2x2,1x1,1x1) ----
+struct Geom {
+    int w, h;
+    int pitch;              // device pitch in bytes (multiple of 16)
+    int bgr;                // 1 = BGR byte order
+    int mcu_cols, mcu_rows;
+    int yblk_w, yblk_h;     // real luma block counts
+    int crows_real;         // ceil(h/2): downsampled rows that come from pixels
+    int nblocks;            // 6 * mcu_cols * mcu_rows
+    int ntiles;             // entropy tiles = ceil(nblocks / 32)
+};
+
+__host__ __device__ inline Geom make_geom(int w, int h, int pitch, int bgr)
+{
+    Geom g;
+    g.w = w; g.h = h; g.pitch = pitch; g.bgr = bgr;
+    g.mcu_cols = (w + 15) >> 4;
+    g.mcu_rows = (h + 15) >> 4;
+    g.yblk_w = (w + 7) >> 3;
+    g.yblk_h = (h + 7) >> 3;
+    g.crows_real = (h + 1) >> 1;
+    g.nblocks = 6 * g.mcu_cols * g.mcu_rows;
+    g.ntiles = (g.nblocks + 31) >> 5;
+    return g;
+}
+
+// ---- transform kernel tiling ----
+constexpr int TILE_MCUS = 16;                       // MCUs per tile (one MCU row)
+constexpr int TILE_ROW_BYTES = TILE_MCUS * 48;      // 768 B of RGB per pixel row
+constexpr int TILE_IN_BYTES = TILE_ROW_BYTES * 16;  // 12 KB per TMA box
+constexpr int TILE_BLOCKS = TILE_MCUS * 6;          // 96 blocks
+constexpr int XF_THREADS = 128;
+constexpr int XF_STAGES = 2;
+
+// ---- entropy pass tiling ----
+constexpr int ENT_TILE_BLOCKS = 32;                 // blocks per warp tile
+constexpr int ENT_WARPS = 8;
+constexpr int ENT_THREADS = ENT_WARPS * 32;
+// worst case per block: DC 9+11 bits, 63 x (16+10) bits = 1658 bits -> 208 B
+constexpr int ENT_STAGE_WORDS = (ENT_TILE_BLOCKS * 208) / 4 + 4;   // per warp
+
+constexpr int HEADER_BYTES = 623;                   // a2.8, 3-component JFIF
+
+// ---- device state of one fit job (lives in HBM, one per slot) ----
+enum FitMode { MODE_SEARCH = 0, MODE_SINGLE = 1 };
+
+struct FitState {
+    // search control (core/ImageCompressionJpg.java:158-200), float32 as in Java
+    float lo, hi, best;
+    float cur_q;
+    int iter;               // iterations started
+    int done;
+    int cur_valid;          // the coming pass has work
+    int mode;
+    int cur_buf, best_buf;  // ping-pong output buffers
+    int epoch;              // descriptor epoch of the coming pass (1..31)
+    int n_trace;
+    int table_mode, jfif_minor;
+    int passes;             // entropy passes actually run
+    int pad0;
+    long long target;
+    long long cur_size, best_size;
+    float trace_q[8];
+    long long trace_size[8];
+    // tables of the coming pass, ZIGZAG order; [0]=luma [1]=chroma
+    unsigned int recip[2][64];      // ceil-ish 2^32 / (8 q): floor(t/(8q)) == umulhi(t, recip)
+    unsigned short half[2][64];     // 4 q
+    unsigned char qtab[2][64];
+    // pass scratch
+    unsigned int ticket;
+    unsigned int pad1;
+    unsigned long long ff_total;    // stuffed 0x00 bytes (= number of 0xFF data bytes)
+    unsigned long long total_bits;  // entropy-coded bits before padding
+};
+
+// ---- Annex K tables (T.81), natural order; IJG jcparam.c / JDK JPEGQTable ----
+__constant__ unsigned char c_base_lum[64] = {
+    16, 11, 10, 16, 24, 40, 51, 61, 12, 12, 14, 19, 26, 58, 60, 55,
+    14, 13, 16, 24, 40, 57, 69, 56, 14, 17, 22, 29, 51, 87, 80, 62,
+    18, 22, 37, 56, 68, 109, 103, 77, 24, 35, 55, 64, 81, 104, 113, 92,
+    49, 64, 78, 87, 103, 121, 120, 101, 72, 92, 95, 98, 112, 100, 103, 99};
+__constant__ unsigned char c_base_chr[64] = {
+    17, 18, 24, 47, 99, 99, 99, 99, 18, 21, 26, 66, 99, 99, 99, 99,
+    24, 26, 56, 99, 99, 99, 99, 99, 47, 66, 99, 99, 99, 99, 99, 99,
+    99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99,
+    99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99, 99};
+// zigzag index -> natural index
+__constant__ unsigned char c_zigzag[64] = {
+    0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5,
+    12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28,
+    35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51,
+    58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+
+// Huffman tables as they go into the DHT segments
+__constant__ unsigned char c_dc_bits[2][16] = {
+    {0, 1, 5, 1, 1, 1, 1, 1, 1, 0, 0, 0, 0, 0, 0, 0},
+    {0, 3, 1, 1, 1, 1, 1, 1, 1, 1, 1, 0, 0, 0, 0, 0}};
+__constant__ unsigned char c_ac_bits[2][16] = {
+    {0, 2, 1, 3, 3, 2, 4, 3, 5, 5, 4, 4, 0, 0, 1, 0x7d},
+    {0, 2, 1, 2, 4, 4, 3, 4, 7, 5, 4, 4, 0, 1, 2, 0x77}};
+__constant__ unsigned char c_ac_vals[2][162] = {
+    {0x01, 0x02, 0x03, 0x00, 0x04, 0x11, 0x05, 0x12, 0x21, 0x31, 0x41, 0x06, 0x13, 0x51, 0x61, 0x07,
+     0x22, 0x71, 0x14, 0x32, 0x81, 0x91, 0xa1, 0x08, 0x23, 0x42, 0xb1, 0xc1, 0x15, 0x52, 0xd1, 0xf0,
+     0x24, 0x33, 0x62, 0x72, 0x82, 0x09, 0x0a, 0x16, 0x17, 0x18, 0x19, 0x1a, 0x25, 0x26, 0x27, 0x28,
+     0x29, 0x2a, 0x34, 0x35, 0x36, 0x37, 0x38, 0x39, 0x3a, 0x43, 0x44, 0x45, 0x46, 0x47, 0x48, 0x49,
+     0x4a, 0x53, 0x54, 0x55, 0x56, 0x57, 0x58, 0x59, 0x5a, 0x63, 0x64, 0x65, 0x66, 0x67, 0x68, 0x69,
+     0x6a, 0x73, 0x74, 0x75, 0x76, 0x77, 0x78, 0x79, 0x7a, 0x83, 0x84, 0x85, 0x86, 0x87, 0x88, 0x89,
+     0x8a, 0x92, 0x93, 0x94, 0x95, 0x96, 0x97, 0x98, 0x99, 0x9a, 0xa2, 0xa3, 0xa4, 0xa5, 0xa6, 0xa7,
+     0xa8, 0xa9, 0xaa, 0xb2, 0xb3, 0xb4, 0xb5, 0xb6, 0xb7, 0xb8, 0xb9, 0xba, 0xc2, 0xc3, 0xc4, 0xc5,
+     0xc6, 0xc7, 0xc8, 0xc9, 0xca, 0xd2, 0xd3, 0xd4, 0xd5, 0xd6, 0xd7, 0xd8, 0xd9, 0xda, 0xe1, 0xe2,
+     0xe3, 0xe4, 0xe5, 0xe6, 0xe7, 0xe8, 0xe9, 0xea, 0xf1, 0xf2, 0xf3, 0xf4, 0xf5, 0xf6, 0xf7, 0xf8,
+     0xf9, 0xfa},
+    {0x00, 0x01, 0x02, 0x03, 0x11, 0x04, 0x05, 0x21, 0x31, 0x06, 0x12, 0x41, 0x51, 0x07, 0x61, 0x71,
+     0x13, 0x22, 0x32, 0x81, 0x08, 0x14, 0x42, 0x91, 0xa1, 0xb1, 0xc1, 0x09, 0x23, 0x33, 0x52, 0xf0,
+     0x15, 0x62, 0x72, 0xd1, 0x0a, 0x16, 0x24, 0x34, 0xe1, 0x25, 0xf1, 0x17, 0x18, 0x19, 0x1a, 0x26,
+     0x27, 0x28, 0x29, 0x2a, 0x35, 0x36, 0x37, 0x38, 0x39, 0x3a, 0x43, 0x44, 0x45, 0x46, 0x47, 0x48,
+     0x49, 0x4a, 0x53, 0x54, 0x55, 0x56, 0x57, 0x58, 0x59, 0x5a, 0x63, 0x64, 0x65, 0x66, 0x67, 0x68,
+     0x69, 0x6a, 0x73, 0x74, 0x75, 0x76, 0x77, 0x78, 0x79, 0x7a, 0x82, 0x83, 0x84, 0x85, 0x86, 0x87,
+     0x88, 0x89, 0x8a, 0x92, 0x93, 0x94, 0x95, 0x96, 0x97, 0x98, 0x99, 0x9a, 0xa2, 0xa3, 0xa4, 0xa5,
+     0xa6, 0xa7, 0xa8, 0xa9, 0xaa, 0xb2, 0xb3, 0xb4, 0xb5, 0xb6, 0xb7, 0xb8, 0xb9, 0xba, 0xc2, 0xc3,
+     0xc4, 0xc5, 0xc6, 0xc7, 0xc8, 0xc9, 0xca, 0xd2, 0xd3, 0xd4, 0xd5, 0xd6, 0xd7, 0xd8, 0xd9, 0xda,
+     0xe2, 0xe3, 0xe4, 0xe5, 0xe6, 0xe7, 0xe8, 0xe9, 0xea, 0xf2, 0xf3, 0xf4, 0xf5, 0xf6, 0xf7, 0xf8,
+     0xf9, 0xfa}};
+
+// Derived encode tables (jchuff.c jpeg_make_c_derived_tbl), filled by the host at
+// init: entry = (code << 8) | length.  [table][symbol]
+__constant__ unsigned int c_dc_enc[2][16];
+__constant__ unsigned int c_ac_enc[2][256];
+
+}  // namespace icb

@@ -1,0 +1,167 @@
+/*
+ * imgcomp_b200.h -- C ABI of the B200-native JPG target-size / bilinear-downscale
+ * hot path of PolloChang/image-compression.
+ *
+ * The reference has no FFI of its own: the path sits behind four static Java
+ * methods.  Each entry point below names the reference
+ * seam it replaces; INTEGRATION.md shows the java.lang.foreign (Panama FFM)
+ * downcall a maintainer binds to it.  Plain pointers and sizes only; the library
+ * never throws or aborts -- every call returns an icb_status.
+ *
+ * All citations are into /root/reference/src/main/java/work/pollochang/compression/image/.
+ */
+#ifndef IMGCOMP_B200_H
+#define IMGCOMP_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Status codes.  Mapping to core/CompressionResult.java:3-16 (done by the Java
+ * caller, core/ImageCompression.java:81-104):
+ *   ICB_OK          -> seam returns true  -> COMPRESSED_SUCCESS
+ *   ICB_NO_FIT      -> seam returns false -> FAILED_COMPRESSION (output deleted)
+ *   ICB_ERR_OOM     -> OutOfMemoryError   -> FAILED_OUT_OF_MEMORY
+ *   ICB_ERR_INVALID -> NullPointerException / IllegalArgumentException
+ *   ICB_ERR_UNSUPPORTED -> fall back to the stock Java path (gray / CMYK / ICC)
+ *   other negatives -> FAILED_UNKNOWN */
+typedef enum {
+    ICB_OK = 0,
+    ICB_NO_FIT = 1,
+    ICB_ERR_INVALID = -1,
+    ICB_ERR_OOM = -2,
+    ICB_ERR_CUDA = -3,
+    ICB_ERR_UNSUPPORTED = -4,
+    ICB_ERR_CAPACITY = -5,   /* caller's output buffer too small; *out_len = needed */
+    ICB_ERR_NO_DEVICE = -6,
+    ICB_ERR_TICKET = -7
+} icb_status;
+
+/* Pixel formats = byte order in memory of the decoded BufferedImage raster. */
+typedef enum {
+    ICB_FMT_RGB8 = 0,    /* what JPEGImageWriter hands libjpeg                       */
+    ICB_FMT_BGR8 = 1,    /* BufferedImage.TYPE_3BYTE_BGR (ImageIO JPEG reader)       */
+    ICB_FMT_RGBA8 = 2,   /* resize only                                              */
+    ICB_FMT_ABGR8 = 3    /* BufferedImage.TYPE_4BYTE_ABGR (ImageIO PNG reader); resize only */
+} icb_fmt;
+
+typedef struct icb_handle icb_handle;
+typedef struct icb_image icb_image;      /* a decoded image resident in one GPU's HBM */
+
+/* Pool creation.  Replaces Executors.newFixedThreadPool(availableProcessors)
+ * (CompressionBatch.java:64-68): every listed GPU gets `slots_per_gpu` work
+ * slots, each a CUDA stream + device arenas sized for max_w x max_h (grown on
+ * demand).  devices == NULL / n_devices == 0 means "every visible GPU". */
+int icb_init(const int *devices, int n_devices, int slots_per_gpu, int max_w, int max_h,
+             icb_handle **out_handle);
+void icb_shutdown(icb_handle *h);
+int icb_device_count(const icb_handle *h);
+const char *icb_last_error(const icb_handle *h);
+
+/* [JDK-mem] switches kept in one place (SURVEY.md section 7 hard part 3):
+ * table_mode 0 = JDK float32 JPEG.convertToLinearQuality + getScaledInstance,
+ * 1 = IJG integer jpeg_quality_scaling; jfif_minor = APP0 version byte (JDK 2). */
+int icb_set_profile(icb_handle *h, int table_mode, int jfif_minor);
+
+/* Page-locked host staging for FFM MemorySegments (decode straight into these). */
+void *icb_alloc_pinned(size_t bytes);
+void icb_free_pinned(void *p);
+
+/* core/ImageCompressionJpg.java:77-122 compressJpgWithTargetSize, including
+ * :216-238 tryCachedParams, :158-200 findBestQualityByBinarySearch and :255-260
+ * saveCompressedImage.  File write (:258) and cache.put (:111) stay in Java: the
+ * JFIF bytes and the learned (best_q, scale) come back instead.
+ *   px/pitch/fmt : decoded pixels (RGB8 or BGR8), caller-owned
+ *   init_q       : CompressionParams.quality()      target: targetMaxSizeBytes()
+ *   has_cached / cached_q / cached_scale : cache.get(key) (LearnedParams.java:8)
+ *   out/out_cap  : caller-owned output buffer; out_len <= target on ICB_OK */
+int icb_jpg_fit(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, int fmt,
+                float init_q, int64_t target,
+                int has_cached, float cached_q, double cached_scale,
+                uint8_t *out, size_t out_cap, size_t *out_len,
+                float *best_q, double *scale, int *used_cache);
+
+/* core/ImageCompressionJpg.java:136-147 compressJpgToStream(image, os, quality):
+ * one baseline JFIF encode at an explicit quality. */
+int icb_jpg_encode(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, int fmt,
+                   float q, uint8_t *out, size_t out_cap, size_t *out_len);
+
+/* Test / bench hook (no reference seam): exact stuffed stream size of the same
+ * image at each of n qualities, one forward transform. */
+int icb_jpg_sizes(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, int fmt,
+                  const float *qs, int n, int64_t *sizes);
+
+/* Test hook: the unquantised islow coefficients the transform kernel produced
+ * (MCU-interleaved block order, 64 int16 per block, zigzag order). */
+int icb_jpg_coefficients(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, int fmt,
+                         int16_t *out, size_t out_elems);
+
+/* tools/ImageTools.java:7-26 resizeImage: bilinear drawImage into dw x dh.
+ * icb_resize_dims is lines :8-9 (newW = max(1,(int)(w*scale))). */
+void icb_resize_dims(int w, int hgt, double scale, int *dw, int *dh);
+int icb_resize_bilinear(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt,
+                        uint8_t *dst, int dw, int dh, int dpitch);
+
+/* core/ImageCompressionPng.java:37-75 compressPngWithTargetSize up to (not
+ * including) ImageIO.write :70, which stays on the host: dimension rule :49-61,
+ * then the resize.  ICB_NO_FIT = "already within min_w x min_h" (:49-53 returns
+ * false).  dst must hold dw*dh*bpp bytes (query with dst == NULL first). */
+int icb_png_fit(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt,
+                int min_w, int min_h, uint8_t *dst, size_t dst_cap, int *dw, int *dh);
+
+/* Asynchronous form = the per-GPU stream work queue that replaces the executor
+ * (CompressionBatch.java:77-88 submit, :97-107 await).  submit blocks only while
+ * every slot is busy; wait returns that job's status and releases the slot.
+ * Host buffers must stay valid until wait returns (pinned ones copy async). */
+typedef struct {
+    int status;
+    size_t out_len;
+    float best_q;
+    double scale;
+    int used_cache;
+    int n_passes;       /* entropy passes run on the device for this image */
+    int device;
+} icb_result;
+
+int icb_submit_jpg_fit(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, int fmt,
+                       float init_q, int64_t target,
+                       int has_cached, float cached_q, double cached_scale,
+                       uint8_t *out, size_t out_cap, int64_t *ticket);
+int icb_wait(icb_handle *h, int64_t ticket, icb_result *res);
+
+/* Device-resident inputs (bench `value`: pixels already in HBM when timing starts). */
+int icb_image_upload(icb_handle *h, int device_index, const uint8_t *px, int w, int hgt, int pitch,
+                     int fmt, icb_image **img);
+void icb_image_free(icb_handle *h, icb_image *img);
+int icb_submit_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q, int64_t target,
+                             int has_cached, float cached_q, double cached_scale,
+                             uint8_t *out, size_t out_cap, int64_t *ticket);
+int icb_submit_resize_image(icb_handle *h, const icb_image *img, int dw, int dh,
+                            uint8_t *dst, int dpitch, int64_t *ticket);
+
+/* Counters (CompressionBatch.java:56-62 are summed by the Java caller; these are
+ * the device-side ones) and per-stage CUDA-event times of the last profiled job. */
+typedef struct {
+    uint64_t images_done;
+    uint64_t kernels_launched;     /* every kernel this library launched */
+    uint64_t entropy_passes;
+    uint64_t h2d_bytes, d2h_bytes;
+    float last_transform_ms;       /* set by icb_profile_jpg_fit_image only */
+    float last_entropy_ms;
+    float last_total_ms;
+    int last_transform_launches, last_entropy_launches;
+} icb_stats_t;
+int icb_stats(icb_handle *h, icb_stats_t *out);
+
+/* Runs one fit on a resident image with CUDA events around the transform kernel
+ * and around the entropy passes, on the slot's own stream (bench roofline). */
+int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q, int64_t target,
+                              int reps, float *transform_ms, float *entropy_ms, float *total_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
