@@ -27,6 +27,7 @@ ABI_SYMBOLS = [
     "icb_jpg_coefficients", "icb_resize_dims", "icb_resize_bilinear", "icb_png_fit",
     "icb_submit_jpg_fit", "icb_wait", "icb_image_upload", "icb_image_free",
     "icb_submit_jpg_fit_image", "icb_submit_resize_image", "icb_stats", "icb_profile_jpg_fit_image",
+    "icb_mark", "icb_elapsed_ms",
 ]
 
 
@@ -103,7 +104,10 @@ def load_library(build_if_missing: bool = True):
     L.icb_submit_resize_image.argtypes = [vp, vp, C.c_int, C.c_int, vp, C.c_int, C.POINTER(C.c_int64)]
     L.icb_stats.argtypes = [vp, C.POINTER(_Stats)]
     L.icb_profile_jpg_fit_image.argtypes = [vp, vp, C.c_float, C.c_int64, C.c_int, C.POINTER(C.c_float),
-                                            C.POINTER(C.c_float), C.POINTER(C.c_float)]
+                                            C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float),
+                                            C.POINTER(C.c_int)]
+    L.icb_mark.argtypes = [vp, C.c_int, C.c_int]
+    L.icb_elapsed_ms.argtypes = [vp, C.c_int, C.POINTER(C.c_float)]
     _lib = L
     return L
 
@@ -403,12 +407,26 @@ class Engine:
         self._L.icb_image_free(self._h, img_handle)
 
     def profile_jpg_fit_image(self, img_handle, init_q: float, target: int, reps: int = 1):
-        a, b, c = C.c_float(0), C.c_float(0), C.c_float(0)
+        """-> dict(transform_ms, search_ms, total_ms, entropy_kernel_ms, entropy_kernel_launches)"""
+        a, b, c, d, n = C.c_float(0), C.c_float(0), C.c_float(0), C.c_float(0), C.c_int(0)
         rc = self._L.icb_profile_jpg_fit_image(self._h, img_handle, C.c_float(init_q), int(target), reps,
-                                               C.byref(a), C.byref(b), C.byref(c))
+                                               C.byref(a), C.byref(b), C.byref(c), C.byref(d), C.byref(n))
         if rc:
             raise self._err(rc)
-        return float(a.value), float(b.value), float(c.value)
+        return dict(transform_ms=float(a.value), search_ms=float(b.value), total_ms=float(c.value),
+                    entropy_kernel_ms=float(d.value), entropy_kernel_launches=int(n.value))
+
+    def mark(self, device_index: int, which: int):
+        rc = self._L.icb_mark(self._h, device_index, which)
+        if rc:
+            raise self._err(rc)
+
+    def elapsed_ms(self, device_index: int) -> float:
+        ms = C.c_float(0)
+        rc = self._L.icb_elapsed_ms(self._h, device_index, C.byref(ms))
+        if rc:
+            raise self._err(rc)
+        return float(ms.value)
 
     def stats(self) -> Dict[str, float]:
         s = _Stats()

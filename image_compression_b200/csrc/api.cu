@@ -35,6 +35,9 @@ typedef CUresult (*PFN_encodeTiled)(CUtensorMap *, CUtensorMapDataType, cuuint32
 struct DeviceCtx {
     int dev = 0;
     int sms = 148;
+    cudaStream_t timer_stream = nullptr;    // icb_mark: joins every slot stream of this GPU
+    cudaEvent_t mark[2] = {nullptr, nullptr};
+    cudaEvent_t join = nullptr;
 };
 
 enum Phase { PH_IDLE = 0, PH_CACHED, PH_SEARCH, PH_RESIZE };
@@ -271,7 +274,7 @@ int max_search_iters(float init_q)
 }
 
 int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, int npairs, bool emit,
-                   long long dev_cap)
+                   long long dev_cap, cudaEvent_t *pass_ev = nullptr)
 {
     const Geom &g = s->geom;
     // descriptor epochs restart at 1 with every k_init_state: clear the old ones
@@ -291,7 +294,9 @@ int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, 
     const int grid = (g.ntiles + ENT_WARPS - 1) / ENT_WARPS;
     for (int i = 0; i < npairs; i++) {
         k_step<<<1, 128, 0, s->stream>>>(s->d_state, ep.out0, ep.out1, dev_cap, g.w, g.h, 0);
+        if (pass_ev) cudaEventRecord(pass_ev[2 * i], s->stream);
         k_entropy<<<grid, ENT_THREADS, ENT_SMEM_BYTES, s->stream>>>(ep);
+        if (pass_ev) cudaEventRecord(pass_ev[2 * i + 1], s->stream);
         h->kernels += 2;
     }
     k_step<<<1, 128, 0, s->stream>>>(s->d_state, ep.out0, ep.out1, dev_cap, g.w, g.h, 1);
@@ -900,17 +905,21 @@ int icb_stats(icb_handle *h, icb_stats_t *out)
 }
 
 int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q, int64_t target, int reps,
-                              float *transform_ms, float *entropy_ms, float *total_ms)
+                              float *transform_ms, float *entropy_ms, float *total_ms, float *entropy_kernel_ms,
+                              int *entropy_kernel_launches)
 {
     if (!h || !img || reps < 1) return ICB_ERR_INVALID;
     if (img->fmt != ICB_FMT_RGB8 && img->fmt != ICB_FMT_BGR8) return fail(h, ICB_ERR_UNSUPPORTED, "format");
     Slot *s = acquire_slot(h, img->devi);
     int rc = ICB_OK;
-    cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr;
-    float xf = 0, ent = 0;
+    cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr, pe[16] = {nullptr};
+    float xf = 0, ent = 0, entk = 0;
+    int launches = 0;
     do {
-        if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess || cudaEventCreate(&e0) != cudaSuccess ||
-            cudaEventCreate(&e1) != cudaSuccess || cudaEventCreate(&e2) != cudaSuccess) { rc = ICB_ERR_CUDA; break; }
+        bool ok = cudaSetDevice(h->devs[s->devi].dev) == cudaSuccess && cudaEventCreate(&e0) == cudaSuccess &&
+                  cudaEventCreate(&e1) == cudaSuccess && cudaEventCreate(&e2) == cudaSuccess;
+        for (int i = 0; i < 16 && ok; i++) ok = cudaEventCreate(&pe[i]) == cudaSuccess;
+        if (!ok) { rc = ICB_ERR_CUDA; break; }
         for (int r = 0; r < reps && !rc; r++) {
             const uint64_t k0 = h->kernels.load();
             cudaEventRecord(e0, s->stream);
@@ -921,16 +930,26 @@ int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q,
             const long long cap = std::min<long long>(target, worst_stream_bytes(s->geom));
             rc = ensure_out(h, s, cap);
             if (rc) break;
-            rc = enqueue_passes(h, s, MODE_SEARCH, init_q, target, max_search_iters(init_q), true, cap);
+            const int npairs = max_search_iters(init_q);
+            rc = enqueue_passes(h, s, MODE_SEARCH, init_q, target, npairs, true, cap, pe);
             if (rc) break;
             cudaEventRecord(e2, s->stream);
-            cudaError_t e = cudaStreamSynchronize(s->stream);
+            cudaError_t e = cudaMemcpyAsync(s->h_state, s->d_state, sizeof(FitState), cudaMemcpyDeviceToHost,
+                                            s->stream);
+            if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
             if (e != cudaSuccess) { rc = fail(h, ICB_ERR_CUDA, "profile", e); break; }
             float a = 0, b = 0;
             cudaEventElapsedTime(&a, e0, e1);
             cudaEventElapsedTime(&b, e1, e2);
             xf += a;
             ent += b;
+            launches = std::min(s->h_state->passes, npairs);       // passes that did work
+            for (int i = 0; i < launches; i++) {
+                float c = 0;
+                cudaEventElapsedTime(&c, pe[2 * i], pe[2 * i + 1]);
+                entk += c;
+            }
+            h->passes += (uint64_t)s->h_state->passes;
             h->last_xf_launches = (int)(k1 - k0);
             h->last_ent_launches = (int)(h->kernels.load() - k1);
         }
@@ -939,16 +958,53 @@ int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q,
     if (e0) cudaEventDestroy(e0);
     if (e1) cudaEventDestroy(e1);
     if (e2) cudaEventDestroy(e2);
+    for (int i = 0; i < 16; i++) if (pe[i]) cudaEventDestroy(pe[i]);
     xf /= (float)reps;
     ent /= (float)reps;
+    entk /= (float)reps;
     h->last_xf_ms = xf;
     h->last_ent_ms = ent;
     h->last_total_ms = xf + ent;
     if (transform_ms) *transform_ms = xf;
     if (entropy_ms) *entropy_ms = ent;
     if (total_ms) *total_ms = xf + ent;
+    if (entropy_kernel_ms) *entropy_kernel_ms = entk;
+    if (entropy_kernel_launches) *entropy_kernel_launches = launches;
     release_slot(h, s);
     return rc;
+}
+
+// Device-side stopwatch over ALL slot streams of one GPU: mark(0) before the first
+// submit, mark(1) after the last wait; elapsed = CUDA-event time between them.
+int icb_mark(icb_handle *h, int device_index, int which)
+{
+    if (!h || device_index < 0 || device_index >= (int)h->devs.size() || which < 0 || which > 1) return ICB_ERR_INVALID;
+    DeviceCtx &d = h->devs[device_index];
+    CK(cudaSetDevice(d.dev));
+    if (!d.timer_stream) {
+        CK(cudaStreamCreateWithFlags(&d.timer_stream, cudaStreamNonBlocking));
+        CK(cudaEventCreate(&d.mark[0]));
+        CK(cudaEventCreate(&d.mark[1]));
+        CK(cudaEventCreateWithFlags(&d.join, cudaEventDisableTiming));
+    }
+    for (Slot &s : h->slots) {
+        if (s.devi != device_index) continue;
+        CK(cudaEventRecord(d.join, s.stream));
+        CK(cudaStreamWaitEvent(d.timer_stream, d.join, 0));
+    }
+    CK(cudaEventRecord(d.mark[which], d.timer_stream));
+    return ICB_OK;
+}
+
+int icb_elapsed_ms(icb_handle *h, int device_index, float *ms)
+{
+    if (!h || !ms || device_index < 0 || device_index >= (int)h->devs.size()) return ICB_ERR_INVALID;
+    DeviceCtx &d = h->devs[device_index];
+    if (!d.timer_stream) return fail(h, ICB_ERR_INVALID, "icb_mark not called");
+    CK(cudaSetDevice(d.dev));
+    CK(cudaEventSynchronize(d.mark[1]));
+    CK(cudaEventElapsedTime(ms, d.mark[0], d.mark[1]));
+    return ICB_OK;
 }
 
 }  // extern "C"

@@ -33,11 +33,8 @@ def _texture(rng: np.random.Generator, h: int, w: int, beta: float) -> np.ndarra
     x0 = np.minimum(xs.astype(np.int32), ww - 2)
     fyv = (ys - y0)[:, None]
     fxv = (xs - x0)[None, :]
-    a = t[y0][:, x0]
-    b = t[y0][:, x0 + 1]
-    c = t[y0 + 1][:, x0]
-    d = t[y0 + 1][:, x0 + 1]
-    return (a * (1 - fxv) + b * fxv) * (1 - fyv) + (c * (1 - fxv) + d * fxv) * fyv
+    rows = t[y0] * (1 - fyv) + t[y0 + 1] * fyv            # separable: rows first, then columns
+    return rows[:, x0] * (1 - fxv) + rows[:, x0 + 1] * fxv
 
 
 def natural_image(index: int, w: int, h: int, channels: int = 3) -> np.ndarray:

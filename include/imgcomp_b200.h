@@ -156,10 +156,18 @@ typedef struct {
 } icb_stats_t;
 int icb_stats(icb_handle *h, icb_stats_t *out);
 
-/* Runs one fit on a resident image with CUDA events around the transform kernel
- * and around the entropy passes, on the slot's own stream (bench roofline). */
+/* Runs one fit on a resident image with CUDA events, on the slot's own stream,
+ * around the transform kernel, around the whole search (step + entropy + publish
+ * kernels) and around every entropy-pass launch that did work (bench roofline). */
 int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q, int64_t target,
-                              int reps, float *transform_ms, float *entropy_ms, float *total_ms);
+                              int reps, float *transform_ms, float *entropy_ms, float *total_ms,
+                              float *entropy_kernel_ms, int *entropy_kernel_launches);
+
+/* Device-side stopwatch over all slot streams of one GPU (bench timing with CUDA
+ * events although the work runs on library-owned streams): icb_mark(.., 0) before
+ * the first submit, icb_mark(.., 1) after the last wait, then icb_elapsed_ms. */
+int icb_mark(icb_handle *h, int device_index, int which);
+int icb_elapsed_ms(icb_handle *h, int device_index, float *ms);
 
 #ifdef __cplusplus
 }
