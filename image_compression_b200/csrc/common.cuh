@@ -50,6 +50,7 @@ constexpr int ENT_WARPS = 8;
 constexpr int ENT_THREADS = ENT_WARPS * 32;
 // worst case per block: DC 9+11 bits, 63 x (16+10) bits = 1658 bits -> 208 B
 constexpr int ENT_STAGE_WORDS = (ENT_TILE_BLOCKS * 208) / 4 + 4;   // per warp
+constexpr int ENT_RING = 512;                       // symbol-entry ring per warp (power of two)
 
 constexpr int HEADER_BYTES = 623;                   // a2.8, 3-component JFIF
 
