@@ -67,8 +67,8 @@ struct Slot {
     unsigned char *d_rgb = nullptr;   size_t rgb_cap = 0;
     unsigned char *d_rgb2 = nullptr;  size_t rgb2_cap = 0;
     int16_t *d_coef = nullptr;        size_t coef_cap = 0;      // bytes
-    unsigned long long *d_desc = nullptr; size_t desc_cap = 0;  // tiles
-    unsigned char *d_out[2] = {nullptr, nullptr}; size_t out_cap = 0;
+    unsigned char *d_pass = nullptr;  size_t pass_cap = 0;      // 2 x entropy pass arena (ping-pong)
+    unsigned char *d_out = nullptr;   size_t out_cap = 0;       // final JFIF stream
     FitState *d_state = nullptr;
     FitState *h_state = nullptr;            // pinned
     Geom geom{};
@@ -181,7 +181,7 @@ int setup_device(icb_handle *h, DeviceCtx &d)
     CK(cudaMemcpyToSymbol(c_hdr, hdr, HEADER_BYTES));
     CK(cudaFuncSetAttribute(k_transform<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_transform<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
-    CK(cudaFuncSetAttribute(k_entropy, cudaFuncAttributeMaxDynamicSharedMemorySize, ENT_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_entropy_symbols, cudaFuncAttributeMaxDynamicSharedMemorySize, ENT_SMEM_BYTES));
     return ICB_OK;
 }
 
@@ -236,12 +236,6 @@ int enqueue_transform(icb_handle *h, Slot *s, const unsigned char *d_px, int w, 
     s->geom = g;
     int rc = ensure(h, s->d_coef, s->coef_cap, (size_t)g.nblocks * 128);
     if (rc) return rc;
-    {
-        size_t cap_bytes = s->desc_cap * 16, need = (size_t)g.ntiles * 16;
-        rc = ensure(h, s->d_desc, cap_bytes, need);
-        if (rc) return rc;
-        s->desc_cap = cap_bytes / 16;
-    }
     CUtensorMap tmap;
     const cuuint64_t gdim[2] = {(cuuint64_t)(pitch / 4), (cuuint64_t)hgt};
     const cuuint64_t gstr[1] = {(cuuint64_t)pitch};
@@ -277,33 +271,41 @@ int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, 
                    long long dev_cap, cudaEvent_t *pass_ev = nullptr)
 {
     const Geom &g = s->geom;
-    // descriptor epochs restart at 1 with every k_init_state: clear the old ones
-    CK(cudaMemsetAsync(s->d_desc, 0, (size_t)g.ntiles * 16, s->stream));
-    k_init_state<<<1, 32, 0, s->stream>>>(s->d_state, mode, q, target, h->table_mode, h->jfif_minor);
-    h->kernels++;
+    const size_t per = round_up(ent_pass_bytes(g.ntiles), 256);
+    int rc = ensure(h, s->d_pass, s->pass_cap, 2 * per);
+    if (rc) return rc;
     EntParams ep;
     ep.coef = s->d_coef;
     ep.st = s->d_state;
-    ep.desc_bits = s->d_desc;
-    ep.desc_bytes = s->d_desc + g.ntiles;
-    ep.out0 = emit ? s->d_out[0] : nullptr;
-    ep.out1 = emit ? s->d_out[1] : nullptr;
-    ep.out_cap = dev_cap;
     ep.nblocks = g.nblocks;
     ep.ntiles = g.ntiles;
+    for (int b = 0; b < 2; b++) {
+        unsigned char *base = s->d_pass + (size_t)b * per;
+        const size_t n = (size_t)g.ntiles;
+        ep.buf[b].scratch = reinterpret_cast<uint32_t *>(base);
+        base += n * ENT_SCR_STRIDE * 4;
+        ep.buf[b].P = reinterpret_cast<unsigned long long *>(base);
+        base += n * 8;
+        ep.buf[b].Q = reinterpret_cast<unsigned long long *>(base);
+        base += n * 8;
+        ep.buf[b].L = reinterpret_cast<unsigned int *>(base);
+        base += n * 4;
+        ep.buf[b].bytes = reinterpret_cast<unsigned int *>(base);
+    }
+    k_begin<<<1, 128, 0, s->stream>>>(s->d_state, mode, q, target, h->table_mode, h->jfif_minor);
+    h->kernels++;
     const int grid = (g.ntiles + ENT_WARPS - 1) / ENT_WARPS;
     for (int i = 0; i < npairs; i++) {
-        k_step<<<1, 128, 0, s->stream>>>(s->d_state, ep.out0, ep.out1, dev_cap, g.w, g.h, 0);
         if (pass_ev) cudaEventRecord(pass_ev[2 * i], s->stream);
-        k_entropy<<<grid, ENT_THREADS, ENT_SMEM_BYTES, s->stream>>>(ep);
+        k_entropy_symbols<<<grid, ENT_THREADS, ENT_SMEM_BYTES, s->stream>>>(ep);
+        k_entropy_count<<<grid, ENT_THREADS, 0, s->stream>>>(ep);
         if (pass_ev) cudaEventRecord(pass_ev[2 * i + 1], s->stream);
         h->kernels += 2;
     }
-    k_step<<<1, 128, 0, s->stream>>>(s->d_state, ep.out0, ep.out1, dev_cap, g.w, g.h, 1);
-    h->kernels++;
     if (emit) {
-        k_publish<<<64, 256, 0, s->stream>>>(s->d_state, s->d_out[0], s->d_out[1], dev_cap);
-        h->kernels++;
+        k_finish<<<1, ENT_THREADS, 0, s->stream>>>(ep, s->d_out, dev_cap, g.w, g.h);
+        k_entropy_emit<<<grid, ENT_THREADS, 0, s->stream>>>(ep, s->d_out, dev_cap);
+        h->kernels += 2;
     }
     CK(cudaGetLastError());
     return ICB_OK;
@@ -391,13 +393,8 @@ int fit_enqueue_phase(icb_handle *h, Slot *s)
     if (cap < 0) cap = 0;
     j.dev_cap = cap;
     {
-        size_t c0 = s->out_cap, c1 = s->out_cap;
-        const size_t need = round_up((size_t)cap, 16) + 32;
-        int rc = ensure(h, s->d_out[0], c0, need);
+        int rc = ensure(h, s->d_out, s->out_cap, round_up((size_t)cap, 16) + 32);
         if (rc) return rc;
-        rc = ensure(h, s->d_out[1], c1, need);
-        if (rc) return rc;
-        s->out_cap = std::min(c0, c1);
     }
     int rc;
     if (j.phase == PH_CACHED)
@@ -408,7 +405,7 @@ int fit_enqueue_phase(icb_handle *h, Slot *s)
     CK(cudaMemcpyAsync(s->h_state, s->d_state, sizeof(FitState), cudaMemcpyDeviceToHost, s->stream));
     const size_t ncopy = (size_t)std::min<long long>((long long)j.out_cap, cap);
     if (ncopy && j.out) {
-        CK(cudaMemcpyAsync(j.out, s->d_out[0], ncopy, cudaMemcpyDeviceToHost, s->stream));
+        CK(cudaMemcpyAsync(j.out, s->d_out, ncopy, cudaMemcpyDeviceToHost, s->stream));
         h->d2h += ncopy;
     }
     h->d2h += sizeof(FitState);
@@ -557,8 +554,8 @@ void icb_shutdown(icb_handle *h)
     for (Slot &s : h->slots) {
         if (s.devi < (int)h->devs.size()) cudaSetDevice(h->devs[s.devi].dev);
         if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); }
-        cudaFree(s.d_rgb); cudaFree(s.d_rgb2); cudaFree(s.d_coef); cudaFree(s.d_desc);
-        cudaFree(s.d_out[0]); cudaFree(s.d_out[1]); cudaFree(s.d_state);
+        cudaFree(s.d_rgb); cudaFree(s.d_rgb2); cudaFree(s.d_coef); cudaFree(s.d_pass);
+        cudaFree(s.d_out); cudaFree(s.d_state);
         if (s.h_state) cudaFreeHost(s.h_state);
     }
     delete h;
@@ -712,12 +709,7 @@ int stage_and_transform(icb_handle *h, Slot *s, const uint8_t *px, int w, int hg
 
 int ensure_out(icb_handle *h, Slot *s, long long cap)
 {
-    size_t c0 = s->out_cap, c1 = s->out_cap;
-    const size_t need = round_up((size_t)cap, 16) + 32;
-    int rc = ensure(h, s->d_out[0], c0, need);
-    if (!rc) rc = ensure(h, s->d_out[1], c1, need);
-    s->out_cap = std::min(c0, c1);
-    return rc;
+    return ensure(h, s->d_out, s->out_cap, round_up((size_t)cap, 16) + 32);
 }
 
 }  // namespace
@@ -750,7 +742,7 @@ int icb_jpg_encode(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, 
         if (size > cap) {
             rc = ICB_ERR_CAPACITY;
         } else {
-            cudaError_t e = cudaMemcpyAsync(out, s->d_out[0], (size_t)size, cudaMemcpyDeviceToHost, s->stream);
+            cudaError_t e = cudaMemcpyAsync(out, s->d_out, (size_t)size, cudaMemcpyDeviceToHost, s->stream);
             if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
             if (e != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "encode D2H", e);
             h->d2h += (uint64_t)size;

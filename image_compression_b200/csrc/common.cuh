@@ -49,7 +49,8 @@ constexpr int ENT_TILE_BLOCKS = 32;                 // blocks per warp tile
 constexpr int ENT_WARPS = 8;
 constexpr int ENT_THREADS = ENT_WARPS * 32;
 // worst case per block: DC 9+11 bits, 63 x (16+10) bits = 1658 bits -> 208 B
-constexpr int ENT_STAGE_WORDS = (ENT_TILE_BLOCKS * 208) / 4 + 4;   // per warp
+constexpr int ENT_SCR_STRIDE = (ENT_TILE_BLOCKS * 208) / 4 + 4;    // scratch words per tile
+constexpr int ENT_WIN = 256;                        // shared-memory bit window per warp (words)
 constexpr int ENT_RING = 512;                       // symbol-entry ring per warp (power of two)
 
 constexpr int HEADER_BYTES = 623;                   // a2.8, 3-component JFIF
@@ -79,9 +80,11 @@ struct FitState {
     unsigned int recip[2][64];      // ceil-ish 2^32 / (8 q): floor(t/(8q)) == umulhi(t, recip)
     unsigned short half[2][64];     // 4 q
     unsigned char qtab[2][64];
+    unsigned char best_qtab[2][64]; // tables of the best pass so far (header of the final stream)
     // pass scratch
-    unsigned int ticket;
-    unsigned int pad1;
+    unsigned int done_a, done_c;    // finished CTAs of k_entropy_symbols / k_entropy_count
+    int emit_valid;
+    int pad1;
     unsigned long long ff_total;    // stuffed 0x00 bytes (= number of 0xFF data bytes)
     unsigned long long total_bits;  // entropy-coded bits before padding
 };
