@@ -29,4 +29,6 @@ from .api import (  # noqa: F401
     create_key,
     library_path,
     load_library,
+    png_target_dims,
+    resize_dims,
 )

@@ -24,7 +24,7 @@ _LIB_PATH = os.path.join(_HERE, "libimgcomp_b200.so")
 ABI_SYMBOLS = [
     "icb_init", "icb_shutdown", "icb_device_count", "icb_last_error", "icb_set_profile",
     "icb_alloc_pinned", "icb_free_pinned", "icb_jpg_fit", "icb_jpg_encode", "icb_jpg_sizes",
-    "icb_jpg_coefficients", "icb_resize_dims", "icb_resize_bilinear", "icb_png_fit",
+    "icb_jpg_coefficients", "icb_resize_dims", "icb_resize_bilinear", "icb_png_fit", "icb_png_target_dims",
     "icb_submit_jpg_fit", "icb_wait", "icb_image_upload", "icb_image_free",
     "icb_submit_jpg_fit_image", "icb_submit_resize_image", "icb_stats", "icb_profile_jpg_fit_image",
     "icb_mark", "icb_elapsed_ms",
@@ -93,6 +93,8 @@ def load_library(build_if_missing: bool = True):
     L.icb_resize_bilinear.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int]
     L.icb_png_fit.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_size_t,
                               C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.icb_png_target_dims.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
+                                      C.POINTER(C.c_double)]
     L.icb_submit_jpg_fit.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int64, C.c_int,
                                      C.c_float, C.c_double, vp, C.c_size_t, C.POINTER(C.c_int64)]
     L.icb_wait.argtypes = [vp, C.c_int64, C.POINTER(_Result)]
@@ -164,6 +166,27 @@ def _image_args(image: np.ndarray, fmt: Optional[int]) -> Tuple[np.ndarray, int,
     if fmt is None:
         fmt = FMT_RGB8 if c == 3 else FMT_RGBA8
     return image, w, h, image.strides[0], fmt
+
+
+def resize_dims(w: int, h: int, scale: float) -> Tuple[int, int]:
+    """tools/ImageTools.java:8-9 (host arithmetic in the library, no device needed)."""
+    L = load_library()
+    a, b = C.c_int(0), C.c_int(0)
+    L.icb_resize_dims(w, h, C.c_double(scale), C.byref(a), C.byref(b))
+    return a.value, b.value
+
+
+def png_target_dims(w: int, h: int, min_w: int, min_h: int):
+    """core/ImageCompressionPng.java:49-61 -> None when no resize is due (the seam returns false),
+    else (new_w, new_h, scale)."""
+    L = load_library()
+    a, b, s = C.c_int(0), C.c_int(0), C.c_double(0)
+    rc = L.icb_png_target_dims(w, h, min_w, min_h, C.byref(a), C.byref(b), C.byref(s))
+    if rc == ICB_NO_FIT:
+        return None
+    if rc:
+        raise IcbError(rc, "bad dimensions")
+    return a.value, b.value, s.value
 
 
 class Engine:

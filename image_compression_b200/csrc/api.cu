@@ -68,6 +68,7 @@ struct Slot {
     unsigned char *d_rgb2 = nullptr;  size_t rgb2_cap = 0;
     int16_t *d_coef = nullptr;        size_t coef_cap = 0;      // bytes
     unsigned char *d_pass = nullptr;  size_t pass_cap = 0;      // 2 x entropy pass arena (ping-pong)
+    uint32_t *d_ent = nullptr;        size_t ent_cap = 0;       // survivor entries + per-tile counts
     unsigned char *d_out = nullptr;   size_t out_cap = 0;       // final JFIF stream
     FitState *d_state = nullptr;
     FitState *h_state = nullptr;            // pinned
@@ -181,7 +182,6 @@ int setup_device(icb_handle *h, DeviceCtx &d)
     CK(cudaMemcpyToSymbol(c_hdr, hdr, HEADER_BYTES));
     CK(cudaFuncSetAttribute(k_transform<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_transform<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
-    CK(cudaFuncSetAttribute(k_entropy_symbols, cudaFuncAttributeMaxDynamicSharedMemorySize, ENT_SMEM_BYTES));
     return ICB_OK;
 }
 
@@ -267,45 +267,69 @@ int max_search_iters(float init_q)
     return std::min(8, n + 1);
 }
 
-int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, int npairs, bool emit,
+// persistent grid of the entropy pass: c CTAs per SM (c <= 5 by registers) such that the statically
+// dealt tiles fill the last round of every warp as evenly as possible
+int pass_grid(int ntiles, int sms)
+{
+    const int need = (ntiles + ENT_WARPS - 1) / ENT_WARPS;
+    if (need <= sms * 5) return need;
+    int best_grid = sms * 5;
+    double best_eff = 0.0;
+    for (int c = 5; c >= 2; c--) {
+        const long long warps = (long long)sms * c * ENT_WARPS;
+        const long long rounds = (ntiles + warps - 1) / warps;
+        const double eff = (double)ntiles / (double)(rounds * warps);
+        if (eff > best_eff + 0.02) { best_eff = eff; best_grid = sms * c; }
+    }
+    return best_grid;
+}
+
+int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, int npasses, bool emit,
                    long long dev_cap, cudaEvent_t *pass_ev = nullptr)
 {
     const Geom &g = s->geom;
-    const size_t per = round_up(ent_pass_bytes(g.ntiles), 256);
-    int rc = ensure(h, s->d_pass, s->pass_cap, 2 * per);
+    const int nctas = (g.ntiles + ENT_WARPS - 1) / ENT_WARPS;
+    const int ngroups = (g.ntiles + 31) / 32;
+    const size_t per = round_up(ent_pass_bytes(g.ntiles, ngroups), 256);
+    int rc = ensure(h, s->d_pass, s->pass_cap, 2 * per + (size_t)ngroups * 4 + 256);
+    if (rc) return rc;
+    rc = ensure(h, s->d_ent, s->ent_cap, ((size_t)g.ntiles * ENT_CAP + (size_t)g.ntiles) * 4 + 256);
     if (rc) return rc;
     EntParams ep;
     ep.coef = s->d_coef;
     ep.st = s->d_state;
+    ep.ent = s->d_ent;
+    ep.ent_cnt = s->d_ent + (size_t)g.ntiles * ENT_CAP;
+    ep.grp_cnt = reinterpret_cast<unsigned int *>(s->d_pass + 2 * per);
     ep.nblocks = g.nblocks;
     ep.ntiles = g.ntiles;
+    ep.ngroups = ngroups;
     for (int b = 0; b < 2; b++) {
         unsigned char *base = s->d_pass + (size_t)b * per;
-        const size_t n = (size_t)g.ntiles;
-        ep.buf[b].scratch = reinterpret_cast<uint32_t *>(base);
-        base += n * ENT_SCR_STRIDE * 4;
-        ep.buf[b].P = reinterpret_cast<unsigned long long *>(base);
-        base += n * 8;
-        ep.buf[b].Q = reinterpret_cast<unsigned long long *>(base);
-        base += n * 8;
-        ep.buf[b].L = reinterpret_cast<unsigned int *>(base);
-        base += n * 4;
-        ep.buf[b].bytes = reinterpret_cast<unsigned int *>(base);
+        const size_t n = (size_t)g.ntiles, c = (size_t)ngroups;
+        ep.buf[b].ff = reinterpret_cast<uint4 *>(base);                 base += n * 16;
+        ep.buf[b].ffg = reinterpret_cast<uint4 *>(base);                base += c * 32;
+        ep.buf[b].Pg = reinterpret_cast<unsigned long long *>(base);    base += c * 8;
+        ep.buf[b].scratch = reinterpret_cast<uint32_t *>(base);         base += n * ENT_SCR_STRIDE * 4;
+        ep.buf[b].L = reinterpret_cast<unsigned int *>(base);           base += n * 4;
+        ep.buf[b].ones = reinterpret_cast<unsigned int *>(base);        base += n * 4;
+        ep.buf[b].Lg = reinterpret_cast<unsigned int *>(base);          base += c * 4;
+        ep.buf[b].onesg = reinterpret_cast<unsigned int *>(base);       base += c * 4;
+        ep.buf[b].Fg = reinterpret_cast<unsigned int *>(base);
     }
-    k_begin<<<1, 128, 0, s->stream>>>(s->d_state, mode, q, target, h->table_mode, h->jfif_minor);
-    h->kernels++;
-    const int grid = (g.ntiles + ENT_WARPS - 1) / ENT_WARPS;
-    for (int i = 0; i < npairs; i++) {
+    k_begin<<<1, 32, 0, s->stream>>>(s->d_state, mode, q, target, h->table_mode, h->jfif_minor, ep.grp_cnt, ngroups);
+    k_entropy_prepare<<<nctas, ENT_THREADS, 0, s->stream>>>(ep);
+    h->kernels += 2;
+    const int pgrid = pass_grid(g.ntiles, h->devs[s->devi].sms);
+    for (int i = 0; i < npasses; i++) {
         if (pass_ev) cudaEventRecord(pass_ev[2 * i], s->stream);
-        k_entropy_symbols<<<grid, ENT_THREADS, ENT_SMEM_BYTES, s->stream>>>(ep);
-        k_entropy_count<<<grid, ENT_THREADS, 0, s->stream>>>(ep);
+        k_entropy_pass<<<pgrid, ENT_THREADS, 0, s->stream>>>(ep);
         if (pass_ev) cudaEventRecord(pass_ev[2 * i + 1], s->stream);
-        h->kernels += 2;
+        h->kernels += 1;
     }
     if (emit) {
-        k_finish<<<1, ENT_THREADS, 0, s->stream>>>(ep, s->d_out, dev_cap, g.w, g.h);
-        k_entropy_emit<<<grid, ENT_THREADS, 0, s->stream>>>(ep, s->d_out, dev_cap);
-        h->kernels += 2;
+        k_entropy_emit<<<nctas, ENT_THREADS, 0, s->stream>>>(ep, s->d_out, dev_cap, g.w, g.h);
+        h->kernels += 1;
     }
     CK(cudaGetLastError());
     return ICB_OK;
@@ -555,7 +579,7 @@ void icb_shutdown(icb_handle *h)
         if (s.devi < (int)h->devs.size()) cudaSetDevice(h->devs[s.devi].dev);
         if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); }
         cudaFree(s.d_rgb); cudaFree(s.d_rgb2); cudaFree(s.d_coef); cudaFree(s.d_pass);
-        cudaFree(s.d_out); cudaFree(s.d_state);
+        cudaFree(s.d_out); cudaFree(s.d_state); cudaFree(s.d_ent);
         if (s.h_state) cudaFreeHost(s.h_state);
     }
     delete h;
@@ -833,15 +857,24 @@ int icb_resize_bilinear(icb_handle *h, const uint8_t *src, int w, int hgt, int p
     return rc;
 }
 
+int icb_png_target_dims(int w, int hgt, int min_w, int min_h, int *dw, int *dh, double *scale)
+{
+    if (w < 1 || hgt < 1) return ICB_ERR_INVALID;
+    if (w <= min_w && hgt <= min_h) return ICB_NO_FIT;              // :49-53 returns false
+    const double wr = (double)min_w / w, hr = (double)min_h / hgt;  // :57-58
+    const double sc = wr < hr ? wr : hr;                             // :61 Math.min
+    if (scale) *scale = sc;
+    icb_resize_dims(w, hgt, sc, dw, dh);                             // ImageTools.java:8-9
+    return ICB_OK;
+}
+
 int icb_png_fit(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt, int min_w, int min_h,
                 uint8_t *dst, size_t dst_cap, int *dw, int *dh)
 {
     if (!h) return ICB_ERR_INVALID;
     if (!src || !dw || !dh || w < 1 || hgt < 1) return fail(h, ICB_ERR_INVALID, "null argument");   // :39-41 NPE
-    if (w <= min_w && hgt <= min_h) return ICB_NO_FIT;              // :49-53 returns false
-    const double wr = (double)min_w / w, hr = (double)min_h / hgt;  // :57-58
-    const double scale = wr < hr ? wr : hr;                          // :61
-    icb_resize_dims(w, hgt, scale, dw, dh);                          // ImageTools.java:8-9
+    const int rc0 = icb_png_target_dims(w, hgt, min_w, min_h, dw, dh, nullptr);
+    if (rc0) return rc0;
     if (!dst) return ICB_OK;                                         // dimension query
     const int bpp = bpp_of(fmt);
     if (dst_cap < (size_t)*dw * *dh * bpp) return fail(h, ICB_ERR_CAPACITY, "dst too small");

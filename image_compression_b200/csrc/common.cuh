@@ -6,6 +6,7 @@
 #pragma once
 
 #include <cuda_runtime.h>
+#include <stddef.h>
 #include <stdint.h>
 
 namespace icb {
@@ -50,8 +51,9 @@ constexpr int ENT_WARPS = 8;
 constexpr int ENT_THREADS = ENT_WARPS * 32;
 // worst case per block: DC 9+11 bits, 63 x (16+10) bits = 1658 bits -> 208 B
 constexpr int ENT_SCR_STRIDE = (ENT_TILE_BLOCKS * 208) / 4 + 4;    // scratch words per tile
-constexpr int ENT_WIN = 256;                        // shared-memory bit window per warp (words)
-constexpr int ENT_RING = 512;                       // symbol-entry ring per warp (power of two)
+constexpr int ENT_WIN = 128;                        // shared-memory bit window per warp (words)
+constexpr int ENT_WSTRIDE = ENT_WIN + 4;
+constexpr int ENT_CAP = ENT_TILE_BLOCKS * 64;       // survivor entries per tile, worst case
 
 constexpr int HEADER_BYTES = 623;                   // a2.8, 3-component JFIF
 
@@ -80,14 +82,17 @@ struct FitState {
     unsigned int recip[2][64];      // ceil-ish 2^32 / (8 q): floor(t/(8q)) == umulhi(t, recip)
     unsigned short half[2][64];     // 4 q
     unsigned char qtab[2][64];
+    unsigned short thr[2][64];      // survivor thresholds (4 q at the highest quality of the job), zigzag order
     unsigned char best_qtab[2][64]; // tables of the best pass so far (header of the final stream)
     // pass scratch
-    unsigned int done_a, done_c;    // finished CTAs of k_entropy_symbols / k_entropy_count
-    int emit_valid;
-    int pad1;
+    unsigned int done_a;            // finished CTAs of k_entropy_pass
+    int pad1, pad2, pad3;
+    unsigned long long dbg_t[8][4]; // per pass: globaltimer at kernel start / tail start / step start / tail end
     unsigned long long ff_total;    // stuffed 0x00 bytes (= number of 0xFF data bytes)
     unsigned long long total_bits;  // entropy-coded bits before padding
 };
+
+static_assert(offsetof(FitState, qtab) % 4 == 0 && offsetof(FitState, best_qtab) % 4 == 0, "word copies of the tables");
 
 // ---- Annex K tables (T.81), natural order; IJG jcparam.c / JDK JPEGQTable ----
 __constant__ unsigned char c_base_lum[64] = {

@@ -6,7 +6,7 @@
 // (findBestQualityByBinarySearch) in float32 exactly as Java evaluates it:
 // lo = 0, hi = initialQuality, mid = (lo + hi) / 2.0f, `mid < 0.01f` break before
 // encoding, fit -> best = lo = mid else hi = mid, `(hi - lo) < 0.01f` break after.
-// It runs inside the last CTA of k_entropy_count (the exact stuffed size of the
+// It runs inside the last CTA of k_entropy_pass (the exact stuffed size of the
 // pass is known there) and once in k_begin, and builds the quantisation tables of
 // the coming pass (a2.1: JDK JPEG.convertToLinearQuality +
 // JPEGQTable.getScaledInstance in float32, or the IJG integer formula under the
@@ -19,10 +19,6 @@
 #include "k_entropy.cuh"
 
 namespace icb {
-
-// header template (tables, dims and JFIF minor patched per image); filled by the host
-__constant__ unsigned char c_hdr[HEADER_BYTES];
-constexpr int HDR_OFF_MINOR = 12, HDR_OFF_DQT0 = 25, HDR_OFF_DQT1 = 94, HDR_OFF_H = 163, HDR_OFF_W = 165;
 
 // a2.1 -- one table entry for quality q
 __device__ __forceinline__ int scaled_qval(int base, float q, int table_mode)
@@ -46,95 +42,107 @@ __device__ __forceinline__ int scaled_qval(int base, float q, int table_mode)
     return sv;
 }
 
-// Called by every thread of ONE CTA (>= 128 threads).  Consumes the pass that just
-// ran (if any), decides, and prepares the next one.
+// Called by all 32 lanes of ONE warp.  Consumes the pass that just ran (if any),
+// decides, and prepares the next one.  Lane 0 reads every control field first and
+// writes them back at the end, so the global accesses pipeline instead of chaining.
 __device__ void device_step(FitState *st, int final_call)
 {
-    __shared__ int s_go;
-    if (threadIdx.x == 0) {
-        if (st->cur_valid) {                                    // consume the pass that just ran
-            const unsigned long long tbits = *(volatile unsigned long long *)&st->total_bits;
-            const unsigned long long ffs = *(volatile unsigned long long *)&st->ff_total;
+    const int lane = threadIdx.x & 31;
+    int go = 0, better = 0;
+    float next_q = 0.0f;
+    if (lane == 0) {
+        float lo = st->lo, hi = st->hi, best = st->best, cur_q = st->cur_q;
+        int iter = st->iter, done = st->done, n_trace = st->n_trace, passes = st->passes;
+        int cur_buf = st->cur_buf, best_buf = st->best_buf;
+        const int cur_valid = st->cur_valid, mode = st->mode;
+        const long long target = st->target;
+        long long best_size = st->best_size, cur_size = st->cur_size;
+        const unsigned long long tbits = *(volatile unsigned long long *)&st->total_bits;
+        const unsigned long long ffs = *(volatile unsigned long long *)&st->ff_total;
+        if (cur_valid) {                                        // consume the pass that just ran
             const long long size = (long long)HEADER_BYTES + (long long)((tbits + 7ull) >> 3) + (long long)ffs + 2;
-            bool better = false;
-            st->cur_size = size;
-            st->passes++;
-            st->cur_valid = 0;
-            if (st->mode == MODE_SEARCH) {
-                if (st->n_trace < 8) {
-                    st->trace_q[st->n_trace] = st->cur_q;
-                    st->trace_size[st->n_trace] = size;
-                    st->n_trace++;
+            cur_size = size;
+            passes++;
+            if (mode == MODE_SEARCH) {
+                if (n_trace < 8) {
+                    st->trace_q[n_trace] = cur_q;
+                    st->trace_size[n_trace] = size;
+                    n_trace++;
                 }
-                if (size <= st->target) {                       // :180-185
-                    st->best = st->cur_q;
-                    st->lo = st->cur_q;
-                    better = true;
+                if (size <= target) {                           // :180-185
+                    best = cur_q;
+                    lo = cur_q;
+                    better = 1;
                 } else {
-                    st->hi = st->cur_q;
+                    hi = cur_q;
                 }
-                if (__fsub_rn(st->hi, st->lo) < 0.01f) st->done = 1;   // :187-189
+                if (__fsub_rn(hi, lo) < 0.01f) done = 1;        // :187-189
             } else {
-                st->best = st->cur_q;
-                better = true;
-                st->done = 1;
+                best = cur_q;
+                better = 1;
+                done = 1;
             }
             if (better) {
-                st->best_buf = st->cur_buf;
-                st->best_size = size;
-                for (int i = 0; i < 64; i++) {
-                    st->best_qtab[0][i] = st->qtab[0][i];
-                    st->best_qtab[1][i] = st->qtab[1][i];
-                }
+                best_buf = cur_buf;
+                best_size = size;
             }
         }
-        int go = 0;
-        if (!st->done && !final_call) {
-            if (st->mode == MODE_SEARCH) {
-                if (st->iter >= 8) {                            // :167
-                    st->done = 1;
+        if (!done && !final_call) {
+            if (mode == MODE_SEARCH) {
+                if (iter >= 8) {                                // :167
+                    done = 1;
                 } else {
-                    const float mid = __fdiv_rn(__fadd_rn(st->lo, st->hi), 2.0f);   // :168
+                    const float mid = __fdiv_rn(__fadd_rn(lo, hi), 2.0f);   // :168
                     if (mid < 0.01f) {                          // :170-172
-                        st->done = 1;
+                        done = 1;
                     } else {
-                        st->cur_q = mid;
+                        cur_q = mid;
                         go = 1;
                     }
                 }
             } else {
-                go = st->iter == 0;
+                go = iter == 0;
             }
         }
         if (go) {
-            st->iter++;
-            st->cur_valid = 1;
-            st->cur_buf = (st->best_size > 0) ? (1 - st->best_buf) : 0;
+            iter++;
+            cur_buf = (best_size > 0) ? (1 - best_buf) : 0;
         }
+        next_q = cur_q;
+        st->lo = lo; st->hi = hi; st->best = best; st->cur_q = cur_q;
+        st->iter = iter; st->done = done; st->n_trace = n_trace; st->passes = passes;
+        st->cur_buf = cur_buf; st->best_buf = best_buf; st->cur_valid = go;
+        st->best_size = best_size; st->cur_size = cur_size;
         st->done_a = 0;
-        st->done_c = 0;
         st->ff_total = 0;
         st->total_bits = 0;
-        s_go = go;
     }
-    __syncthreads();
-    if (!s_go) return;
-    const int t = threadIdx.x;
-    if (t < 128) {                                              // 2 tables x 64 entries, zigzag order
-        const float q = st->cur_q;
-        const int tb = t >> 6, k = t & 63;
-        const int nat = c_zigzag[k];
-        const int qv = scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], q, st->table_mode);
-        const unsigned d = (unsigned)qv << 3;                   // jcdctmgr.c: divisor = quantval << 3
-        st->qtab[tb][k] = (unsigned char)qv;
-        st->recip[tb][k] = (unsigned)((1ull << 32) / d) + 1u;   // umulhi(t, recip) == t / d for t < 2^17
-        st->half[tb][k] = (unsigned short)(d >> 1);
+    better = __shfl_sync(0xffffffffu, better, 0);
+    go = __shfl_sync(0xffffffffu, go, 0);
+    next_q = __shfl_sync(0xffffffffu, next_q, 0);
+    if (better)                                                 // tables of the best pass so far: 128 B, one word per lane
+        reinterpret_cast<unsigned int *>(&st->best_qtab[0][0])[lane] =
+            reinterpret_cast<const unsigned int *>(&st->qtab[0][0])[lane];
+    __syncwarp();
+    if (go) {
+        const int table_mode = st->table_mode;
+        for (int t = lane; t < 128; t += 32) {                  // 2 tables x 64 entries, zigzag order
+            const int tb = t >> 6, k = t & 63;
+            const int nat = c_zigzag[k];
+            const int qv = scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], next_q, table_mode);
+            const unsigned d = (unsigned)qv << 3;               // jcdctmgr.c: divisor = quantval << 3
+            st->qtab[tb][k] = (unsigned char)qv;
+            st->recip[tb][k] = (unsigned)((1ull << 32) / d) + 1u;   // umulhi(t, recip) == t / d for t < 2^17
+            st->half[tb][k] = (unsigned short)(d >> 1);
+        }
     }
+    __threadfence();
 }
 
-__global__ void __launch_bounds__(128) k_begin(FitState *st, int mode, float q, long long target, int table_mode,
-                                               int jfif_minor)
+__global__ void __launch_bounds__(32) k_begin(FitState *st, int mode, float q, long long target, int table_mode,
+                                              int jfif_minor, unsigned int *grp_cnt, int ngroups)
 {
+    for (int i = threadIdx.x; i < ngroups; i += 32) grp_cnt[i] = 0;
     if (threadIdx.x == 0) {
         st->lo = 0.0f;
         st->hi = q;
@@ -154,35 +162,20 @@ __global__ void __launch_bounds__(128) k_begin(FitState *st, int mode, float q, 
         st->target = target;
         st->cur_size = 0;
         st->best_size = 0;
-        st->emit_valid = 0;
     }
-    __syncthreads();
+    {   // survivor thresholds for k_entropy_prepare: a coefficient is non-zero at quality q iff
+        // |x| >= 4 * table(q), and table(q) never grows with q, so the tables of the highest
+        // quality this job can reach (q itself: every midpoint is below hi <= q) bound them all
+        for (int t = threadIdx.x; t < 128; t += 32) {
+            const int tb = t >> 6, k = t & 63;
+            const int nat = c_zigzag[k];
+            const int qv = scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], q, table_mode);
+            st->thr[tb][k] = (unsigned short)(qv << 2);
+        }
+    }
+    __threadfence();
+    __syncwarp();
     device_step(st, 0);
-}
-
-__global__ void __launch_bounds__(ENT_THREADS) k_finish(const EntParams p, unsigned char *out, long long out_cap,
-                                                        int w, int h)
-{
-    __shared__ unsigned long long s_part[ENT_THREADS + 1];
-    FitState *st = p.st;
-    if (st->best_size <= 0 || out == nullptr) {
-        if (threadIdx.x == 0) st->emit_valid = 0;
-        return;
-    }
-    const PassBufs pb = pick_buf(p, st->best_buf);
-    cta_exclusive_scan(pb.bytes, pb.Q, p.ntiles, s_part);
-    for (int i = threadIdx.x; i < HEADER_BYTES; i += blockDim.x) {
-        unsigned char b = c_hdr[i];
-        if (i == HDR_OFF_MINOR) b = (unsigned char)st->jfif_minor;
-        else if (i >= HDR_OFF_DQT0 && i < HDR_OFF_DQT0 + 64) b = st->best_qtab[0][i - HDR_OFF_DQT0];
-        else if (i >= HDR_OFF_DQT1 && i < HDR_OFF_DQT1 + 64) b = st->best_qtab[1][i - HDR_OFF_DQT1];
-        else if (i == HDR_OFF_H) b = (unsigned char)(h >> 8);
-        else if (i == HDR_OFF_H + 1) b = (unsigned char)h;
-        else if (i == HDR_OFF_W) b = (unsigned char)(w >> 8);
-        else if (i == HDR_OFF_W + 1) b = (unsigned char)w;
-        if (i < out_cap) out[i] = b;
-    }
-    if (threadIdx.x == 0) st->emit_valid = 1;
 }
 
 }  // namespace icb

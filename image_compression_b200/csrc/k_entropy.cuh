@@ -1,31 +1,37 @@
-// k_entropy.cuh -- K2/K3: the entropy pass = quantise + zigzag run-lengths +
-// baseline Huffman + exact byte stuffing at ONE quality, reading the coefficients
-// K1 left in HBM/L2, and the final emission of the chosen stream.
+// k_entropy.cuh -- K2/K3: survivor compaction, the entropy pass (quantise +
+// run lengths + baseline Huffman + exact byte-stuffing count at ONE quality) and
+// the emission of the chosen stream.
 //
 // Replaces the back half of each javax.imageio encode of the reference's search
 // (core/ImageCompressionJpg.java:167-190) and of saveCompressedImage (:255-260):
 // IJG jcdctmgr.c quantisation (a2.5), jchuff.c encode_one_block / emit_bits /
 // flush_bits (a2.7).  The reference compares the STUFFED stream size with the
-// target (:176-180), so the pass computes exact sizes: a bit-length sum is not
-// enough, every 0xFF data byte adds a stuffed 0x00 and that depends on the
+// target (:176-180), so every pass computes the exact size: a bit-length sum is
+// not enough, every 0xFF data byte adds a stuffed 0x00 and that depends on the
 // absolute bit alignment of each code.
 //
 // Three kernels, no inter-CTA waiting anywhere:
-//   k_entropy_symbols  one warp = 32 consecutive blocks (MCU order).  Phase A, 8
-//       lanes per block: quantise, DC-predict, and append every coefficient that
-//       codes a symbol to a compact ring.  Phase B, all 32 lanes busy: run length
-//       = distance to the previous ring entry, Huffman lookup, ZRL prefix, EOB
-//       suffix, warp scan of code lengths, OR into a shared-memory bit window that
-//       is flushed to a per-tile scratch stream (tile-local alignment 0).  The last
-//       CTA to finish turns the per-tile bit counts into exclusive prefixes.
-//   k_entropy_count    one warp per tile: re-reads the tile's bits through a funnel
-//       shift at its absolute alignment (borrowing the predecessor's last bits for
-//       the shared byte) and counts 0xFF bytes.  The last CTA to finish runs the
-//       reference's bisection step on the exact size and sets up the next pass.
-//   k_entropy_emit     once per image, for the chosen quality only: same shifted
-//       read, writes the stuffed bytes at their scanned offsets, then EOI.
+//   k_entropy_prepare  once per image (per scale): walks the dense coefficients K1
+//       left in HBM/L2 and keeps only the "survivors" -- coefficients that are
+//       non-zero at the HIGHEST quality any pass of this job can use
+//       (|x| >= 4*q_table, tables are monotone in quality) -- as compact 32-bit
+//       entries in scan order, one list per tile of 32 blocks.  Every block
+//       contributes a DC entry that also carries its predictor's raw DC.
+//   k_entropy_pass     once per search step: one warp per tile, one survivor per
+//       lane: quantise at the current tables, drop what became zero, run length =
+//       distance to the previous live entry, Huffman lookup, ZRL prefixes, the
+//       end-of-block code as a prefix of the next block's DC symbol, warp scan of
+//       code lengths, OR into a shared-memory bit window flushed to a per-tile
+//       scratch stream (tile-local alignment 0).  While flushing, 0xFF bytes are
+//       counted for all 8 possible start alignments; the last warp to finish a
+//       group of 32 tiles folds the group, and the last group to finish scans the
+//       group records into the exact stuffed size and runs the reference's
+//       bisection step (k_control.cuh).  Warps are persistent and never wait.
+//   k_entropy_emit     once per image, for the chosen pass only: re-reads the
+//       tile streams through a funnel shift at their absolute alignment, writes
+//       the stuffed bytes at their final offsets, the 623-byte header and EOI.
 // Integer/bit work throughout: the integer pipes, not HBM, bound these kernels
-// (coefficients stay L2-resident between passes).
+// (coefficients and survivor lists stay L2-resident between passes).
 #pragma once
 
 #include "common.cuh"
@@ -35,16 +41,23 @@ namespace icb {
 struct PassBufs {
     uint32_t *scratch;              // [ntiles][ENT_SCR_STRIDE] tile-local bit streams, big-endian words
     unsigned int *L;                // [ntiles] bits per tile
-    unsigned long long *P;          // [ntiles] exclusive bit prefix
-    unsigned int *bytes;            // [ntiles] stuffed bytes the tile completes
-    unsigned long long *Q;          // [ntiles] exclusive byte prefix (k_finish, chosen pass only)
+    uint4 *ff;                      // [ntiles] 8 x u16: 0xFF bytes inside the tile per absolute start offset mod 8
+    unsigned int *ones;             // [ntiles] leading 1-bits | trailing 1-bits << 8 (each capped at 8)
+    unsigned int *Lg;               // [ngroups] bits per group of 32 tiles
+    uint4 *ffg;                     // [ngroups][2] the same 8 counters (u32) folded over the group's tiles
+    unsigned int *onesg;            // [ngroups]
+    unsigned long long *Pg;         // [ngroups] exclusive bit prefix            (last warp of the pass)
+    unsigned int *Fg;               // [ngroups] exclusive prefix of 0xFF bytes  (last warp of the pass)
 };
 
 struct EntParams {
     const int16_t *coef;
     FitState *st;
+    uint32_t *ent;                  // [ntiles][ENT_CAP] survivor entries
+    unsigned int *ent_cnt;          // [ntiles]
+    unsigned int *grp_cnt;          // [ngroups] tiles of the group that finished (self-resetting)
     PassBufs buf[2];                // ping-pong: the best pass so far is never overwritten
-    int nblocks, ntiles;
+    int nblocks, ntiles, ngroups;
 };
 
 // select without dynamic indexing of the kernel parameter block (keeps it out of local memory)
@@ -53,58 +66,140 @@ __device__ __forceinline__ PassBufs pick_buf(const EntParams &p, int i)
     PassBufs b;
     b.scratch = i ? p.buf[1].scratch : p.buf[0].scratch;
     b.L = i ? p.buf[1].L : p.buf[0].L;
-    b.P = i ? p.buf[1].P : p.buf[0].P;
-    b.bytes = i ? p.buf[1].bytes : p.buf[0].bytes;
-    b.Q = i ? p.buf[1].Q : p.buf[0].Q;
+    b.ff = i ? p.buf[1].ff : p.buf[0].ff;
+    b.ones = i ? p.buf[1].ones : p.buf[0].ones;
+    b.Lg = i ? p.buf[1].Lg : p.buf[0].Lg;
+    b.ffg = i ? p.buf[1].ffg : p.buf[0].ffg;
+    b.onesg = i ? p.buf[1].onesg : p.buf[0].onesg;
+    b.Pg = i ? p.buf[1].Pg : p.buf[0].Pg;
+    b.Fg = i ? p.buf[1].Fg : p.buf[0].Fg;
     return b;
 }
 
 // a2.1 / :158-200 -- defined in k_control.cuh
 __device__ void device_step(FitState *st, int final_call);
 
-// exclusive scan of src[0..n) by one CTA; returns the total in every thread
-template <typename T>
-__device__ __forceinline__ unsigned long long cta_exclusive_scan(const T *src, unsigned long long *dst, int n,
-                                                                 unsigned long long *s_part)
+// ---- survivor entries ------------------------------------------------------------
+// AC: val(16) | zigzag pos(6) << 16 | table << 30
+// DC: dc(14)  | predictor dc(14) << 14 | table << 30 | 1 << 31      (raw DC = sum - 8192: 14 bits signed)
+constexpr uint32_t ENTRY_DC = 0x80000000u;
+
+__device__ __forceinline__ uint32_t ff_select(const uint4 &f, uint32_t r)        // counter r of 8 x u16
 {
-    const int tid = threadIdx.x, nt = blockDim.x;
-    const int chunk = (n + nt - 1) / nt;
-    const int lo = min(n, tid * chunk), hi = min(n, lo + chunk);
-    unsigned long long sum = 0;
-    for (int i = lo; i < hi; i++) sum += (unsigned long long)__ldcg(src + i);
-    s_part[tid] = sum;
-    __syncthreads();
-    if (tid == 0) {
-        unsigned long long run = 0;
-        for (int i = 0; i < nt; i++) {
-            const unsigned long long v = s_part[i];
-            s_part[i] = run;
-            run += v;
-        }
-        s_part[nt] = run;
-    }
-    __syncthreads();
-    unsigned long long run = s_part[tid];
-    for (int i = lo; i < hi; i++) {
-        dst[i] = run;
-        run += (unsigned long long)__ldcg(src + i);
-    }
-    return s_part[nt];
+    const uint32_t lo = (r & 4u) ? f.z : f.x, hi = (r & 4u) ? f.w : f.y;
+    const uint32_t w = (r & 2u) ? hi : lo;
+    return (r & 1u) ? (w >> 16) : (w & 0xffffu);
 }
 
-__global__ void __launch_bounds__(ENT_THREADS) k_entropy_symbols(const EntParams p)
+// number of 0xFF bytes in a word (bytes whose 8 bits are all ones)
+__device__ __forceinline__ uint32_t ff_bytes(uint32_t v)
+{
+    return __popc(((v & 0x7f7f7f7fu) + 0x01010101u) & v & 0x80808080u);
+}
+
+// byte shared by two neighbouring tiles: r = start offset mod 8 of the second (r != 0)
+__device__ __forceinline__ uint32_t span_ff(uint32_t ones_prev, uint32_t ones_cur, uint32_t r)
+{
+    return (r != 0u && (ones_prev >> 8) >= r && (ones_cur & 0xffu) >= 8u - r) ? 1u : 0u;
+}
+
+__global__ void __launch_bounds__(ENT_THREADS) k_entropy_prepare(const EntParams p)
+{
+    __shared__ __align__(16) unsigned short s_thr[2][64];
+    const FitState *st = p.st;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid < 128) s_thr[tid >> 6][tid & 63] = st->thr[tid >> 6][tid & 63];
+    __syncthreads();
+    const int tile = blockIdx.x * ENT_WARPS + warp;
+    if (tile >= p.ntiles) return;
+    const int g = lane >> 3, j = lane & 7;
+    uint32_t *out = p.ent + (size_t)tile * ENT_CAP;
+    uint32_t cnt = 0;
+    for (int it = 0; it < ENT_TILE_BLOCKS / 4; it++) {
+        const int b = tile * ENT_TILE_BLOCKS + it * 4 + g;
+        const bool valid = b < p.nblocks;
+        const int cidx = b % 6;
+        const uint32_t tb = cidx >= 4 ? 1u : 0u;
+        // DC predictor = previous block of the same component in scan order
+        int prev = b - 1;
+        bool has_prev = true;
+        if (cidx == 0) { prev = b - 3; has_prev = b >= 6; }
+        else if (cidx >= 4) { prev = b - 6; has_prev = b >= 6; }
+        uint4 raw = make_uint4(0, 0, 0, 0);
+        int xp = 0;
+        if (valid) {
+            raw = __ldg(reinterpret_cast<const uint4 *>(p.coef) + (size_t)b * 8 + j);
+            if (j == 0 && has_prev) xp = (int)__ldg(p.coef + (size_t)prev * 64);
+        }
+        const uint4 tt = *reinterpret_cast<const uint4 *>(&s_thr[tb][8 * j]);
+        const uint32_t rw[4] = {raw.x, raw.y, raw.z, raw.w};
+        const uint32_t tw[4] = {tt.x, tt.y, tt.z, tt.w};
+        int x[8];
+        uint32_t m8 = 0;
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            x[i] = (i & 1) ? ((int)rw[i >> 1] >> 16) : ((int)(rw[i >> 1] << 16) >> 16);
+            const uint32_t thr = (i & 1) ? (tw[i >> 1] >> 16) : (tw[i >> 1] & 0xffffu);
+            m8 |= ((uint32_t)abs(x[i]) >= thr ? 1u : 0u) << i;
+        }
+        if (j == 0) m8 |= 1u;                               // DC always codes a symbol
+        if (!valid) m8 = 0;
+        const uint32_t npop = __popc(m8);
+        uint32_t incl = npop;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        uint32_t rank = cnt + incl - npop;
+        cnt += __shfl_sync(0xffffffffu, incl, 31);
+        const uint32_t tag = (tb << 30) | ((uint32_t)(8 * j) << 16);
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            if ((m8 >> i) & 1u) {
+                uint32_t e;
+                if (i == 0 && j == 0)
+                    e = ENTRY_DC | (tb << 30) | (((uint32_t)xp & 0x3fffu) << 14) | ((uint32_t)x[0] & 0x3fffu);
+                else
+                    e = ((uint32_t)x[i] & 0xffffu) | (tag + ((uint32_t)i << 16));
+                out[rank++] = e;
+            }
+        }
+    }
+    if (lane == 0) p.ent_cnt[tile] = cnt;
+}
+
+__device__ __forceinline__ unsigned long long gtime()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// run-of-8 detector: bit (31 - p) of the result is set iff bits p .. p+7 of the 64-bit
+// big-endian pair (a, b) are all ones, for starts p = 0..31 inside a
+__device__ __forceinline__ uint32_t ff_starts(uint32_t a, uint32_t b)
+{
+    const uint32_t a1 = a & __funnelshift_l(b, a, 1), b1 = b & (b << 1);
+    const uint32_t a2 = a1 & __funnelshift_l(b1, a1, 2), b2 = b1 & (b1 << 2);
+    return a2 & __funnelshift_l(b2, a2, 4);
+}
+
+__global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
 {
     __shared__ uint32_t s_ac[2][256];
     __shared__ uint32_t s_dc[2][16];
-    __shared__ __align__(16) uint32_t s_recip[2][64];
-    __shared__ __align__(16) unsigned short s_half[2][64];
-    __shared__ unsigned long long s_part[ENT_THREADS + 1];
-    __shared__ int s_last;
-    extern __shared__ __align__(16) uint32_t s_dyn[];
+    __shared__ uint32_t s_recip[2][64];
+    __shared__ uint32_t s_half[2][64];
+    __shared__ uint32_t s_win[ENT_WARPS * ENT_WSTRIDE];
 
     FitState *st = p.st;
     if (!st->cur_valid) return;
     const PassBufs pb = pick_buf(p, st->cur_buf);
+#ifdef ICB_TIMING
+    const int dbg_pass = (st->iter - 1) & 7;
+    if (blockIdx.x == 0 && threadIdx.x == 0) st->dbg_t[dbg_pass][0] = gtime();
+#endif
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     for (int i = tid; i < 512; i += ENT_THREADS) s_ac[i >> 8][i & 255] = c_ac_enc[i >> 8][i & 255];
@@ -113,71 +208,127 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_symbols(const EntParams
         s_recip[tid >> 6][tid & 63] = st->recip[tid >> 6][tid & 63];
         s_half[tid >> 6][tid & 63] = st->half[tid >> 6][tid & 63];
     }
-    uint32_t *stage = s_dyn + warp * (ENT_WIN + ENT_RING);
-    uint32_t *ring = stage + ENT_WIN;
-    for (int i = lane * 4; i < ENT_WIN; i += 128) *reinterpret_cast<uint4 *>(stage + i) = make_uint4(0, 0, 0, 0);
+    uint32_t *stage = s_win + warp * ENT_WSTRIDE;
+    for (int i = lane; i < ENT_WSTRIDE; i += 32) stage[i] = 0;
     __syncthreads();
 
-    const int tile = blockIdx.x * ENT_WARPS + warp;
-    if (tile < p.ntiles) {
-        const int g = lane >> 3, j = lane & 7;
+    const uint32_t zrl0 = s_ac[0][0xF0], zrl1 = s_ac[1][0xF0];
+    const uint32_t eob0 = s_ac[0][0], eob1 = s_ac[1][0];
+    const uint32_t lt_mask = (1u << lane) - 1u;
+
+    // persistent warps: tiles are dealt out statically (no shared cursor a late CTA could overrun)
+    for (int tile = blockIdx.x * ENT_WARPS + warp; tile < p.ntiles; tile += gridDim.x * ENT_WARPS) {
         uint32_t *scr = pb.scratch + (size_t)tile * ENT_SCR_STRIDE;
+        const uint32_t *ent = p.ent + (size_t)tile * ENT_CAP;
+        const uint32_t n = __ldg(p.ent_cnt + tile);
         uint32_t running = 0;       // bits produced so far (tile-local)
         uint32_t flushed = 0;       // whole words already copied to scratch
-        uint32_t cnt = 0, head = 0; // ring entries appended / consumed
-        const uint32_t zrl0 = s_ac[0][0xF0], zrl1 = s_ac[1][0xF0];
-        const uint32_t eob0 = s_ac[0][0], eob1 = s_ac[1][0];
+        uint32_t acc0 = 0, acc1 = 0;   // 0xFF counters, 4 x 8 bits each: local start bit s = 0..3 | 4..7
+        uint32_t carry = 63u;       // zigzag pos | table << 6 of the last live entry (63: no EOB owed)
+        uint32_t first_word = 0;    // word 0 of the tile stream (for the leading-ones count)
 
-        // copy the complete words of the window to scratch and slide the window
-        auto flush = [&](bool final_flush) {
+        // 0xFF bytes that START in window words [0, nw) -- word w+1 must be final already --
+        // for the 8 local start bits s; limit = tile bits that exist (a byte must end <= limit)
+        auto count_ff = [&](uint32_t nw, uint32_t limit) {
+            for (uint32_t w = lane; w < nw; w += 32) {
+                uint32_t m = ff_starts(stage[w], stage[w + 1]);
+                const uint32_t bit0 = (flushed + w) << 5;
+                const uint32_t rem = limit > bit0 ? limit - bit0 : 0u;      // bits from this word on
+                if (rem < 40u) m &= rem < 8u ? 0u : 0xffffffffu << (39u - rem);
+                if (m) {
+#pragma unroll
+                    for (uint32_t s = 0; s < 4; s++) {
+                        acc0 += __popc(m & (0x80808080u >> s)) << (8 * s);
+                        acc1 += __popc(m & (0x08080808u >> s)) << (8 * s);
+                    }
+                }
+            }
+        };
+
+        // copy finished words of the window to scratch and slide the window; one finished word
+        // stays behind so that bytes straddling it can still be counted
+        auto flush_some = [&]() {
             __syncwarp();
-            const uint32_t have = (running >> 5) - flushed + (final_flush ? 2u : 0u);   // final: partial word + a zero
-            const uint32_t carry = final_flush ? 0u : stage[have];                      // partial word stays
-            __syncwarp();
-            for (uint32_t w = lane; w < have; w += 32) scr[flushed + w] = stage[w];
-            for (uint32_t w = lane; w <= have + 2; w += 32) stage[w] = 0;
-            __syncwarp();
-            if (lane == 0 && !final_flush) stage[0] = carry;
-            flushed += final_flush ? 0u : have;
+            const uint32_t have = (running >> 5) - flushed;         // finished words in the window
+            if (have >= 2) {
+                if (flushed == 0) first_word = stage[0];
+                const uint32_t nf = have - 1;
+                count_ff(nf, 0xffffffffu);
+                const uint32_t c0 = stage[nf], c1 = stage[nf + 1], c2 = stage[nf + 2];
+                for (uint32_t w = lane; w < nf; w += 32) scr[flushed + w] = stage[w];
+                __syncwarp();
+                for (uint32_t w = lane; w < nf + 3; w += 32) stage[w] = 0;
+                __syncwarp();
+                if (lane == 0) { stage[0] = c0; stage[1] = c1; stage[2] = c2; }
+                flushed += nf;
+            }
             __syncwarp();
         };
 
-        auto process_round = [&](uint32_t n, bool at_end) {
-            const uint32_t idx = head + lane;
-            const bool active = (uint32_t)lane < n;
-            const uint32_t e = ring[idx & (ENT_RING - 1)];
-            const uint32_t pe = ring[(idx - 1) & (ENT_RING - 1)];
-            const uint32_t ne = ring[(idx + 1) & (ENT_RING - 1)];
-            const int val = (int)(short)(e & 0xffffu);
-            const int pos = (int)((e >> 16) & 63u);
-            const int tb = (int)((e >> 22) & 1u);
-            const int nb = 32 - __clz(abs(val));
-            const uint32_t vbits = (uint32_t)(val + (val >> 31)) & ((1u << nb) - 1u);
-            uint32_t ent, nz = 0;
-            if (pos == 0) {
-                ent = s_dc[tb][nb & 15];
-            } else {
-                const int r = (pos - (int)((pe >> 16) & 63u) - 1) & 63;
-                nz = (uint32_t)r >> 4;
-                ent = s_ac[tb][((r & 15) << 4) | (nb & 15)];
+        auto put = [&](unsigned long long sym, uint32_t len, uint32_t off) {
+            const unsigned long long V = sym << (64 - len);
+            const uint32_t hiw = (uint32_t)(V >> 32), low = (uint32_t)V;
+            const uint32_t w = (off >> 5) - flushed, sh = off & 31;
+            const uint32_t w0 = hiw >> sh;
+            const uint32_t w1 = __funnelshift_r(low, hiw, sh);
+            const uint32_t w2 = __funnelshift_r(0u, low, sh);
+            if (w0) atomicOr(&stage[w], w0);
+            if (w1) atomicOr(&stage[w + 1], w1);
+            if (w2) atomicOr(&stage[w + 2], w2);
+        };
+
+        for (uint32_t i0 = 0; i0 < n; i0 += 32) {
+            const uint32_t idx = i0 + lane;
+            const bool valid = idx < n;
+            const uint32_t e = valid ? __ldg(ent + idx) : 0u;
+            const bool isdc = (e & ENTRY_DC) != 0u;
+            const uint32_t tb = (e >> 30) & 1u;
+            const uint32_t pos = isdc ? 0u : ((e >> 16) & 63u);
+            const int x = isdc ? ((int)(e << 18) >> 18) : (int)(short)(e & 0xffffu);
+            const uint32_t rc = s_recip[tb][pos], hf = s_half[tb][pos];
+            // a2.5 quantise: sign(x) * ((|x| + 4q) / 8q), division as a multiply-high
+            const uint32_t qa = __umulhi((uint32_t)abs(x) + hf, rc);
+            int v = x < 0 ? -(int)qa : (int)qa;
+            if (isdc) {                                          // DC difference against the predictor block
+                const int xp = (int)(e << 4) >> 18;
+                const uint32_t qp = __umulhi((uint32_t)abs(xp) + hf, rc);
+                v -= xp < 0 ? -(int)qp : (int)qp;
             }
-            unsigned long long sym = ((unsigned long long)(ent >> 8) << nb) | vbits;
-            uint32_t len = (ent & 0xffu) + nb;
-            if (nz && active) {                                 // runs of 16 zeros: ZRL codes in front
-                const uint32_t z = tb ? zrl1 : zrl0;
-                for (uint32_t k = 0; k < nz; k++) {
+            const bool live = valid && (isdc || v != 0);
+            const uint32_t bal = __ballot_sync(0xffffffffu, live);
+            const uint32_t key = pos | (tb << 6);
+            const uint32_t below = bal & lt_mask;
+            uint32_t pk = __shfl_sync(0xffffffffu, key, (31 - __clz(below)) & 31);
+            if (!below) pk = carry;
+            const uint32_t ppos = pk & 63u, ptb = pk >> 6;
+            const int nb = 32 - __clz(abs(v));
+            const uint32_t vbits = (uint32_t)(v + (v >> 31)) & ((1u << nb) - 1u);
+            uint32_t ent_code, nz = 0;
+            if (isdc) {
+                ent_code = s_dc[tb][nb & 15];
+            } else {
+                const uint32_t r = (pos - ppos - 1u) & 63u;
+                nz = r >> 4;
+                ent_code = s_ac[tb][((r & 15u) << 4) | (uint32_t)(nb & 15)];
+            }
+            unsigned long long sym = ((unsigned long long)(ent_code >> 8) << nb) | vbits;
+            uint32_t len = (ent_code & 0xffu) + nb;
+            if (live) {
+                if (isdc && ppos < 63u) {                       // previous block ended early: its EOB goes first
+                    const uint32_t z = ptb ? eob1 : eob0;
                     sym |= (unsigned long long)(z >> 8) << len;
                     len += z & 0xffu;
                 }
+                if (nz) {                                       // runs of 16 zeros: ZRL codes in front
+                    const uint32_t z = tb ? zrl1 : zrl0;
+                    for (uint32_t k = 0; k < nz; k++) {
+                        sym |= (unsigned long long)(z >> 8) << len;
+                        len += z & 0xffu;
+                    }
+                }
+            } else {
+                len = 0;
             }
-            const bool last_in_block =
-                (at_end && idx + 1 == cnt) || (idx + 1 < cnt && ((ne >> 16) & 63u) == 0);
-            if (last_in_block && pos < 63) {                    // end-of-block
-                const uint32_t z = tb ? eob1 : eob0;
-                sym = (sym << (z & 0xffu)) | (z >> 8);
-                len += z & 0xffu;
-            }
-            if (!active) len = 0;
             uint32_t incl = len;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -186,99 +337,163 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_symbols(const EntParams
             }
             const uint32_t off = running + incl - len;
             running += __shfl_sync(0xffffffffu, incl, 31);
-            if (len) {
-                const unsigned long long V = sym << (64 - len);
-                const uint32_t hiw = (uint32_t)(V >> 32), low = (uint32_t)V;
-                const uint32_t w = (off >> 5) - flushed, sh = off & 31;
-                const uint32_t w0 = hiw >> sh;
-                const uint32_t w1 = __funnelshift_r(low, hiw, sh);
-                const uint32_t w2 = __funnelshift_r(0u, low, sh);
-                if (w0) atomicOr(&stage[w], w0);
-                if (w1) atomicOr(&stage[w + 1], w1);
-                if (w2) atomicOr(&stage[w + 2], w2);
-            }
-            head += n;
-            if ((running >> 5) - flushed > (uint32_t)(ENT_WIN - 72)) flush(false);   // a round adds <= 63 words
-        };
-
-        for (int it = 0; it < ENT_TILE_BLOCKS / 4; it++) {
-            const int b = tile * ENT_TILE_BLOCKS + it * 4 + g;
-            const bool valid = b < p.nblocks;
-            const int cidx = b % 6;
-            const int tb = cidx >= 4 ? 1 : 0;
-            // DC predictor = previous block of the same component in scan order
-            int prev = b - 1;
-            bool has_prev = true;
-            if (cidx == 0) { prev = b - 3; has_prev = b >= 6; }
-            else if (cidx >= 4) { prev = b - 6; has_prev = b >= 6; }
-            uint4 raw = make_uint4(0, 0, 0, 0);
-            int xp = 0;
-            if (valid) {
-                raw = __ldg(reinterpret_cast<const uint4 *>(p.coef) + (size_t)b * 8 + j);
-                if (j == 0 && has_prev) xp = (int)__ldg(p.coef + (size_t)prev * 64);
-            }
-            const uint4 m0 = *reinterpret_cast<const uint4 *>(&s_recip[tb][8 * j]);
-            const uint4 m1 = *reinterpret_cast<const uint4 *>(&s_recip[tb][8 * j + 4]);
-            const uint4 hh = *reinterpret_cast<const uint4 *>(&s_half[tb][8 * j]);
-            const uint32_t rw[4] = {raw.x, raw.y, raw.z, raw.w};
-            const uint32_t mm[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-            const uint32_t hw[4] = {hh.x, hh.y, hh.z, hh.w};
-
-            // a2.5 quantise: sign(x) * ((|x| + 4q) / 8q), division as a multiply-high
-            int v[8];
+            if (len) put(sym, len, off);
+            if (bal) carry = __shfl_sync(0xffffffffu, key, 31 - __clz(bal));
+            if ((running >> 5) - flushed > (uint32_t)(ENT_WIN - 64)) flush_some();   // a round adds <= 59 words
+        }
+        if (n && (carry & 63u) < 63u) {                         // EOB of the tile's last block
+            const uint32_t z = (carry >> 6) ? eob1 : eob0;
+            if (lane == 0) put((unsigned long long)(z >> 8), z & 0xffu, running);
+            running += z & 0xffu;
+        }
+        __syncwarp();
+        // final flush: finished words + the partial one + a zero word (emit reads one word ahead)
+        const uint32_t nw = ((running + 31) >> 5) - flushed;
+        if (flushed == 0) first_word = stage[0];
+        count_ff(nw, running);
+        for (uint32_t w = lane; w < nw + 1; w += 32) scr[flushed + w] = stage[w];
+        uint32_t f[8];
+        if (__any_sync(0xffffffffu, (acc0 | acc1) != 0u)) {
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                const int x = (i & 1) ? ((int)rw[i >> 1] >> 16) : ((int)(rw[i >> 1] << 16) >> 16);
-                const uint32_t half = (i & 1) ? (hw[i >> 1] >> 16) : (hw[i >> 1] & 0xffffu);
-                const uint32_t q = __umulhi((uint32_t)abs(x) + half, mm[i]);
-                v[i] = x < 0 ? -(int)q : (int)q;
+            for (int s = 0; s < 8; s++) {
+                const uint32_t a = s < 4 ? (acc0 >> (8 * s)) & 0xffu : (acc1 >> (8 * (s - 4))) & 0xffu;
+                f[s] = __reduce_add_sync(0xffffffffu, a);
             }
-            if (j == 0) {
-                const uint32_t q = __umulhi((uint32_t)abs(xp) + (hw[0] & 0xffffu), mm[0]);
-                v[0] -= xp < 0 ? -(int)q : (int)q;
-            }
-            uint32_t m8 = 0;
+        } else {
 #pragma unroll
-            for (int i = 0; i < 8; i++) m8 |= (v[i] != 0 ? 1u : 0u) << i;
-            if (j == 0) m8 |= 1u;                               // DC always codes a symbol
-            if (!valid) m8 = 0;
-            const uint32_t npop = __popc(m8);
-            uint32_t incl = npop;
+            for (int s = 0; s < 8; s++) f[s] = 0;
+        }
+        uint32_t tail_bits = 0;
+        if (lane == 0 && running) {
+            const uint32_t eb = running >= 8u ? running - 8u : 0u;
+            const uint32_t w = (eb >> 5) - flushed, sh = eb & 31;
+            const unsigned long long two = ((unsigned long long)stage[w] << 32) | stage[w + 1];
+            const uint32_t nbv = running >= 8u ? 8u : running;
+            const uint32_t last = (uint32_t)(two >> (64 - nbv - sh)) & ((1u << nbv) - 1u);
+            tail_bits = min(nbv, (uint32_t)(__ffs(~last) - 1));
+        }
+        __syncwarp();
+        for (uint32_t w = lane; w < nw + 3; w += 32) stage[w] = 0;      // window clean for the next tile
+        if (lane == 0) {
+            // counters are indexed by the tile's absolute start offset r = (8 - s) & 7
+            pb.ff[tile] = make_uint4(f[0] | (f[7] << 16), f[6] | (f[5] << 16), f[4] | (f[3] << 16),
+                                     f[2] | (f[1] << 16));
+            uint32_t head = min(8u, (uint32_t)__clz(~first_word));
+            if (running < 8u) head = min(head, running);
+            pb.L[tile] = running;
+            pb.ones[tile] = head | (tail_bits << 8);
+            __threadfence();
+        }
+        __syncwarp();
+
+        // ---- the last warp to finish a group of 32 tiles folds it (no waiting anywhere)
+        const int grp = tile >> 5;
+        const int g_first = grp << 5, g_n = min(32, p.ntiles - g_first);
+        uint32_t arrived = 0;
+        if (lane == 0) arrived = atomicAdd(p.grp_cnt + grp, 1u);
+        arrived = __shfl_sync(0xffffffffu, arrived, 0);
+        if (arrived != (uint32_t)(g_n - 1)) continue;
+        if (lane == 0) p.grp_cnt[grp] = 0;                              // ready for the next pass
+        __threadfence();
+        {
+            const bool have = lane < g_n;
+            const uint32_t L_l = have ? __ldcg(pb.L + g_first + lane) : 0u;
+            const uint4 f_l = have ? __ldcg(pb.ff + g_first + lane) : make_uint4(0, 0, 0, 0);
+            const uint32_t on_l = have ? __ldcg(pb.ones + g_first + lane) : 0u;
+            uint32_t inclL = L_l;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+                const uint32_t t = __shfl_up_sync(0xffffffffu, inclL, o);
+                if (lane >= o) inclL += t;
+            }
+            const uint32_t ex = inclL - L_l;
+            const uint32_t on_prev = __shfl_up_sync(0xffffffffu, on_l, 1);
+            uint32_t tot[8];
+#pragma unroll
+            for (uint32_t R = 0; R < 8; R++) {                          // R = the group's absolute start offset mod 8
+                const uint32_t r = (R + ex) & 7u;
+                uint32_t c = have ? ff_select(f_l, r) : 0u;
+                if (have && lane > 0) c += span_ff(on_prev, on_l, r);
+                tot[R] = __reduce_add_sync(0xffffffffu, c);
+            }
+            const uint32_t Lg = __shfl_sync(0xffffffffu, inclL, 31);
+            const uint32_t head = __shfl_sync(0xffffffffu, on_l, 0) & 0xffu;
+            const uint32_t tail = __shfl_sync(0xffffffffu, on_l, g_n - 1) >> 8;
+            if (lane == 0) {
+                pb.Lg[grp] = Lg;
+                pb.onesg[grp] = head | (tail << 8);
+                pb.ffg[2 * grp] = make_uint4(tot[0], tot[1], tot[2], tot[3]);
+                pb.ffg[2 * grp + 1] = make_uint4(tot[4], tot[5], tot[6], tot[7]);
+                __threadfence();
+                arrived = atomicAdd(&st->done_a, 1u);
+            }
+        }
+        arrived = __shfl_sync(0xffffffffu, arrived, 0);
+        if (arrived != (uint32_t)(p.ngroups - 1)) continue;
+        __threadfence();
+
+        // ---- the last group of the pass: scan the group records into prefixes and the exact size
+#ifdef ICB_TIMING
+        if (lane == 0) st->dbg_t[dbg_pass][1] = gtime();
+#endif
+        {
+            const int n_g = p.ngroups;
+            const int chunk = (n_g + 31) / 32;
+            const int lo = min(n_g, lane * chunk), hi = min(n_g, lo + chunk);
+            unsigned long long sum = 0;
+            for (int i = lo; i < hi; i++) sum += (unsigned long long)__ldcg(pb.Lg + i);
+            unsigned long long incl = sum;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o);
                 if (lane >= o) incl += t;
             }
-            uint32_t rank = cnt + incl - npop;
-            cnt += __shfl_sync(0xffffffffu, incl, 31);
-            const uint32_t tag = ((uint32_t)tb << 22) | ((uint32_t)(8 * j) << 16);
+            unsigned long long run = incl - sum;
+            const unsigned long long total_bits = __shfl_sync(0xffffffffu, incl, 31);
+            uint32_t cnt = 0;
+            uint32_t prev_ones = lo > 0 && lo < n_g ? __ldcg(pb.onesg + lo - 1) : 0u;
+            for (int i = lo; i < hi; i++) {
+                const uint32_t Li = __ldcg(pb.Lg + i);
+                const uint4 fa = __ldcg(pb.ffg + 2 * i), fb = __ldcg(pb.ffg + 2 * i + 1);
+                const uint32_t on = __ldcg(pb.onesg + i);
+                const uint32_t r = (uint32_t)run & 7u;
+                const uint32_t f4[8] = {fa.x, fa.y, fa.z, fa.w, fb.x, fb.y, fb.z, fb.w};
+                uint32_t c = 0;
 #pragma unroll
-            for (int i = 0; i < 8; i++) {
-                if ((m8 >> i) & 1u) {
-                    ring[rank & (ENT_RING - 1)] = ((uint32_t)v[i] & 0xffffu) | (tag + ((uint32_t)i << 16));
-                    rank++;
-                }
+                for (uint32_t k = 0; k < 8; k++) c = r == k ? f4[k] : c;
+                pb.Pg[i] = run;
+                pb.Fg[i] = cnt;                                         // chunk-local for now
+                cnt += c + (i > 0 ? span_ff(prev_ones, on, r) : 0u);
+                prev_ones = on;
+                run += Li;
             }
+            if (hi == n_g && lo < n_g) {                                // jchuff.c flush_bits: last byte padded with 1s
+                const uint32_t rem = (uint32_t)run & 7u;
+                if (rem && (prev_ones >> 8) >= rem) cnt++;
+            }
+            uint32_t inclc = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, inclc, o);
+                if (lane >= o) inclc += t;
+            }
+            const uint32_t basef = inclc - cnt;
+            for (int i = lo; i < hi; i++) pb.Fg[i] += basef;
+            if (lane == 31) {
+                st->total_bits = total_bits;
+                st->ff_total = inclc;
+            }
+            __threadfence();
             __syncwarp();
-            while (cnt - head > 32) process_round(32, false);
         }
-        while (head < cnt) {
-            const uint32_t n = min(32u, cnt - head);
-            process_round(n, head + n == cnt);
-        }
-        flush(true);
-        if (lane == 0) pb.L[tile] = running;
+#ifdef ICB_TIMING
+        if (lane == 0) st->dbg_t[dbg_pass][2] = gtime();
+#endif
+        device_step(st, 0);         // :176-189 on the exact size, then tables of the next pass
+#ifdef ICB_TIMING
+        if (lane == 0) st->dbg_t[dbg_pass][3] = gtime();
+#endif
     }
-
-    // ---- last CTA: per-tile bit counts -> exclusive prefixes (replaces a look-back chain)
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) s_last = atomicAdd(&st->done_a, 1u) == gridDim.x - 1;
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    const unsigned long long total = cta_exclusive_scan(pb.L, pb.P, p.ntiles, s_part);
-    if (tid == 0) st->total_bits = total;
 }
 
 // ---- a tile's bits at their absolute alignment --------------------------------
@@ -291,10 +506,10 @@ struct TileView {
     bool last;
 };
 
-__device__ __forceinline__ TileView tile_view(const PassBufs &pb, int tile, int ntiles)
+__device__ __forceinline__ TileView tile_view(const PassBufs &pb, int tile, int ntiles, unsigned long long P,
+                                              uint32_t L, uint32_t Lp)
 {
     TileView v;
-    const unsigned long long L = __ldcg(pb.L + tile), P = __ldcg(pb.P + tile);
     v.scr = pb.scratch + (size_t)tile * ENT_SCR_STRIDE;
     v.r = (uint32_t)(P & 7ull);
     v.nbytes = (uint32_t)(((P + L) >> 3) - (P >> 3));
@@ -312,7 +527,6 @@ __device__ __forceinline__ TileView tile_view(const PassBufs &pb, int tile, int 
     }
     v.prev_tail = 0;
     if (v.r && tile > 0) {
-        const uint32_t Lp = __ldcg(pb.L + tile - 1);
         const uint32_t *sp = pb.scratch + (size_t)(tile - 1) * ENT_SCR_STRIDE;
         const uint32_t o = Lp - v.r, w = o >> 5, sh = o & 31;
         const unsigned long long two = ((unsigned long long)__ldcg(sp + w) << 32) | __ldcg(sp + w + 1);
@@ -322,78 +536,85 @@ __device__ __forceinline__ TileView tile_view(const PassBufs &pb, int tile, int 
 }
 
 // word w of the tile's byte stream (4 bytes, big-endian), and how many of them are real
-__device__ __forceinline__ uint32_t tile_word(const TileView &v, uint32_t w, uint32_t &eq_ff, uint32_t &nvalid)
+__device__ __forceinline__ uint32_t tile_word(const TileView &v, uint32_t w, uint32_t &nvalid)
 {
     const uint32_t hi = w ? __ldcg(v.scr + w - 1) : v.prev_tail;
     uint32_t val = __funnelshift_r(__ldcg(v.scr + w), hi, v.r);
     if (w == v.pad_word) val |= v.pad_mask;
     nvalid = min(4u, v.nbytes - 4 * w);
-    eq_ff = __vcmpeq4(val, 0xffffffffu);
-    if (nvalid < 4) eq_ff &= 0xffffffffu << (8 * (4 - nvalid));
+    if (nvalid < 4) val &= 0xffffffffu << (8 * (4 - nvalid));
     return val;
 }
 
-__global__ void __launch_bounds__(ENT_THREADS) k_entropy_count(const EntParams p)
-{
-    __shared__ unsigned int s_ff[ENT_WARPS];
-    __shared__ int s_last;
-    FitState *st = p.st;
-    if (!st->cur_valid) return;
-    const PassBufs pb = pick_buf(p, st->cur_buf);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x * ENT_WARPS + warp;
-    uint32_t ff = 0;
-    if (tile < p.ntiles) {
-        const TileView v = tile_view(pb, tile, p.ntiles);
-        const uint32_t nwords = (v.nbytes + 3) >> 2;
-        for (uint32_t w = lane; w < nwords; w += 32) {
-            uint32_t eq, nvalid;
-            tile_word(v, w, eq, nvalid);
-            ff += __popc(eq) >> 3;
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) ff += __shfl_xor_sync(0xffffffffu, ff, o);
-        if (lane == 0) pb.bytes[tile] = v.nbytes + ff;
-    }
-    if (lane == 0) s_ff[warp] = ff;
-    __syncthreads();
-    if (tid == 0) {
-        unsigned long long t = 0;
-        for (int w = 0; w < ENT_WARPS; w++) t += s_ff[w];
-        if (t) atomicAdd(&st->ff_total, t);
-        __threadfence();
-        s_last = atomicAdd(&st->done_c, 1u) == gridDim.x - 1;
-    }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    device_step(st, 0);         // :176-189 on the exact size, then tables of the next pass
-}
+// header template (tables, dims and JFIF minor patched per image); filled by the host
+__constant__ unsigned char c_hdr[HEADER_BYTES];
+constexpr int HDR_OFF_MINOR = 12, HDR_OFF_DQT0 = 25, HDR_OFF_DQT1 = 94, HDR_OFF_H = 163, HDR_OFF_W = 165;
 
-// once per image: byte prefixes of the chosen pass + the 623-byte header (a2.8)
-__global__ void __launch_bounds__(ENT_THREADS) k_finish(const EntParams p, unsigned char *out, long long out_cap,
-                                                        int w, int h);
-
-// once per image: a2.7 emit_bits byte stuffing of the chosen pass, then EOI
-__global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p, unsigned char *out, long long cap)
+// once per image: header (a2.8), a2.7 emit_bits byte stuffing of the chosen pass, EOI
+__global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p, unsigned char *out, long long cap,
+                                                              int img_w, int img_h)
 {
     const FitState *st = p.st;
-    if (!st->emit_valid) return;
+    if (st->best_size <= 0 || out == nullptr) return;
     const PassBufs pb = pick_buf(p, st->best_buf);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (blockIdx.x == 0) {
+        for (int i = tid; i < HEADER_BYTES; i += ENT_THREADS) {
+            unsigned char b = c_hdr[i];
+            if (i == HDR_OFF_MINOR) b = (unsigned char)st->jfif_minor;
+            else if (i >= HDR_OFF_DQT0 && i < HDR_OFF_DQT0 + 64) b = st->best_qtab[0][i - HDR_OFF_DQT0];
+            else if (i >= HDR_OFF_DQT1 && i < HDR_OFF_DQT1 + 64) b = st->best_qtab[1][i - HDR_OFF_DQT1];
+            else if (i == HDR_OFF_H) b = (unsigned char)(img_h >> 8);
+            else if (i == HDR_OFF_H + 1) b = (unsigned char)img_h;
+            else if (i == HDR_OFF_W) b = (unsigned char)(img_w >> 8);
+            else if (i == HDR_OFF_W + 1) b = (unsigned char)img_w;
+            if (i < cap) out[i] = b;
+        }
+    }
     const int tile = blockIdx.x * ENT_WARPS + warp;
     if (tile >= p.ntiles) return;
-    const TileView v = tile_view(pb, tile, p.ntiles);
+
+    // this tile's bit prefix and the 0xFF bytes completed before it: the group prefixes of the pass
+    // plus the tiles in front of it inside its group of 32 (lane = tile of the group)
+    const int grp = tile >> 5, g_first = grp << 5, me = tile & 31;
+    const bool have = g_first + lane < p.ntiles;
+    const uint32_t L_l = have ? __ldcg(pb.L + g_first + lane) : 0u;
+    const uint4 f_l = have ? __ldcg(pb.ff + g_first + lane) : make_uint4(0, 0, 0, 0);
+    const uint32_t on_l = have ? __ldcg(pb.ones + g_first + lane) : 0u;
+    uint32_t inclL = L_l;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inclL, o);
+        if (lane >= o) inclL += t;
+    }
+    const unsigned long long P_l = __ldcg(pb.Pg + grp) + (inclL - L_l);
+    const uint32_t r_l = (uint32_t)P_l & 7u;
+    uint32_t on_prev = __shfl_up_sync(0xffffffffu, on_l, 1);
+    if (lane == 0) on_prev = grp > 0 ? __ldcg(pb.onesg + grp - 1) : 0u;
+    const uint32_t c_l = have ? ff_select(f_l, r_l) + ((g_first + lane > 0) ? span_ff(on_prev, on_l, r_l) : 0u) : 0u;
+    uint32_t inclC = c_l;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t t = __shfl_up_sync(0xffffffffu, inclC, o);
+        if (lane >= o) inclC += t;
+    }
+    const uint32_t ffb_l = __ldcg(pb.Fg + grp) + (inclC - c_l);
+    const unsigned long long P = __shfl_sync(0xffffffffu, P_l, me);
+    const uint32_t L = __shfl_sync(0xffffffffu, L_l, me);
+    const uint32_t ff_before = __shfl_sync(0xffffffffu, ffb_l, me);
+    uint32_t Lp = __shfl_sync(0xffffffffu, L_l, (me + 31) & 31);
+    if (me == 0 && tile > 0) Lp = __ldcg(pb.L + tile - 1);
+
+    const TileView v = tile_view(pb, tile, p.ntiles, P, L, Lp);
     const uint32_t nwords = (v.nbytes + 3) >> 2;
-    const long long pos0 = (long long)HEADER_BYTES + (long long)__ldcg(pb.Q + tile);
-    uint32_t ff_before = 0;
+    const long long pos0 = (long long)HEADER_BYTES + (long long)(P >> 3) + (long long)ff_before;
+    uint32_t ff_run = 0;
     for (uint32_t wb = 0; wb < nwords; wb += 32) {
         const uint32_t w = wb + lane;
         uint32_t val = 0, cntf = 0, nvalid = 0;
         if (w < nwords) {
-            uint32_t eq;
-            val = tile_word(v, w, eq, nvalid);
-            cntf = __popc(eq) >> 3;
+            val = tile_word(v, w, nvalid);
+            cntf = ff_bytes(val);
         }
         uint32_t incl = cntf;
 #pragma unroll
@@ -401,7 +622,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
             const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
             if (lane >= o) incl += t;
         }
-        long long pos = pos0 + 4ll * w + ff_before + (incl - cntf);
+        long long pos = pos0 + 4ll * w + ff_run + (incl - cntf);
         for (uint32_t bi = 0; bi < nvalid; bi++) {
             const uint32_t byte = (val >> (24 - 8 * bi)) & 0xffu;
             if (pos < cap) out[pos] = (unsigned char)byte;
@@ -411,22 +632,20 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
                 pos++;
             }
         }
-        ff_before += __shfl_sync(0xffffffffu, incl, 31);
+        ff_run += __shfl_sync(0xffffffffu, incl, 31);
     }
     if (v.last && lane == 0) {                                  // EOI
-        const long long e = pos0 + (long long)__ldcg(pb.bytes + tile);
-        if (e < cap) out[e] = 0xff;
-        if (e + 1 < cap) out[e + 1] = 0xd9;
+        const long long e = st->best_size - 2;
+        if (e >= 0 && e < cap) out[e] = 0xff;
+        if (e + 1 >= 0 && e + 1 < cap) out[e + 1] = 0xd9;
     }
 }
 
-constexpr int ENT_SMEM_BYTES = ENT_WARPS * (ENT_WIN + ENT_RING) * 4;
-
-// per-slot pass arena: 2 x (scratch + L + P + bytes + Q)
-__host__ __device__ inline size_t ent_pass_bytes(int ntiles)
+// per-slot arenas
+__host__ __device__ inline size_t ent_pass_bytes(int ntiles, int ngroups)
 {
-    const size_t n = (size_t)ntiles;
-    return n * ENT_SCR_STRIDE * 4 + n * 4 + n * 8 + n * 4 + n * 8 + 64;
+    const size_t n = (size_t)ntiles, c = (size_t)ngroups;
+    return n * ENT_SCR_STRIDE * 4 + n * 4 + n * 16 + n * 4 + c * 4 + c * 32 + c * 4 + c * 8 + c * 4 + 256;
 }
 
 }  // namespace icb

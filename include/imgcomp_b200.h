@@ -111,6 +111,10 @@ int icb_resize_bilinear(icb_handle *h, const uint8_t *src, int w, int hgt, int p
  * false).  dst must hold dw*dh*bpp bytes (query with dst == NULL first). */
 int icb_png_fit(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt,
                 int min_w, int min_h, uint8_t *dst, size_t dst_cap, int *dw, int *dh);
+/* The dimension rule alone (core/ImageCompressionPng.java:49-61 + tools/ImageTools.java:8-9),
+ * host arithmetic, no device needed: ICB_NO_FIT when w <= min_w && h <= min_h, else ICB_OK
+ * with the target size and the double scale = min(min_w / w, min_h / h). */
+int icb_png_target_dims(int w, int hgt, int min_w, int min_h, int *dw, int *dh, double *scale);
 
 /* Asynchronous form = the per-GPU stream work queue that replaces the executor
  * (CompressionBatch.java:77-88 submit, :97-107 await).  submit blocks only while
