@@ -35,6 +35,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     cmd = [nvcc_path(), "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
            "--expt-relaxed-constexpr", "-Xcompiler", "-fPIC,-O3,-fno-fast-math", "-shared", "-cudart", "static",
            "-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
+    if os.environ.get("ICB_TIMING"):
+        cmd.insert(1, "-DICB_TIMING")
     if verbose:
         cmd.insert(1, "-Xptxas")
         cmd.insert(2, "-v")

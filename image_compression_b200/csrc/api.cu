@@ -267,15 +267,15 @@ int max_search_iters(float init_q)
     return std::min(8, n + 1);
 }
 
-// persistent grid of the entropy pass: c CTAs per SM (c <= 5 by registers) such that the statically
+// persistent grid of the entropy pass: c CTAs per SM (c <= 4 by registers) such that the statically
 // dealt tiles fill the last round of every warp as evenly as possible
 int pass_grid(int ntiles, int sms)
 {
     const int need = (ntiles + ENT_WARPS - 1) / ENT_WARPS;
-    if (need <= sms * 5) return need;
-    int best_grid = sms * 5;
+    if (need <= sms * 4) return need;
+    int best_grid = sms * 4;
     double best_eff = 0.0;
-    for (int c = 5; c >= 2; c--) {
+    for (int c = 4; c >= 2; c--) {
         const long long warps = (long long)sms * c * ENT_WARPS;
         const long long rounds = (ntiles + warps - 1) / warps;
         const double eff = (double)ntiles / (double)(rounds * warps);
@@ -974,6 +974,16 @@ int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q,
                 cudaEventElapsedTime(&c, pe[2 * i], pe[2 * i + 1]);
                 entk += c;
             }
+#ifdef ICB_TIMING
+            if (r == reps - 1) {
+                const FitState &fs = *s->h_state;
+                for (int i = 0; i < fs.passes && i < 8; i++)
+                    fprintf(stderr, "pass %d: tiles %.1f us, scan %.1f us, step %.1f us, gap to next %.1f us\n", i,
+                            (fs.dbg_t[i][1] - fs.dbg_t[i][0]) * 1e-3, (fs.dbg_t[i][2] - fs.dbg_t[i][1]) * 1e-3,
+                            (fs.dbg_t[i][3] - fs.dbg_t[i][2]) * 1e-3,
+                            i + 1 < fs.passes ? ((double)fs.dbg_t[i + 1][0] - (double)fs.dbg_t[i][3]) * 1e-3 : 0.0);
+            }
+#endif
             h->passes += (uint64_t)s->h_state->passes;
             h->last_xf_launches = (int)(k1 - k0);
             h->last_ent_launches = (int)(h->kernels.load() - k1);

@@ -60,6 +60,12 @@ constexpr int HEADER_BYTES = 623;                   // a2.8, 3-component JFIF
 // ---- device state of one fit job (lives in HBM, one per slot) ----
 enum FitMode { MODE_SEARCH = 0, MODE_SINGLE = 1 };
 
+// quantisation tables of one quality, indexed by key = 2 * zigzag pos + table (0 luma, 1 chroma)
+struct QTables {
+    uint2 rh[128];                  // x = reciprocal: floor(t / (8 q)) == umulhi(t, x) for t < 2^17;  y = 4 q
+    unsigned char qtab[2][64];      // the table itself, zigzag order (DQT payload)
+};
+
 struct FitState {
     // search control (core/ImageCompressionJpg.java:158-200), float32 as in Java
     float lo, hi, best;
@@ -69,7 +75,7 @@ struct FitState {
     int cur_valid;          // the coming pass has work
     int mode;
     int cur_buf, best_buf;  // ping-pong output buffers
-    int epoch;              // descriptor epoch of the coming pass (1..31)
+    int tsel;               // table slot (0..2) of the coming pass
     int n_trace;
     int table_mode, jfif_minor;
     int passes;             // entropy passes actually run
@@ -78,10 +84,10 @@ struct FitState {
     long long cur_size, best_size;
     float trace_q[8];
     long long trace_size[8];
-    // tables of the coming pass, ZIGZAG order; [0]=luma [1]=chroma
-    unsigned int recip[2][64];      // ceil-ish 2^32 / (8 q): floor(t/(8q)) == umulhi(t, recip)
-    unsigned short half[2][64];     // 4 q
-    unsigned char qtab[2][64];
+    // three table slots: the coming pass reads tab[tsel]; while it runs, block 0 fills the other two
+    // with the tables of both possible next midpoints ((tsel+1)%3: this pass fits, (tsel+2)%3: it
+    // does not), so the bisection step at the end of the pass only flips tsel
+    QTables tab[3];
     unsigned short thr[2][64];      // survivor thresholds (4 q at the highest quality of the job), zigzag order
     unsigned char best_qtab[2][64]; // tables of the best pass so far (header of the final stream)
     // pass scratch
@@ -92,7 +98,7 @@ struct FitState {
     unsigned long long total_bits;  // entropy-coded bits before padding
 };
 
-static_assert(offsetof(FitState, qtab) % 4 == 0 && offsetof(FitState, best_qtab) % 4 == 0, "word copies of the tables");
+static_assert(offsetof(FitState, tab) % 8 == 0 && offsetof(FitState, best_qtab) % 4 == 0, "vector copies of the tables");
 
 // ---- Annex K tables (T.81), natural order; IJG jcparam.c / JDK JPEGQTable ----
 __constant__ unsigned char c_base_lum[64] = {

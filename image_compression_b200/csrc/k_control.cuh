@@ -42,23 +42,48 @@ __device__ __forceinline__ int scaled_qval(int base, float q, int table_mode)
     return sv;
 }
 
+// one entry (idx = table * 64 + zigzag k) of the tables for quality q
+__device__ __forceinline__ void table_entry(QTables *t, int idx, float q, int table_mode)
+{
+    const int tb = idx >> 6, k = idx & 63;
+    const int nat = c_zigzag[k];
+    const int qv = scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], q, table_mode);
+    const unsigned d = (unsigned)qv << 3;                       // jcdctmgr.c: divisor = quantval << 3
+    // floor(2^32 / d) + 1 without a 64-bit division: umulhi(t, recip) == t / d for t < 2^17
+    const unsigned recip = 0xffffffffu / d + 1u + ((d & (d - 1u)) == 0u ? 1u : 0u);
+    t->rh[2 * k + tb] = make_uint2(recip, d >> 1);
+    t->qtab[tb][k] = (unsigned char)qv;
+}
+
+// Both midpoints the bisection can ask for after the running pass (:168 with :180-185 applied),
+// computed by 256 threads of one CTA while the pass runs: set 0 = this pass fits, set 1 = it does not.
+__device__ __forceinline__ void precompute_next_tables(FitState *st, int tid)
+{
+    if (st->mode != MODE_SEARCH || tid >= 256) return;
+    const int set = tid >> 7;
+    const float lo = set ? st->lo : st->cur_q, hi = set ? st->cur_q : st->hi;
+    const float mid = __fdiv_rn(__fadd_rn(lo, hi), 2.0f);
+    table_entry(&st->tab[(st->tsel + 1 + set) % 3], tid & 127, mid, st->table_mode);
+}
+
 // Called by all 32 lanes of ONE warp.  Consumes the pass that just ran (if any),
-// decides, and prepares the next one.  Lane 0 reads every control field first and
-// writes them back at the end, so the global accesses pipeline instead of chaining.
-__device__ void device_step(FitState *st, int final_call)
+// decides, and selects the tables of the next one.  Lane 0 reads every control field
+// first and writes them back at the end, so the global accesses pipeline.
+__device__ void device_step(FitState *st, int first)
 {
     const int lane = threadIdx.x & 31;
-    int go = 0, better = 0;
-    float next_q = 0.0f;
+    int go = 0, better = 0, old_sel = 0;
     if (lane == 0) {
         float lo = st->lo, hi = st->hi, best = st->best, cur_q = st->cur_q;
         int iter = st->iter, done = st->done, n_trace = st->n_trace, passes = st->passes;
-        int cur_buf = st->cur_buf, best_buf = st->best_buf;
+        int cur_buf = st->cur_buf, best_buf = st->best_buf, tsel = st->tsel;
         const int cur_valid = st->cur_valid, mode = st->mode;
         const long long target = st->target;
         long long best_size = st->best_size, cur_size = st->cur_size;
         const unsigned long long tbits = *(volatile unsigned long long *)&st->total_bits;
         const unsigned long long ffs = *(volatile unsigned long long *)&st->ff_total;
+        int fit = 0;
+        old_sel = tsel;
         if (cur_valid) {                                        // consume the pass that just ran
             const long long size = (long long)HEADER_BYTES + (long long)((tbits + 7ull) >> 3) + (long long)ffs + 2;
             cur_size = size;
@@ -73,6 +98,7 @@ __device__ void device_step(FitState *st, int final_call)
                     best = cur_q;
                     lo = cur_q;
                     better = 1;
+                    fit = 1;
                 } else {
                     hi = cur_q;
                 }
@@ -87,7 +113,7 @@ __device__ void device_step(FitState *st, int final_call)
                 best_size = size;
             }
         }
-        if (!done && !final_call) {
+        if (!done) {
             if (mode == MODE_SEARCH) {
                 if (iter >= 8) {                                // :167
                     done = 1;
@@ -107,36 +133,23 @@ __device__ void device_step(FitState *st, int final_call)
         if (go) {
             iter++;
             cur_buf = (best_size > 0) ? (1 - best_buf) : 0;
+            if (!first) tsel = (tsel + (fit ? 1 : 2)) % 3;       // precompute_next_tables filled that slot
         }
-        next_q = cur_q;
         st->lo = lo; st->hi = hi; st->best = best; st->cur_q = cur_q;
         st->iter = iter; st->done = done; st->n_trace = n_trace; st->passes = passes;
-        st->cur_buf = cur_buf; st->best_buf = best_buf; st->cur_valid = go;
+        st->cur_buf = cur_buf; st->best_buf = best_buf; st->cur_valid = go; st->tsel = tsel;
         st->best_size = best_size; st->cur_size = cur_size;
         st->done_a = 0;
         st->ff_total = 0;
         st->total_bits = 0;
     }
     better = __shfl_sync(0xffffffffu, better, 0);
-    go = __shfl_sync(0xffffffffu, go, 0);
-    next_q = __shfl_sync(0xffffffffu, next_q, 0);
+    old_sel = __shfl_sync(0xffffffffu, old_sel, 0);
     if (better)                                                 // tables of the best pass so far: 128 B, one word per lane
         reinterpret_cast<unsigned int *>(&st->best_qtab[0][0])[lane] =
-            reinterpret_cast<const unsigned int *>(&st->qtab[0][0])[lane];
-    __syncwarp();
-    if (go) {
-        const int table_mode = st->table_mode;
-        for (int t = lane; t < 128; t += 32) {                  // 2 tables x 64 entries, zigzag order
-            const int tb = t >> 6, k = t & 63;
-            const int nat = c_zigzag[k];
-            const int qv = scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], next_q, table_mode);
-            const unsigned d = (unsigned)qv << 3;               // jcdctmgr.c: divisor = quantval << 3
-            st->qtab[tb][k] = (unsigned char)qv;
-            st->recip[tb][k] = (unsigned)((1ull << 32) / d) + 1u;   // umulhi(t, recip) == t / d for t < 2^17
-            st->half[tb][k] = (unsigned short)(d >> 1);
-        }
-    }
+            reinterpret_cast<const unsigned int *>(&st->tab[old_sel].qtab[0][0])[lane];
     __threadfence();
+    __syncwarp();
 }
 
 __global__ void __launch_bounds__(32) k_begin(FitState *st, int mode, float q, long long target, int table_mode,
@@ -154,7 +167,7 @@ __global__ void __launch_bounds__(32) k_begin(FitState *st, int mode, float q, l
         st->mode = mode;
         st->cur_buf = 0;
         st->best_buf = 0;
-        st->epoch = 0;
+        st->tsel = 0;
         st->n_trace = 0;
         st->table_mode = table_mode;
         st->jfif_minor = jfif_minor;
@@ -163,19 +176,22 @@ __global__ void __launch_bounds__(32) k_begin(FitState *st, int mode, float q, l
         st->cur_size = 0;
         st->best_size = 0;
     }
-    {   // survivor thresholds for k_entropy_prepare: a coefficient is non-zero at quality q iff
-        // |x| >= 4 * table(q), and table(q) never grows with q, so the tables of the highest
-        // quality this job can reach (q itself: every midpoint is below hi <= q) bound them all
-        for (int t = threadIdx.x; t < 128; t += 32) {
-            const int tb = t >> 6, k = t & 63;
-            const int nat = c_zigzag[k];
-            const int qv = scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], q, table_mode);
-            st->thr[tb][k] = (unsigned short)(qv << 2);
-        }
+    // survivor thresholds for k_entropy_prepare: a coefficient is non-zero at quality q iff
+    // |x| >= 4 * table(q), and table(q) never grows with q, so the tables of the highest
+    // quality this job can reach (q itself: every midpoint is below hi <= q) bound them all
+    for (int t = threadIdx.x; t < 128; t += 32) {
+        const int tb = t >> 6, k = t & 63;
+        const int nat = c_zigzag[k];
+        const int qv = scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], q, table_mode);
+        st->thr[tb][k] = (unsigned short)(qv << 2);
     }
     __threadfence();
     __syncwarp();
-    device_step(st, 0);
+    device_step(st, 1);
+    if (st->cur_valid) {
+        const float q0 = st->cur_q;
+        for (int t = threadIdx.x; t < 128; t += 32) table_entry(&st->tab[0], t, q0, table_mode);
+    }
 }
 
 }  // namespace icb

@@ -77,12 +77,14 @@ __device__ __forceinline__ PassBufs pick_buf(const EntParams &p, int i)
 }
 
 // a2.1 / :158-200 -- defined in k_control.cuh
-__device__ void device_step(FitState *st, int final_call);
+__device__ void device_step(FitState *st, int first);
+__device__ __forceinline__ void precompute_next_tables(FitState *st, int tid);
 
 // ---- survivor entries ------------------------------------------------------------
-// AC: val(16) | zigzag pos(6) << 16 | table << 30
-// DC: dc(14)  | predictor dc(14) << 14 | table << 30 | 1 << 31      (raw DC = sum - 8192: 14 bits signed)
-constexpr uint32_t ENTRY_DC = 0x80000000u;
+// AC: val(16) | table << 17 | zigzag pos(6) << 18
+// DC: dc(16)  | 1 << 16 | table << 17 | predictor dc(14) << 18      (raw DC = sum - 8192: 14 bits signed)
+// so that (e >> 17) & 127 = 2 * pos + table is the key of an AC entry's quantiser
+constexpr uint32_t ENTRY_DC = 0x10000u;
 
 __device__ __forceinline__ uint32_t ff_select(const uint4 &f, uint32_t r)        // counter r of 8 x u16
 {
@@ -153,15 +155,15 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prepare(const EntParams
         }
         uint32_t rank = cnt + incl - npop;
         cnt += __shfl_sync(0xffffffffu, incl, 31);
-        const uint32_t tag = (tb << 30) | ((uint32_t)(8 * j) << 16);
+        const uint32_t tag = (tb << 17) | ((uint32_t)(8 * j) << 18);
 #pragma unroll
         for (int i = 0; i < 8; i++) {
             if ((m8 >> i) & 1u) {
                 uint32_t e;
                 if (i == 0 && j == 0)
-                    e = ENTRY_DC | (tb << 30) | (((uint32_t)xp & 0x3fffu) << 14) | ((uint32_t)x[0] & 0x3fffu);
+                    e = ENTRY_DC | (tb << 17) | ((uint32_t)xp << 18) | ((uint32_t)x[0] & 0xffffu);
                 else
-                    e = ((uint32_t)x[i] & 0xffffu) | (tag + ((uint32_t)i << 16));
+                    e = ((uint32_t)x[i] & 0xffffu) | (tag + ((uint32_t)i << 18));
                 out[rank++] = e;
             }
         }
@@ -187,10 +189,8 @@ __device__ __forceinline__ uint32_t ff_starts(uint32_t a, uint32_t b)
 
 __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
 {
-    __shared__ uint32_t s_ac[2][256];
-    __shared__ uint32_t s_dc[2][16];
-    __shared__ uint32_t s_recip[2][64];
-    __shared__ uint32_t s_half[2][64];
+    __shared__ uint32_t s_huf[512 + 32];            // AC: table * 256 + run * 16 + size;  DC: 512 + table * 16 + size
+    __shared__ uint2 s_qt[128];                     // quantiser by key = 2 * pos + table
     __shared__ uint32_t s_win[ENT_WARPS * ENT_WSTRIDE];
 
     FitState *st = p.st;
@@ -202,18 +202,16 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
 #endif
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < 512; i += ENT_THREADS) s_ac[i >> 8][i & 255] = c_ac_enc[i >> 8][i & 255];
-    if (tid < 32) s_dc[tid >> 4][tid & 15] = c_dc_enc[tid >> 4][tid & 15];
-    if (tid < 128) {
-        s_recip[tid >> 6][tid & 63] = st->recip[tid >> 6][tid & 63];
-        s_half[tid >> 6][tid & 63] = st->half[tid >> 6][tid & 63];
-    }
-    uint32_t *stage = s_win + warp * ENT_WSTRIDE;
-    for (int i = lane; i < ENT_WSTRIDE; i += 32) stage[i] = 0;
+    for (int i = tid; i < 512; i += ENT_THREADS) s_huf[i] = c_ac_enc[i >> 8][i & 255];
+    if (tid < 32) s_huf[512 + tid] = c_dc_enc[tid >> 4][tid & 15];
+    if (tid < 128) s_qt[tid] = st->tab[st->tsel].rh[tid];
+    const uint32_t wbase = warp * ENT_WSTRIDE;
+    for (int i = lane; i < ENT_WSTRIDE; i += 32) s_win[wbase + i] = 0;
+    if (blockIdx.x == 0) precompute_next_tables(st, tid);      // off the critical path of the pass
     __syncthreads();
 
-    const uint32_t zrl0 = s_ac[0][0xF0], zrl1 = s_ac[1][0xF0];
-    const uint32_t eob0 = s_ac[0][0], eob1 = s_ac[1][0];
+    const uint32_t zrl0 = s_huf[0xF0], zrl1 = s_huf[256 + 0xF0];
+    const uint32_t eob0 = s_huf[0], eob1 = s_huf[256];
     const uint32_t lt_mask = (1u << lane) - 1u;
 
     // persistent warps: tiles are dealt out statically (no shared cursor a late CTA could overrun)
@@ -224,14 +222,14 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         uint32_t running = 0;       // bits produced so far (tile-local)
         uint32_t flushed = 0;       // whole words already copied to scratch
         uint32_t acc0 = 0, acc1 = 0;   // 0xFF counters, 4 x 8 bits each: local start bit s = 0..3 | 4..7
-        uint32_t carry = 63u;       // zigzag pos | table << 6 of the last live entry (63: no EOB owed)
+        uint32_t carry = 126u;      // key of the last live entry (126 = pos 63: no EOB owed)
         uint32_t first_word = 0;    // word 0 of the tile stream (for the leading-ones count)
 
         // 0xFF bytes that START in window words [0, nw) -- word w+1 must be final already --
         // for the 8 local start bits s; limit = tile bits that exist (a byte must end <= limit)
         auto count_ff = [&](uint32_t nw, uint32_t limit) {
             for (uint32_t w = lane; w < nw; w += 32) {
-                uint32_t m = ff_starts(stage[w], stage[w + 1]);
+                uint32_t m = ff_starts(s_win[wbase + w], s_win[wbase + w + 1]);
                 const uint32_t bit0 = (flushed + w) << 5;
                 const uint32_t rem = limit > bit0 ? limit - bit0 : 0u;      // bits from this word on
                 if (rem < 40u) m &= rem < 8u ? 0u : 0xffffffffu << (39u - rem);
@@ -251,107 +249,104 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             __syncwarp();
             const uint32_t have = (running >> 5) - flushed;         // finished words in the window
             if (have >= 2) {
-                if (flushed == 0) first_word = stage[0];
+                if (flushed == 0) first_word = s_win[wbase];
                 const uint32_t nf = have - 1;
                 count_ff(nf, 0xffffffffu);
-                const uint32_t c0 = stage[nf], c1 = stage[nf + 1], c2 = stage[nf + 2];
-                for (uint32_t w = lane; w < nf; w += 32) scr[flushed + w] = stage[w];
+                const uint32_t c0 = s_win[wbase + nf], c1 = s_win[wbase + nf + 1], c2 = s_win[wbase + nf + 2];
+                for (uint32_t w = lane; w < nf; w += 32) scr[flushed + w] = s_win[wbase + w];
                 __syncwarp();
-                for (uint32_t w = lane; w < nf + 3; w += 32) stage[w] = 0;
+                for (uint32_t w = lane; w < nf + 3; w += 32) s_win[wbase + w] = 0;
                 __syncwarp();
-                if (lane == 0) { stage[0] = c0; stage[1] = c1; stage[2] = c2; }
+                if (lane == 0) { s_win[wbase] = c0; s_win[wbase + 1] = c1; s_win[wbase + 2] = c2; }
                 flushed += nf;
             }
             __syncwarp();
         };
 
-        auto put = [&](unsigned long long sym, uint32_t len, uint32_t off) {
-            const unsigned long long V = sym << (64 - len);
-            const uint32_t hiw = (uint32_t)(V >> 32), low = (uint32_t)V;
-            const uint32_t w = (off >> 5) - flushed, sh = off & 31;
-            const uint32_t w0 = hiw >> sh;
-            const uint32_t w1 = __funnelshift_r(low, hiw, sh);
-            const uint32_t w2 = __funnelshift_r(0u, low, sh);
-            if (w0) atomicOr(&stage[w], w0);
-            if (w1) atomicOr(&stage[w + 1], w1);
-            if (w2) atomicOr(&stage[w + 2], w2);
+        // OR `len` (1..32) bits of sym into the window at tile bit offset off
+        auto put = [&](uint32_t sym, uint32_t len, uint32_t off) {
+            const uint32_t V = sym << (32u - len);
+            const uint32_t a = wbase + (off >> 5) - flushed, sh = off & 31u;
+            const uint32_t w0 = V >> sh, w1 = __funnelshift_r(0u, V, sh);
+            atomicOr(&s_win[a], w0);
+            if (w1) atomicOr(&s_win[a + 1], w1);
         };
 
+        uint32_t e_next = (uint32_t)lane < n ? __ldg(ent + lane) : 0u;
         for (uint32_t i0 = 0; i0 < n; i0 += 32) {
-            const uint32_t idx = i0 + lane;
-            const bool valid = idx < n;
-            const uint32_t e = valid ? __ldg(ent + idx) : 0u;
+            const uint32_t e = e_next;
+            {   // next round's entries are in flight while this one is coded
+                const uint32_t ni = i0 + 32 + lane;
+                e_next = ni < n ? __ldg(ent + ni) : 0u;
+            }
             const bool isdc = (e & ENTRY_DC) != 0u;
-            const uint32_t tb = (e >> 30) & 1u;
-            const uint32_t pos = isdc ? 0u : ((e >> 16) & 63u);
-            const int x = isdc ? ((int)(e << 18) >> 18) : (int)(short)(e & 0xffffu);
-            const uint32_t rc = s_recip[tb][pos], hf = s_half[tb][pos];
+            const uint32_t key = (e >> 17) & (isdc ? 1u : 127u);         // 2 * pos + table
+            const int x = (int)(short)(e & 0xffffu);
+            const uint2 qt = s_qt[key];
             // a2.5 quantise: sign(x) * ((|x| + 4q) / 8q), division as a multiply-high
-            const uint32_t qa = __umulhi((uint32_t)abs(x) + hf, rc);
+            const uint32_t qa = __umulhi((uint32_t)abs(x) + qt.y, qt.x);
             int v = x < 0 ? -(int)qa : (int)qa;
             if (isdc) {                                          // DC difference against the predictor block
-                const int xp = (int)(e << 4) >> 18;
-                const uint32_t qp = __umulhi((uint32_t)abs(xp) + hf, rc);
+                const int xp = (int)e >> 18;
+                const uint32_t qp = __umulhi((uint32_t)abs(xp) + qt.y, qt.x);
                 v -= xp < 0 ? -(int)qp : (int)qp;
             }
-            const bool live = valid && (isdc || v != 0);
+            const bool live = isdc || v != 0;                    // lanes past n hold e = 0: dead
             const uint32_t bal = __ballot_sync(0xffffffffu, live);
-            const uint32_t key = pos | (tb << 6);
+            if (bal == 0u) continue;
             const uint32_t below = bal & lt_mask;
             uint32_t pk = __shfl_sync(0xffffffffu, key, (31 - __clz(below)) & 31);
-            if (!below) pk = carry;
-            const uint32_t ppos = pk & 63u, ptb = pk >> 6;
-            const int nb = 32 - __clz(abs(v));
+            if (!below) pk = carry;                              // key of the previous live entry
+            const uint32_t nb = 32u - (uint32_t)__clz(abs(v));
             const uint32_t vbits = (uint32_t)(v + (v >> 31)) & ((1u << nb) - 1u);
-            uint32_t ent_code, nz = 0;
+            const uint32_t r = ((key - pk) >> 1) - 1u;           // zero run in front of an AC coefficient
+            const uint32_t hidx = isdc ? 512u + (key << 4) + nb : ((key & 1u) << 8) | ((r & 15u) << 4) | nb;
+            const uint32_t code = s_huf[hidx];
+            uint32_t sym = ((code >> 8) << nb) | vbits;
+            uint32_t len = (code & 0xffu) + nb;
+            uint32_t nz = 0, zlen = 0;
             if (isdc) {
-                ent_code = s_dc[tb][nb & 15];
-            } else {
-                const uint32_t r = (pos - ppos - 1u) & 63u;
-                nz = r >> 4;
-                ent_code = s_ac[tb][((r & 15u) << 4) | (uint32_t)(nb & 15)];
-            }
-            unsigned long long sym = ((unsigned long long)(ent_code >> 8) << nb) | vbits;
-            uint32_t len = (ent_code & 0xffu) + nb;
-            if (live) {
-                if (isdc && ppos < 63u) {                       // previous block ended early: its EOB goes first
-                    const uint32_t z = ptb ? eob1 : eob0;
-                    sym |= (unsigned long long)(z >> 8) << len;
+                if (pk < 126u) {                                 // previous block ended early: its EOB goes first
+                    const uint32_t z = (pk & 1u) ? eob1 : eob0;
+                    sym |= (z >> 8) << len;
                     len += z & 0xffu;
                 }
-                if (nz) {                                       // runs of 16 zeros: ZRL codes in front
-                    const uint32_t z = tb ? zrl1 : zrl0;
-                    for (uint32_t k = 0; k < nz; k++) {
-                        sym |= (unsigned long long)(z >> 8) << len;
-                        len += z & 0xffu;
-                    }
-                }
             } else {
-                len = 0;
+                nz = r >> 4;                                     // runs of 16 zeros: ZRL codes in front
+                zlen = nz * (((key & 1u) ? zrl1 : zrl0) & 0xffu);
             }
-            uint32_t incl = len;
+            if (!live) { len = 0; nz = 0; zlen = 0; }
+            const uint32_t tot = len + zlen;
+            uint32_t incl = tot;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
                 const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
                 if (lane >= o) incl += t;
             }
-            const uint32_t off = running + incl - len;
+            uint32_t off = running + incl - tot;
             running += __shfl_sync(0xffffffffu, incl, 31);
+            if (nz) {
+                const uint32_t z = (key & 1u) ? zrl1 : zrl0;
+                for (uint32_t k = 0; k < nz; k++) {
+                    put(z >> 8, z & 0xffu, off);
+                    off += z & 0xffu;
+                }
+            }
             if (len) put(sym, len, off);
-            if (bal) carry = __shfl_sync(0xffffffffu, key, 31 - __clz(bal));
+            carry = __shfl_sync(0xffffffffu, key, 31 - __clz(bal));
             if ((running >> 5) - flushed > (uint32_t)(ENT_WIN - 64)) flush_some();   // a round adds <= 59 words
         }
-        if (n && (carry & 63u) < 63u) {                         // EOB of the tile's last block
-            const uint32_t z = (carry >> 6) ? eob1 : eob0;
-            if (lane == 0) put((unsigned long long)(z >> 8), z & 0xffu, running);
+        if (carry < 126u) {                                     // EOB of the tile's last block
+            const uint32_t z = (carry & 1u) ? eob1 : eob0;
+            if (lane == 0) put(z >> 8, z & 0xffu, running);
             running += z & 0xffu;
         }
         __syncwarp();
         // final flush: finished words + the partial one + a zero word (emit reads one word ahead)
         const uint32_t nw = ((running + 31) >> 5) - flushed;
-        if (flushed == 0) first_word = stage[0];
+        if (flushed == 0) first_word = s_win[wbase];
         count_ff(nw, running);
-        for (uint32_t w = lane; w < nw + 1; w += 32) scr[flushed + w] = stage[w];
+        for (uint32_t w = lane; w < nw + 1; w += 32) scr[flushed + w] = s_win[wbase + w];
         uint32_t f[8];
         if (__any_sync(0xffffffffu, (acc0 | acc1) != 0u)) {
 #pragma unroll
@@ -366,14 +361,14 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         uint32_t tail_bits = 0;
         if (lane == 0 && running) {
             const uint32_t eb = running >= 8u ? running - 8u : 0u;
-            const uint32_t w = (eb >> 5) - flushed, sh = eb & 31;
-            const unsigned long long two = ((unsigned long long)stage[w] << 32) | stage[w + 1];
+            const uint32_t w = wbase + (eb >> 5) - flushed, sh = eb & 31;
+            const unsigned long long two = ((unsigned long long)s_win[w] << 32) | s_win[w + 1];
             const uint32_t nbv = running >= 8u ? 8u : running;
             const uint32_t last = (uint32_t)(two >> (64 - nbv - sh)) & ((1u << nbv) - 1u);
             tail_bits = min(nbv, (uint32_t)(__ffs(~last) - 1));
         }
         __syncwarp();
-        for (uint32_t w = lane; w < nw + 3; w += 32) stage[w] = 0;      // window clean for the next tile
+        for (uint32_t w = lane; w < nw + 3; w += 32) s_win[wbase + w] = 0;     // window clean for the next tile
         if (lane == 0) {
             // counters are indexed by the tile's absolute start offset r = (8 - s) & 7
             pb.ff[tile] = make_uint4(f[0] | (f[7] << 16), f[6] | (f[5] << 16), f[4] | (f[3] << 16),
@@ -408,13 +403,13 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             }
             const uint32_t ex = inclL - L_l;
             const uint32_t on_prev = __shfl_up_sync(0xffffffffu, on_l, 1);
-            uint32_t tot[8];
+            uint32_t tot8[8];
 #pragma unroll
             for (uint32_t R = 0; R < 8; R++) {                          // R = the group's absolute start offset mod 8
                 const uint32_t r = (R + ex) & 7u;
                 uint32_t c = have ? ff_select(f_l, r) : 0u;
                 if (have && lane > 0) c += span_ff(on_prev, on_l, r);
-                tot[R] = __reduce_add_sync(0xffffffffu, c);
+                tot8[R] = __reduce_add_sync(0xffffffffu, c);
             }
             const uint32_t Lg = __shfl_sync(0xffffffffu, inclL, 31);
             const uint32_t head = __shfl_sync(0xffffffffu, on_l, 0) & 0xffu;
@@ -422,8 +417,8 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             if (lane == 0) {
                 pb.Lg[grp] = Lg;
                 pb.onesg[grp] = head | (tail << 8);
-                pb.ffg[2 * grp] = make_uint4(tot[0], tot[1], tot[2], tot[3]);
-                pb.ffg[2 * grp + 1] = make_uint4(tot[4], tot[5], tot[6], tot[7]);
+                pb.ffg[2 * grp] = make_uint4(tot8[0], tot8[1], tot8[2], tot8[3]);
+                pb.ffg[2 * grp + 1] = make_uint4(tot8[4], tot8[5], tot8[6], tot8[7]);
                 __threadfence();
                 arrived = atomicAdd(&st->done_a, 1u);
             }
@@ -433,55 +428,68 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         __threadfence();
 
         // ---- the last group of the pass: scan the group records into prefixes and the exact size
+        // (lane = group, 128 groups per trip with all their loads in flight together)
 #ifdef ICB_TIMING
         if (lane == 0) st->dbg_t[dbg_pass][1] = gtime();
 #endif
         {
             const int n_g = p.ngroups;
-            const int chunk = (n_g + 31) / 32;
-            const int lo = min(n_g, lane * chunk), hi = min(n_g, lo + chunk);
-            unsigned long long sum = 0;
-            for (int i = lo; i < hi; i++) sum += (unsigned long long)__ldcg(pb.Lg + i);
-            unsigned long long incl = sum;
+            unsigned long long base_bits = 0;
+            uint32_t base_ff = 0, carry_on = 0;
+            for (int b0 = 0; b0 < n_g; b0 += 128) {
+                uint32_t Lr[4], onr[4];
+                uint4 fa[4], fb[4];
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += t;
-            }
-            unsigned long long run = incl - sum;
-            const unsigned long long total_bits = __shfl_sync(0xffffffffu, incl, 31);
-            uint32_t cnt = 0;
-            uint32_t prev_ones = lo > 0 && lo < n_g ? __ldcg(pb.onesg + lo - 1) : 0u;
-            for (int i = lo; i < hi; i++) {
-                const uint32_t Li = __ldcg(pb.Lg + i);
-                const uint4 fa = __ldcg(pb.ffg + 2 * i), fb = __ldcg(pb.ffg + 2 * i + 1);
-                const uint32_t on = __ldcg(pb.onesg + i);
-                const uint32_t r = (uint32_t)run & 7u;
-                const uint32_t f4[8] = {fa.x, fa.y, fa.z, fa.w, fb.x, fb.y, fb.z, fb.w};
-                uint32_t c = 0;
+                for (int u = 0; u < 4; u++) {
+                    const int g = b0 + 32 * u + lane;
+                    const bool hv = g < n_g;
+                    Lr[u] = hv ? __ldcg(pb.Lg + g) : 0u;
+                    onr[u] = hv ? __ldcg(pb.onesg + g) : 0u;
+                    fa[u] = hv ? __ldcg(pb.ffg + 2 * g) : make_uint4(0, 0, 0, 0);
+                    fb[u] = hv ? __ldcg(pb.ffg + 2 * g + 1) : make_uint4(0, 0, 0, 0);
+                }
 #pragma unroll
-                for (uint32_t k = 0; k < 8; k++) c = r == k ? f4[k] : c;
-                pb.Pg[i] = run;
-                pb.Fg[i] = cnt;                                         // chunk-local for now
-                cnt += c + (i > 0 ? span_ff(prev_ones, on, r) : 0u);
-                prev_ones = on;
-                run += Li;
-            }
-            if (hi == n_g && lo < n_g) {                                // jchuff.c flush_bits: last byte padded with 1s
-                const uint32_t rem = (uint32_t)run & 7u;
-                if (rem && (prev_ones >> 8) >= rem) cnt++;
-            }
-            uint32_t inclc = cnt;
+                for (int u = 0; u < 4; u++) {
+                    const int g0 = b0 + 32 * u;
+                    if (g0 >= n_g) break;
+                    const int g = g0 + lane;
+                    const bool hv = g < n_g;
+                    uint32_t incl = Lr[u];
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t t = __shfl_up_sync(0xffffffffu, inclc, o);
-                if (lane >= o) inclc += t;
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+                        if (lane >= o) incl += t;
+                    }
+                    const unsigned long long P = base_bits + (incl - Lr[u]);
+                    const uint32_t r = (uint32_t)P & 7u;
+                    uint32_t on_prev = __shfl_up_sync(0xffffffffu, onr[u], 1);
+                    if (lane == 0) on_prev = carry_on;
+                    const uint4 fsel = (r & 4u) ? fb[u] : fa[u];
+                    const uint32_t f2a = (r & 2u) ? fsel.z : fsel.x, f2b = (r & 2u) ? fsel.w : fsel.y;
+                    uint32_t c = (r & 1u) ? f2b : f2a;
+                    if (g > 0) c += span_ff(on_prev, onr[u], r);
+                    if (!hv) c = 0;
+                    uint32_t inclc = c;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) {
+                        const uint32_t t = __shfl_up_sync(0xffffffffu, inclc, o);
+                        if (lane >= o) inclc += t;
+                    }
+                    if (hv) {
+                        pb.Pg[g] = P;
+                        pb.Fg[g] = base_ff + inclc - c;
+                    }
+                    const int nvalid = min(32, n_g - g0);
+                    carry_on = __shfl_sync(0xffffffffu, onr[u], nvalid - 1);
+                    base_bits += __shfl_sync(0xffffffffu, incl, 31);
+                    base_ff += __shfl_sync(0xffffffffu, inclc, 31);
+                }
             }
-            const uint32_t basef = inclc - cnt;
-            for (int i = lo; i < hi; i++) pb.Fg[i] += basef;
-            if (lane == 31) {
-                st->total_bits = total_bits;
-                st->ff_total = inclc;
+            const uint32_t rem = (uint32_t)base_bits & 7u;              // jchuff.c flush_bits: last byte padded with 1s
+            if (rem && (carry_on >> 8) >= rem) base_ff++;
+            if (lane == 0) {
+                st->total_bits = base_bits;
+                st->ff_total = base_ff;
             }
             __threadfence();
             __syncwarp();
@@ -489,7 +497,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
 #ifdef ICB_TIMING
         if (lane == 0) st->dbg_t[dbg_pass][2] = gtime();
 #endif
-        device_step(st, 0);         // :176-189 on the exact size, then tables of the next pass
+        device_step(st, 0);         // :176-189 on the exact size, then the table slot of the next pass
 #ifdef ICB_TIMING
         if (lane == 0) st->dbg_t[dbg_pass][3] = gtime();
 #endif
