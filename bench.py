@@ -200,6 +200,25 @@ def run_step(eng, submit, n_images, slots, outs, cursor):
     return results
 
 
+def run_step_threads(eng, submit, n_images, slots, outs, cursor, threads):
+    """The same batch driven by `threads` caller threads (the reference's pool threads each call the
+    seam, CompressionBatch.java:68-88); every thread keeps slots/threads fits in flight."""
+    if threads <= 1:
+        return run_step(eng, submit, n_images, slots, outs, cursor)
+    per, sl = n_images // threads, max(1, slots // threads)
+    res = [None] * threads
+
+    def work(t):
+        res[t] = run_step(eng, submit, per, sl, outs[t * sl:(t + 1) * sl], cursor + t * per)
+
+    ts = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join()
+    return [r for part in res for r in part]
+
+
 def timed_region(eng, dist, local, steps, step_fn):
     barrier(dist)
     eng.mark(0, 0)
@@ -254,20 +273,21 @@ def run_gpu(args):
         assert (r.status, r.best_q, r.scale) == (rc, rq, rs) and r.data == ref, "GPU result differs from oracle"
         parity = "bit-exact vs oracle on pool[0] (%d bytes, q=%.7f)" % (len(ref), rq)
 
+    T = args.threads
     for s in range(args.warmup):
-        run_step(eng, submit_res, batch, slots, outs, s * batch)
+        run_step_threads(eng, submit_res, batch, slots, outs, s * batch, T)
     k0 = eng.stats()["kernels_launched"]
     sampler = ClockSampler(local)
     sampler.start()
     ms, wall = timed_region(eng, dist, local, args.steps,
-                            lambda s: run_step(eng, submit_res, batch, slots, outs, s * batch))
+                            lambda s: run_step_threads(eng, submit_res, batch, slots, outs, s * batch, T))
     launches = eng.stats()["kernels_launched"] - k0
 
     for s in range(max(1, args.warmup // 2)):
-        run_step(eng, submit_host, batch, slots, outs, s * batch)
+        run_step_threads(eng, submit_host, batch, slots, outs, s * batch, T)
     st0 = eng.stats()
     ms_e2e, wall_e2e = timed_region(eng, dist, local, args.steps,
-                                    lambda s: run_step(eng, submit_host, batch, slots, outs, s * batch))
+                                    lambda s: run_step_threads(eng, submit_host, batch, slots, outs, s * batch, T))
     clocks = sampler.stop()
     st1 = eng.stats()
     h2d_step = (st1["h2d_bytes"] - st0["h2d_bytes"]) / args.steps
@@ -324,6 +344,7 @@ def run_gpu(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int32",
             "data": "synthetic",
             "config": {"workload": desc, "images_per_gpu_per_step": batch, "slots_per_gpu": slots,
+                       "caller_threads": T,
                        "l2": f"pool of {POOL} distinct {w}x{h} images per GPU ({POOL * w * h * 3 >> 20} MiB) > 126 MB L2",
                        "parallelism": f"images sharded over {world} GPU(s), no collective", "parity_check": parity},
             "clocks": clocks,
@@ -346,20 +367,172 @@ def run_gpu(args):
     return 0
 
 
+# ---------------------------------------------------------------- other BASELINE configs (not the headline)
+def run_gpu_png(args):
+    """BASELINE configs[2]: 4K / 8K PNG pixels (RGBA8) into the 1920x1920 box
+    (core/ImageCompressionPng.java:49-66 -> tools/ImageTools.java:7-26).  The PNG deflate stays
+    on the host and is not timed.  MP/s counts SOURCE pixels."""
+    rank, local, world, dist = dist_setup(args.gpus)
+    import image_compression_b200 as pkg
+    from image_compression_b200 import synth
+    w, h = (3840, 2160) if args.workload == "png4k" else (7680, 4320)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak_gbs = float(peaks.get("hbm_gbs", 6650.0))
+    slots, batch = args.slots, args.batch
+    eng = pkg.Engine(devices=[local], slots_per_gpu=slots)
+    dw, dh, _ = pkg.png_target_dims(w, h, 1920, 1920)
+    npool = 4 if w > 4000 else 8                       # 4 x 133 MB / 8 x 33 MB > L2
+    pool = [synth.natural_image(2000 + 10 * rank + i, w, h, channels=4) for i in range(npool)]
+    resident = [eng.upload_image(p, 0) for p in pool]
+    pinned = []
+    for p in pool:
+        a = eng.alloc_pinned((h, w, 4))
+        a[...] = p
+        pinned.append(a)
+    outs = [eng.alloc_pinned((dh, dw, 4)) for _ in range(slots)]
+
+    def step(host):
+        inflight = []
+        for i in range(batch):
+            if len(inflight) == slots:
+                eng.wait(inflight.pop(0))
+            if host:
+                eng.resize_to_into(pinned[i % npool], outs[i % slots])
+            else:
+                inflight.append(eng.submit_resize_image(resident[i % npool], dw, dh, outs[i % slots]))
+        while inflight:
+            eng.wait(inflight.pop(0))
+
+    for _ in range(args.warmup):
+        step(False)
+    k0 = eng.stats()["kernels_launched"]
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms, _ = timed_region(eng, dist, local, args.steps, lambda s: step(False))
+    launches = eng.stats()["kernels_launched"] - k0
+    step(True)
+    st0 = eng.stats()
+    ms_e2e, _ = timed_region(eng, dist, local, args.steps, lambda s: step(True))
+    clocks = sampler.stop()
+    st1 = eng.stats()
+    n_img = batch * args.steps
+    mpx = w * h / 1e6
+    ips = n_img * world / (ms * 1e-3)
+    ips_e2e = n_img * world / (ms_e2e * 1e-3)
+    # resident timing includes the D2H of the 8 MB result; the kernel alone is bounded by the
+    # source bytes the taps touch (scale .5: all of them; .25: 2x2 of every 4x4) + destination
+    touched = (w * h * 4 if w < 4000 else w * h) + dw * dh * 4
+    if rank == 0:
+        print(json.dumps({
+            "metric": "megapixels_per_s", "value": ips * mpx, "unit": "MP/s", "images_per_s": ips, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+            "config": {"workload": f"BASELINE configs[2]: {w}x{h} RGBA8 PNG pixels -> {dw}x{dh} (1920x1920 box)",
+                       "images_per_gpu_per_step": batch, "slots_per_gpu": slots,
+                       "l2": f"pool of {npool} distinct images ({npool * w * h * 4 >> 20} MiB) > 126 MB L2",
+                       "note": "resident value includes the D2H of each resized image"},
+            "clocks": clocks,
+            "e2e": {"value": ips_e2e * mpx, "unit": "MP/s", "images_per_s": ips_e2e,
+                    "h2d_bytes_per_step": (st1["h2d_bytes"] - st0["h2d_bytes"]) / args.steps,
+                    "d2h_bytes_per_step": (st1["d2h_bytes"] - st0["d2h_bytes"]) / args.steps},
+            "gpu_launches": int(launches),
+            "roofline": {"kernel": "k_resize", "bound": "hbm", "achieved": touched * ips / world / 1e9,
+                         "peak": peak_gbs, "unit": "GB/s", "frac": touched * ips / world / 1e9 / peak_gbs,
+                         "traffic": None, "algorithmic_bytes_per_launch": touched,
+                         "note": "pipeline rate incl. D2H, not the kernel alone"},
+            "cpu_baseline": None}), flush=True)
+    for im in resident:
+        eng.free_image(im)
+    eng.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+def run_gpu_latency(args):
+    """BASELINE configs[4]: ONE 100 MP source (decoded 5774x4330 after the s=2 subsampling of
+    core/ImageCompression.java:140-153), 256 KB target, -q 1.0 = the full 7-level sweep and the
+    scale loop.  Reports latency (ms per image), lower is better."""
+    import image_compression_b200 as pkg
+    from image_compression_b200 import synth
+    w, h, target, q = 5774, 4330, 262144, 1.0
+    eng = pkg.Engine(devices=[0], slots_per_gpu=2, max_w=w, max_h=h)
+    img = synth.natural_image(200, w, h)
+    res = eng.upload_image(img, 0)
+    pin = eng.alloc_pinned((h, w, 3))
+    pin[...] = img
+    out = eng.alloc_pinned((target + 16,))
+    r = None
+    for _ in range(args.warmup):
+        r = eng.wait(eng.submit_jpg_fit_image(res, q, target, out))
+    k0 = eng.stats()["kernels_launched"]
+    sampler = ClockSampler(0)
+    sampler.start()
+    eng.mark(0, 0)
+    for _ in range(args.steps):
+        r = eng.wait(eng.submit_jpg_fit_image(res, q, target, out))
+    eng.mark(0, 1)
+    ms = eng.elapsed_ms(0) / args.steps
+    launches = eng.stats()["kernels_launched"] - k0
+    st0 = eng.stats()
+    eng.mark(0, 0)
+    for _ in range(args.steps):
+        eng.wait(eng.submit_jpg_fit(pin, q, target, out))
+    eng.mark(0, 1)
+    ms_e2e = eng.elapsed_ms(0) / args.steps
+    st1 = eng.stats()
+    clocks = sampler.stop()
+    cpu = None
+    if not args.no_cpu:
+        from oracle import oracle as O
+        O.lib()
+        t0 = time.perf_counter()
+        rc, ref, rq, rs, _, ne = O.jpg_fit(img, q, target)
+        dt = time.perf_counter() - t0
+        assert (r.status, r.best_q, r.scale, r.out_len) == (rc, rq, rs, len(ref)), "differs from oracle"
+        cpu = {"value": dt * 1e3, "unit": "ms", "cores": 1, "kind": "port",
+               "sample": f"the same image once, 1 thread, {ne} full encodes + resizes (oracle port)"}
+    print(json.dumps({
+        "metric": "latency_ms_per_image", "value": ms, "unit": "ms", "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
+        "dtype": "int32", "data": "synthetic",
+        "config": {"workload": "BASELINE configs[4]: one 100MP source decoded 5774x4330, -t 262144 -q 1.0",
+                   "result": {"status": r.status, "best_q": r.best_q, "scale": r.scale, "bytes": r.out_len,
+                              "entropy_passes": r.n_passes}},
+        "clocks": clocks,
+        "e2e": {"value": ms_e2e, "unit": "ms", "h2d_bytes_per_step": (st1["h2d_bytes"] - st0["h2d_bytes"]) / args.steps,
+                "d2h_bytes_per_step": (st1["d2h_bytes"] - st0["d2h_bytes"]) / args.steps},
+        "gpu_launches": int(launches), "roofline": None, "cpu_baseline": cpu}), flush=True)
+    eng.free_image(res)
+    eng.close()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="cfg1", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="cfg1", choices=sorted(WORKLOADS) + ["png4k", "png8k", "cfg5"])
     ap.add_argument("--batch", type=int, default=64, help="images per GPU per step")
     ap.add_argument("--slots", type=int, default=6, help="stream work-queue slots per GPU")
+    ap.add_argument("--threads", type=int, default=1, help="caller threads per GPU (each drives slots/threads)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-check", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
+        if args.workload not in WORKLOADS:
+            args.workload = "cfg1"
         return run_reference(args)
+    if args.workload in ("png4k", "png8k"):
+        return run_gpu_png(args)
+    if args.workload == "cfg5":
+        return run_gpu_latency(args)
     return run_gpu(args)
 
 

@@ -346,6 +346,17 @@ class Engine:
             raise self._err(rc)
         return dst
 
+    def resize_to_into(self, image: np.ndarray, dst: np.ndarray, fmt: Optional[int] = None) -> np.ndarray:
+        """Same, into a caller-owned (e.g. pinned) destination of shape (dh, dw, c)."""
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        if dst.dtype != np.uint8 or dst.ndim != 3 or dst.shape[2] != image.shape[2]:
+            raise ValueError("dst must be uint8 (dh, dw, c)")
+        rc = self._L.icb_resize_bilinear(self._h, image.ctypes.data, w, h, pitch, fmt, dst.ctypes.data,
+                                         dst.shape[1], dst.shape[0], dst.strides[0])
+        if rc:
+            raise self._err(rc)
+        return dst
+
     # ---- core/ImageCompressionPng.java:37-75 (PNG file write stays with the caller) ----
     def compress_png_with_target_size(self, original_image: np.ndarray, output_file, params: CompressionParams,
                                       fmt: Optional[int] = None):

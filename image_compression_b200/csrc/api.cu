@@ -11,9 +11,11 @@
 #include <atomic>
 #include <condition_variable>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/imgcomp_b200.h"
@@ -118,6 +120,30 @@ int fail(icb_handle *h, int code, const char *what, cudaError_t e = cudaSuccess)
         if (e_ != cudaSuccess) return fail(h, ICB_ERR_CUDA, #call, e_);       \
     } while (0)
 
+// Launch on `st`; with pdl the kernel may start before its predecessor on the stream has finished
+// (programmatic stream serialization) -- it calls griddepcontrol.wait before touching its results.
+bool pdl_enabled()
+{
+    static const bool on = [] { const char *e = getenv("ICB_PDL"); return !(e && e[0] == '0'); }();
+    return on;
+}
+
+template <typename... KArgs, typename... Args>
+cudaError_t launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool pdl, Args &&...args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = (pdl && pdl_enabled()) ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
+}
+
 inline int bpp_of(int fmt) { return (fmt == ICB_FMT_RGBA8 || fmt == ICB_FMT_ABGR8) ? 4 : 3; }
 inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 // device pitch: 16-byte multiple (TMA global stride) and at least one TMA box wide
@@ -175,8 +201,10 @@ int setup_device(icb_handle *h, DeviceCtx &d)
         derive(dc_bits[t], dc_vals, dc_enc[t], 16);
         derive(ac_bits[t], ac_vals[t], ac_enc[t], 256);
     }
-    CK(cudaMemcpyToSymbol(c_dc_enc, dc_enc, sizeof(dc_enc)));
-    CK(cudaMemcpyToSymbol(c_ac_enc, ac_enc, sizeof(ac_enc)));
+    unsigned huf[HUF_WORDS];
+    memcpy(huf, ac_enc, sizeof(ac_enc));
+    memcpy(huf + 512, dc_enc, sizeof(dc_enc));
+    CK(cudaMemcpyToSymbol(g_huf, huf, sizeof(huf)));
     unsigned char hdr[HEADER_BYTES + 16];
     build_header_template(hdr, dc_bits, ac_bits, ac_vals);
     CK(cudaMemcpyToSymbol(c_hdr, hdr, HEADER_BYTES));
@@ -272,6 +300,8 @@ int max_search_iters(float init_q)
 int pass_grid(int ntiles, int sms)
 {
     const int need = (ntiles + ENT_WARPS - 1) / ENT_WARPS;
+    static const int forced = [] { const char *e = getenv("ICB_PASS_CPS"); return e ? atoi(e) : 0; }();
+    if (forced > 0) return std::min(need, sms * forced);     // tuning knob: CTAs per SM of the pass
     if (need <= sms * 4) return need;
     int best_grid = sms * 4;
     double best_eff = 0.0;
@@ -317,18 +347,20 @@ int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, 
         ep.buf[b].onesg = reinterpret_cast<unsigned int *>(base);       base += c * 4;
         ep.buf[b].Fg = reinterpret_cast<unsigned int *>(base);
     }
-    k_begin<<<1, 32, 0, s->stream>>>(s->d_state, mode, q, target, h->table_mode, h->jfif_minor, ep.grp_cnt, ngroups);
-    k_entropy_prepare<<<nctas, ENT_THREADS, 0, s->stream>>>(ep);
-    h->kernels += 2;
+    BeginArgs ba;
+    ba.mode = mode; ba.q = q; ba.target = target; ba.table_mode = h->table_mode; ba.jfif_minor = h->jfif_minor;
+    CK(launch(k_entropy_prepare, dim3(nctas), dim3(ENT_THREADS), 0, s->stream, true, ep, ba));
+    h->kernels += 1;
     const int pgrid = pass_grid(g.ntiles, h->devs[s->devi].sms);
     for (int i = 0; i < npasses; i++) {
         if (pass_ev) cudaEventRecord(pass_ev[2 * i], s->stream);
-        k_entropy_pass<<<pgrid, ENT_THREADS, 0, s->stream>>>(ep);
+        CK(launch(k_entropy_pass, dim3(pgrid), dim3(ENT_THREADS), 0, s->stream, pass_ev == nullptr, ep));
         if (pass_ev) cudaEventRecord(pass_ev[2 * i + 1], s->stream);
         h->kernels += 1;
     }
     if (emit) {
-        k_entropy_emit<<<nctas, ENT_THREADS, 0, s->stream>>>(ep, s->d_out, dev_cap, g.w, g.h);
+        CK(launch(k_entropy_emit, dim3(nctas), dim3(ENT_THREADS), 0, s->stream, pass_ev == nullptr, ep, s->d_out,
+                  dev_cap, g.w, g.h));
         h->kernels += 1;
     }
     CK(cudaGetLastError());

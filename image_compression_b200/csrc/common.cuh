@@ -11,6 +11,18 @@
 
 namespace icb {
 
+// ---- programmatic dependent launch (sm_90+): the kernels of one fit form a chain on one stream;
+// each lets its successor start early (launch latency and the successor's table set-up overlap
+// the predecessor's tail) and waits for its predecessor's results only where it first needs them
+__device__ __forceinline__ void pdl_launch_dependents()
+{
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait()
+{
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // ---- geometry (IJG jcmaster.c initial_setup, 3 components 2x2,1x1,1x1) ----
 struct Geom {
     int w, h;
@@ -88,7 +100,6 @@ struct FitState {
     // with the tables of both possible next midpoints ((tsel+1)%3: this pass fits, (tsel+2)%3: it
     // does not), so the bisection step at the end of the pass only flips tsel
     QTables tab[3];
-    unsigned short thr[2][64];      // survivor thresholds (4 q at the highest quality of the job), zigzag order
     unsigned char best_qtab[2][64]; // tables of the best pass so far (header of the final stream)
     // pass scratch
     unsigned int done_a;            // finished CTAs of k_entropy_pass
@@ -150,8 +161,10 @@ __constant__ unsigned char c_ac_vals[2][162] = {
      0xf9, 0xfa}};
 
 // Derived encode tables (jchuff.c jpeg_make_c_derived_tbl), filled by the host at
-// init: entry = (code << 8) | length.  [table][symbol]
-__constant__ unsigned int c_dc_enc[2][16];
-__constant__ unsigned int c_ac_enc[2][256];
+// init: entry = (code << 8) | length.  AC: table * 256 + symbol;  DC: 512 + table * 16 + size.
+// Global memory, not __constant__: every CTA of the entropy pass copies the table into shared
+// memory with one coalesced load per thread (an indexed constant load replays 32 times per warp).
+constexpr int HUF_WORDS = 512 + 32;
+__device__ unsigned int g_huf[HUF_WORDS];
 
 }  // namespace icb

@@ -7,7 +7,7 @@
 // lo = 0, hi = initialQuality, mid = (lo + hi) / 2.0f, `mid < 0.01f` break before
 // encoding, fit -> best = lo = mid else hi = mid, `(hi - lo) < 0.01f` break after.
 // It runs inside the last CTA of k_entropy_pass (the exact stuffed size of the
-// pass is known there) and once in k_begin, and builds the quantisation tables of
+// pass is known there) and once in begin_job (k_entropy_prepare), and builds the quantisation tables of
 // the coming pass (a2.1: JDK JPEG.convertToLinearQuality +
 // JPEGQTable.getScaledInstance in float32, or the IJG integer formula under the
 // alternative profile).  Each pass keeps its bit stream in the scratch buffer that
@@ -152,46 +152,42 @@ __device__ void device_step(FitState *st, int first)
     __syncwarp();
 }
 
-__global__ void __launch_bounds__(32) k_begin(FitState *st, int mode, float q, long long target, int table_mode,
-                                              int jfif_minor, unsigned int *grp_cnt, int ngroups)
+// Called by all 32 lanes of ONE warp of k_entropy_prepare: the state a job starts from
+// (:160-162), the first bisection step and the tables of the first pass.
+__device__ void begin_job(FitState *st, const BeginArgs &b, unsigned int *grp_cnt, int ngroups)
 {
-    for (int i = threadIdx.x; i < ngroups; i += 32) grp_cnt[i] = 0;
-    if (threadIdx.x == 0) {
+    const int lane = threadIdx.x & 31;
+    for (int i = lane; i < ngroups; i += 32) grp_cnt[i] = 0;
+    if (lane == 0) {
         st->lo = 0.0f;
-        st->hi = q;
+        st->hi = b.q;
         st->best = -1.0f;
-        st->cur_q = q;
+        st->cur_q = b.q;
         st->iter = 0;
         st->done = 0;
         st->cur_valid = 0;
-        st->mode = mode;
+        st->mode = b.mode;
         st->cur_buf = 0;
         st->best_buf = 0;
         st->tsel = 0;
         st->n_trace = 0;
-        st->table_mode = table_mode;
-        st->jfif_minor = jfif_minor;
+        st->table_mode = b.table_mode;
+        st->jfif_minor = b.jfif_minor;
         st->passes = 0;
-        st->target = target;
+        st->target = b.target;
         st->cur_size = 0;
         st->best_size = 0;
-    }
-    // survivor thresholds for k_entropy_prepare: a coefficient is non-zero at quality q iff
-    // |x| >= 4 * table(q), and table(q) never grows with q, so the tables of the highest
-    // quality this job can reach (q itself: every midpoint is below hi <= q) bound them all
-    for (int t = threadIdx.x; t < 128; t += 32) {
-        const int tb = t >> 6, k = t & 63;
-        const int nat = c_zigzag[k];
-        const int qv = scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], q, table_mode);
-        st->thr[tb][k] = (unsigned short)(qv << 2);
     }
     __threadfence();
     __syncwarp();
     device_step(st, 1);
-    if (st->cur_valid) {
-        const float q0 = st->cur_q;
-        for (int t = threadIdx.x; t < 128; t += 32) table_entry(&st->tab[0], t, q0, table_mode);
-    }
+    int go = 0;
+    float q0 = 0.0f;
+    if (lane == 0) { go = st->cur_valid; q0 = st->cur_q; }
+    go = __shfl_sync(0xffffffffu, go, 0);
+    q0 = __shfl_sync(0xffffffffu, q0, 0);
+    if (go)
+        for (int t = lane; t < 128; t += 32) table_entry(&st->tab[0], t, q0, b.table_mode);
 }
 
 }  // namespace icb

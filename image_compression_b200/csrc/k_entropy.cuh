@@ -76,9 +76,19 @@ __device__ __forceinline__ PassBufs pick_buf(const EntParams &p, int i)
     return b;
 }
 
+// what a fit job starts from (core/ImageCompressionJpg.java:158-162 or one explicit quality)
+struct BeginArgs {
+    int mode;                       // FitMode
+    float q;                        // initial quality (search) or the quality to encode at (single)
+    long long target;
+    int table_mode, jfif_minor;
+};
+
 // a2.1 / :158-200 -- defined in k_control.cuh
 __device__ void device_step(FitState *st, int first);
 __device__ __forceinline__ void precompute_next_tables(FitState *st, int tid);
+__device__ __forceinline__ int scaled_qval(int base, float q, int table_mode);
+__device__ void begin_job(FitState *st, const BeginArgs &b, unsigned int *grp_cnt, int ngroups);
 
 // ---- survivor entries ------------------------------------------------------------
 // AC: val(16) | table << 17 | zigzag pos(6) << 18
@@ -105,13 +115,24 @@ __device__ __forceinline__ uint32_t span_ff(uint32_t ones_prev, uint32_t ones_cu
     return (r != 0u && (ones_prev >> 8) >= r && (ones_cur & 0xffu) >= 8u - r) ? 1u : 0u;
 }
 
-__global__ void __launch_bounds__(ENT_THREADS) k_entropy_prepare(const EntParams p)
+__global__ void __launch_bounds__(ENT_THREADS) k_entropy_prepare(const EntParams p, const BeginArgs ba)
 {
     __shared__ __align__(16) unsigned short s_thr[2][64];
-    const FitState *st = p.st;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid < 128) s_thr[tid >> 6][tid & 63] = st->thr[tid >> 6][tid & 63];
+    pdl_launch_dependents();
+    // survivor thresholds: a coefficient is non-zero at quality q iff |x| >= 4 * table(q), and
+    // table(q) never grows with q, so the tables of the highest quality this job can reach (ba.q:
+    // every midpoint lies below hi <= q) bound them all.  Zigzag order, computed by every CTA.
+    if (tid < 128) {
+        const int tb = tid >> 6, k = tid & 63;
+        const int nat = c_zigzag[k];
+        s_thr[tb][k] = (unsigned short)(scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], ba.q, ba.table_mode) << 2);
+    }
+    // the job's search state and first tables (consumed by the pass kernels that follow)
+    // (nothing of the previous kernel of the stream, the transform, is touched by this)
+    if (blockIdx.x == 0 && warp == ENT_WARPS - 1) begin_job(p.st, ba, p.grp_cnt, p.ngroups);
     __syncthreads();
+    pdl_wait();                     // the coefficients are complete and visible from here on
     const int tile = blockIdx.x * ENT_WARPS + warp;
     if (tile >= p.ntiles) return;
     const int g = lane >> 3, j = lane & 7;
@@ -194,19 +215,20 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
     __shared__ uint32_t s_win[ENT_WARPS * ENT_WSTRIDE];
 
     FitState *st = p.st;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pdl_launch_dependents();
+    // set-up that does not depend on the previous pass: runs while that pass drains
+    for (int i = tid; i < HUF_WORDS; i += ENT_THREADS) s_huf[i] = __ldg(g_huf + i);
+    const uint32_t wbase = warp * ENT_WSTRIDE;
+    for (int i = lane; i < ENT_WSTRIDE; i += 32) s_win[wbase + i] = 0;
+    pdl_wait();                     // the previous pass ran its bisection step: st is final
     if (!st->cur_valid) return;
     const PassBufs pb = pick_buf(p, st->cur_buf);
 #ifdef ICB_TIMING
     const int dbg_pass = (st->iter - 1) & 7;
     if (blockIdx.x == 0 && threadIdx.x == 0) st->dbg_t[dbg_pass][0] = gtime();
 #endif
-
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int i = tid; i < 512; i += ENT_THREADS) s_huf[i] = c_ac_enc[i >> 8][i & 255];
-    if (tid < 32) s_huf[512 + tid] = c_dc_enc[tid >> 4][tid & 15];
     if (tid < 128) s_qt[tid] = st->tab[st->tsel].rh[tid];
-    const uint32_t wbase = warp * ENT_WSTRIDE;
-    for (int i = lane; i < ENT_WSTRIDE; i += 32) s_win[wbase + i] = 0;
     if (blockIdx.x == 0) precompute_next_tables(st, tid);      // off the critical path of the pass
     __syncthreads();
 
@@ -563,6 +585,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
                                                               int img_w, int img_h)
 {
     const FitState *st = p.st;
+    pdl_wait();
     if (st->best_size <= 0 || out == nullptr) return;
     const PassBufs pb = pick_buf(p, st->best_buf);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;

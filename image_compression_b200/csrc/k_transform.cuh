@@ -182,6 +182,7 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
     uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + XF_STAGES * TILE_IN_BYTES + TILE_BLOCKS * 256);
 
     const int tid = threadIdx.x;
+    pdl_launch_dependents();        // k_entropy_prepare may set up while this grid drains
     if (tid == 0) {
         for (int s = 0; s < XF_STAGES; s++) mbar_init(&full[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
