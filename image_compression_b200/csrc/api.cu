@@ -319,9 +319,9 @@ int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, 
 {
     const Geom &g = s->geom;
     const int nctas = (g.ntiles + ENT_WARPS - 1) / ENT_WARPS;
-    const int ngroups = (g.ntiles + 31) / 32;
-    const size_t per = round_up(ent_pass_bytes(g.ntiles, ngroups), 256);
-    int rc = ensure(h, s->d_pass, s->pass_cap, 2 * per + (size_t)ngroups * 4 + 256);
+    const int nchunks = nctas;                       // chunk = the 8 tiles one CTA takes per round
+    const size_t per = round_up(ent_pass_bytes(g.ntiles, nchunks), 256);
+    int rc = ensure(h, s->d_pass, s->pass_cap, 2 * per + 256);
     if (rc) return rc;
     rc = ensure(h, s->d_ent, s->ent_cap, ((size_t)g.ntiles * ENT_CAP + (size_t)g.ntiles) * 4 + 256);
     if (rc) return rc;
@@ -330,22 +330,20 @@ int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, 
     ep.st = s->d_state;
     ep.ent = s->d_ent;
     ep.ent_cnt = s->d_ent + (size_t)g.ntiles * ENT_CAP;
-    ep.grp_cnt = reinterpret_cast<unsigned int *>(s->d_pass + 2 * per);
     ep.nblocks = g.nblocks;
     ep.ntiles = g.ntiles;
-    ep.ngroups = ngroups;
+    ep.nchunks = nchunks;
     for (int b = 0; b < 2; b++) {
         unsigned char *base = s->d_pass + (size_t)b * per;
-        const size_t n = (size_t)g.ntiles, c = (size_t)ngroups;
+        const size_t n = (size_t)g.ntiles, c = (size_t)nchunks;
         ep.buf[b].ff = reinterpret_cast<uint4 *>(base);                 base += n * 16;
-        ep.buf[b].ffg = reinterpret_cast<uint4 *>(base);                base += c * 32;
-        ep.buf[b].Pg = reinterpret_cast<unsigned long long *>(base);    base += c * 8;
+        ep.buf[b].crec = reinterpret_cast<uint4 *>(base);               base += c * 32;
+        ep.buf[b].Pc = reinterpret_cast<unsigned long long *>(base);    base += c * 8;
         ep.buf[b].scratch = reinterpret_cast<uint32_t *>(base);         base += n * ENT_SCR_STRIDE * 4;
         ep.buf[b].L = reinterpret_cast<unsigned int *>(base);           base += n * 4;
         ep.buf[b].ones = reinterpret_cast<unsigned int *>(base);        base += n * 4;
-        ep.buf[b].Lg = reinterpret_cast<unsigned int *>(base);          base += c * 4;
-        ep.buf[b].onesg = reinterpret_cast<unsigned int *>(base);       base += c * 4;
-        ep.buf[b].Fg = reinterpret_cast<unsigned int *>(base);
+        ep.buf[b].Fc = reinterpret_cast<unsigned int *>(base);          base += c * 4;
+        ep.buf[b].Fb = reinterpret_cast<unsigned int *>(base);
     }
     BeginArgs ba;
     ba.mode = mode; ba.q = q; ba.target = target; ba.table_mode = h->table_mode; ba.jfif_minor = h->jfif_minor;

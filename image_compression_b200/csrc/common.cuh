@@ -100,7 +100,7 @@ struct FitState {
     // with the tables of both possible next midpoints ((tsel+1)%3: this pass fits, (tsel+2)%3: it
     // does not), so the bisection step at the end of the pass only flips tsel
     QTables tab[3];
-    unsigned char best_qtab[2][64]; // tables of the best pass so far (header of the final stream)
+    unsigned char cand_qtab[2][2][64];  // [ping-pong buffer] tables of the pass whose stream sits in that buffer (DQT payload)
     // pass scratch
     unsigned int done_a;            // finished CTAs of k_entropy_pass
     int pad1, pad2, pad3;
@@ -109,7 +109,8 @@ struct FitState {
     unsigned long long total_bits;  // entropy-coded bits before padding
 };
 
-static_assert(offsetof(FitState, tab) % 8 == 0 && offsetof(FitState, best_qtab) % 4 == 0, "vector copies of the tables");
+static_assert(offsetof(FitState, iter) == 16 && offsetof(FitState, cur_buf) == 32, "k_entropy_pass reads these as int4");
+static_assert(offsetof(FitState, tab) % 8 == 0 && offsetof(FitState, cand_qtab) % 4 == 0, "vector copies of the tables");
 
 // ---- Annex K tables (T.81), natural order; IJG jcparam.c / JDK JPEGQTable ----
 __constant__ unsigned char c_base_lum[64] = {

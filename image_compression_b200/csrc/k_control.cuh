@@ -69,10 +69,10 @@ __device__ __forceinline__ void precompute_next_tables(FitState *st, int tid)
 // Called by all 32 lanes of ONE warp.  Consumes the pass that just ran (if any),
 // decides, and selects the tables of the next one.  Lane 0 reads every control field
 // first and writes them back at the end, so the global accesses pipeline.
-__device__ void device_step(FitState *st, int first)
+__device__ void device_step(FitState *st, int first, unsigned long long tbits, unsigned long long ffs)
 {
     const int lane = threadIdx.x & 31;
-    int go = 0, better = 0, old_sel = 0;
+    int go = 0, better = 0;
     if (lane == 0) {
         float lo = st->lo, hi = st->hi, best = st->best, cur_q = st->cur_q;
         int iter = st->iter, done = st->done, n_trace = st->n_trace, passes = st->passes;
@@ -80,10 +80,7 @@ __device__ void device_step(FitState *st, int first)
         const int cur_valid = st->cur_valid, mode = st->mode;
         const long long target = st->target;
         long long best_size = st->best_size, cur_size = st->cur_size;
-        const unsigned long long tbits = *(volatile unsigned long long *)&st->total_bits;
-        const unsigned long long ffs = *(volatile unsigned long long *)&st->ff_total;
         int fit = 0;
-        old_sel = tsel;
         if (cur_valid) {                                        // consume the pass that just ran
             const long long size = (long long)HEADER_BYTES + (long long)((tbits + 7ull) >> 3) + (long long)ffs + 2;
             cur_size = size;
@@ -140,24 +137,18 @@ __device__ void device_step(FitState *st, int first)
         st->cur_buf = cur_buf; st->best_buf = best_buf; st->cur_valid = go; st->tsel = tsel;
         st->best_size = best_size; st->cur_size = cur_size;
         st->done_a = 0;
-        st->ff_total = 0;
-        st->total_bits = 0;
+        st->ff_total = ffs;
+        st->total_bits = tbits;
     }
-    better = __shfl_sync(0xffffffffu, better, 0);
-    old_sel = __shfl_sync(0xffffffffu, old_sel, 0);
-    if (better)                                                 // tables of the best pass so far: 128 B, one word per lane
-        reinterpret_cast<unsigned int *>(&st->best_qtab[0][0])[lane] =
-            reinterpret_cast<const unsigned int *>(&st->tab[old_sel].qtab[0][0])[lane];
     __threadfence();
     __syncwarp();
 }
 
 // Called by all 32 lanes of ONE warp of k_entropy_prepare: the state a job starts from
 // (:160-162), the first bisection step and the tables of the first pass.
-__device__ void begin_job(FitState *st, const BeginArgs &b, unsigned int *grp_cnt, int ngroups)
+__device__ void begin_job(FitState *st, const BeginArgs &b)
 {
     const int lane = threadIdx.x & 31;
-    for (int i = lane; i < ngroups; i += 32) grp_cnt[i] = 0;
     if (lane == 0) {
         st->lo = 0.0f;
         st->hi = b.q;
@@ -180,7 +171,7 @@ __device__ void begin_job(FitState *st, const BeginArgs &b, unsigned int *grp_cn
     }
     __threadfence();
     __syncwarp();
-    device_step(st, 1);
+    device_step(st, 1, 0ull, 0ull);
     int go = 0;
     float q0 = 0.0f;
     if (lane == 0) { go = st->cur_valid; q0 = st->cur_q; }

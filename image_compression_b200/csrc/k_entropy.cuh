@@ -43,11 +43,11 @@ struct PassBufs {
     unsigned int *L;                // [ntiles] bits per tile
     uint4 *ff;                      // [ntiles] 8 x u16: 0xFF bytes inside the tile per absolute start offset mod 8
     unsigned int *ones;             // [ntiles] leading 1-bits | trailing 1-bits << 8 (each capped at 8)
-    unsigned int *Lg;               // [ngroups] bits per group of 32 tiles
-    uint4 *ffg;                     // [ngroups][2] the same 8 counters (u32) folded over the group's tiles
-    unsigned int *onesg;            // [ngroups]
-    unsigned long long *Pg;         // [ngroups] exclusive bit prefix            (last warp of the pass)
-    unsigned int *Fg;               // [ngroups] exclusive prefix of 0xFF bytes  (last warp of the pass)
+    uint4 *crec;                    // [nchunks][2] chunk record: the same 8 counters folded over the chunk's
+                                    //              tiles | bits, ones, 0, 0      (chunk = the 8 tiles of one CTA round)
+    unsigned long long *Pc;         // [nchunks] exclusive bit prefix            (last CTA of the pass)
+    unsigned int *Fc;               // [nchunks] exclusive prefix of 0xFF bytes, relative to Fb  (last CTA of the pass)
+    unsigned int *Fb;               // [ENT_THREADS] base of Fc for the chunks thread t of the last CTA scanned
 };
 
 struct EntParams {
@@ -55,9 +55,8 @@ struct EntParams {
     FitState *st;
     uint32_t *ent;                  // [ntiles][ENT_CAP] survivor entries
     unsigned int *ent_cnt;          // [ntiles]
-    unsigned int *grp_cnt;          // [ngroups] tiles of the group that finished (self-resetting)
     PassBufs buf[2];                // ping-pong: the best pass so far is never overwritten
-    int nblocks, ntiles, ngroups;
+    int nblocks, ntiles, nchunks;
 };
 
 // select without dynamic indexing of the kernel parameter block (keeps it out of local memory)
@@ -68,11 +67,10 @@ __device__ __forceinline__ PassBufs pick_buf(const EntParams &p, int i)
     b.L = i ? p.buf[1].L : p.buf[0].L;
     b.ff = i ? p.buf[1].ff : p.buf[0].ff;
     b.ones = i ? p.buf[1].ones : p.buf[0].ones;
-    b.Lg = i ? p.buf[1].Lg : p.buf[0].Lg;
-    b.ffg = i ? p.buf[1].ffg : p.buf[0].ffg;
-    b.onesg = i ? p.buf[1].onesg : p.buf[0].onesg;
-    b.Pg = i ? p.buf[1].Pg : p.buf[0].Pg;
-    b.Fg = i ? p.buf[1].Fg : p.buf[0].Fg;
+    b.crec = i ? p.buf[1].crec : p.buf[0].crec;
+    b.Pc = i ? p.buf[1].Pc : p.buf[0].Pc;
+    b.Fc = i ? p.buf[1].Fc : p.buf[0].Fc;
+    b.Fb = i ? p.buf[1].Fb : p.buf[0].Fb;
     return b;
 }
 
@@ -85,10 +83,10 @@ struct BeginArgs {
 };
 
 // a2.1 / :158-200 -- defined in k_control.cuh
-__device__ void device_step(FitState *st, int first);
+__device__ void device_step(FitState *st, int first, unsigned long long tbits, unsigned long long ffs);
 __device__ __forceinline__ void precompute_next_tables(FitState *st, int tid);
 __device__ __forceinline__ int scaled_qval(int base, float q, int table_mode);
-__device__ void begin_job(FitState *st, const BeginArgs &b, unsigned int *grp_cnt, int ngroups);
+__device__ void begin_job(FitState *st, const BeginArgs &b);
 
 // ---- survivor entries ------------------------------------------------------------
 // AC: val(16) | table << 17 | zigzag pos(6) << 18
@@ -130,7 +128,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prepare(const EntParams
     }
     // the job's search state and first tables (consumed by the pass kernels that follow)
     // (nothing of the previous kernel of the stream, the transform, is touched by this)
-    if (blockIdx.x == 0 && warp == ENT_WARPS - 1) begin_job(p.st, ba, p.grp_cnt, p.ngroups);
+    if (blockIdx.x == 0 && warp == ENT_WARPS - 1) begin_job(p.st, ba);
     __syncthreads();
     pdl_wait();                     // the coefficients are complete and visible from here on
     const int tile = blockIdx.x * ENT_WARPS + warp;
@@ -138,22 +136,34 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prepare(const EntParams
     const int g = lane >> 3, j = lane & 7;
     uint32_t *out = p.ent + (size_t)tile * ENT_CAP;
     uint32_t cnt = 0;
-    for (int it = 0; it < ENT_TILE_BLOCKS / 4; it++) {
+    // all loads of the tile first (8 x 16 B per lane in flight), then the compaction: one memory
+    // round trip per tile instead of one per group of 4 blocks
+    constexpr int NIT = ENT_TILE_BLOCKS / 4;
+    uint4 raw_all[NIT];
+    int xp_all[NIT];
+#pragma unroll
+    for (int it = 0; it < NIT; it++) {
         const int b = tile * ENT_TILE_BLOCKS + it * 4 + g;
-        const bool valid = b < p.nblocks;
         const int cidx = b % 6;
-        const uint32_t tb = cidx >= 4 ? 1u : 0u;
         // DC predictor = previous block of the same component in scan order
         int prev = b - 1;
         bool has_prev = true;
         if (cidx == 0) { prev = b - 3; has_prev = b >= 6; }
         else if (cidx >= 4) { prev = b - 6; has_prev = b >= 6; }
-        uint4 raw = make_uint4(0, 0, 0, 0);
-        int xp = 0;
-        if (valid) {
-            raw = __ldg(reinterpret_cast<const uint4 *>(p.coef) + (size_t)b * 8 + j);
-            if (j == 0 && has_prev) xp = (int)__ldg(p.coef + (size_t)prev * 64);
+        raw_all[it] = make_uint4(0, 0, 0, 0);
+        xp_all[it] = 0;
+        if (b < p.nblocks) {
+            raw_all[it] = __ldg(reinterpret_cast<const uint4 *>(p.coef) + (size_t)b * 8 + j);
+            if (j == 0 && has_prev) xp_all[it] = (int)__ldg(p.coef + (size_t)prev * 64);
         }
+    }
+#pragma unroll
+    for (int it = 0; it < NIT; it++) {
+        const int b = tile * ENT_TILE_BLOCKS + it * 4 + g;
+        const bool valid = b < p.nblocks;
+        const uint32_t tb = (b % 6) >= 4 ? 1u : 0u;
+        const uint4 raw = raw_all[it];
+        const int xp = xp_all[it];
         const uint4 tt = *reinterpret_cast<const uint4 *>(&s_thr[tb][8 * j]);
         const uint32_t rw[4] = {raw.x, raw.y, raw.z, raw.w};
         const uint32_t tw[4] = {tt.x, tt.y, tt.z, tt.w};
@@ -213,6 +223,10 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
     __shared__ uint32_t s_huf[512 + 32];            // AC: table * 256 + run * 16 + size;  DC: 512 + table * 16 + size
     __shared__ uint2 s_qt[128];                     // quantiser by key = 2 * pos + table
     __shared__ uint32_t s_win[ENT_WARPS * ENT_WSTRIDE];
+    __shared__ __align__(16) uint32_t s_rec[2][ENT_WARPS][8];   // tile records of one CTA round: ff (4 words), L, ones
+    __shared__ unsigned long long s_scan[ENT_WARPS];
+    __shared__ unsigned long long s_total[2];
+    __shared__ int s_last;
 
     FitState *st = p.st;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -222,25 +236,61 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
     const uint32_t wbase = warp * ENT_WSTRIDE;
     for (int i = lane; i < ENT_WSTRIDE; i += 32) s_win[wbase + i] = 0;
     pdl_wait();                     // the previous pass ran its bisection step: st is final
-    if (!st->cur_valid) return;
-    const PassBufs pb = pick_buf(p, st->cur_buf);
+    // one memory round trip: the control words and this thread's entry of all three table slots
+    const int4 c1 = __ldcg(reinterpret_cast<const int4 *>(&st->iter));         // iter, done, cur_valid, mode
+    const int4 c2 = __ldcg(reinterpret_cast<const int4 *>(&st->cur_buf));      // cur_buf, best_buf, tsel, n_trace
+    uint2 q0 = make_uint2(0, 0), q1 = q0, q2 = q0;
+    if (tid < 128) {
+        q0 = __ldcg(&st->tab[0].rh[tid]);
+        q1 = __ldcg(&st->tab[1].rh[tid]);
+        q2 = __ldcg(&st->tab[2].rh[tid]);
+    }
+    if (!c1.z) return;
+    const PassBufs pb = pick_buf(p, c2.x);
 #ifdef ICB_TIMING
-    const int dbg_pass = (st->iter - 1) & 7;
+    const int dbg_pass = (c1.x - 1) & 7;
     if (blockIdx.x == 0 && threadIdx.x == 0) st->dbg_t[dbg_pass][0] = gtime();
 #endif
-    if (tid < 128) s_qt[tid] = st->tab[st->tsel].rh[tid];
-    if (blockIdx.x == 0) precompute_next_tables(st, tid);      // off the critical path of the pass
+    if (tid < 128) s_qt[tid] = c2.z == 0 ? q0 : (c2.z == 1 ? q1 : q2);
     __syncthreads();
+    // both possible next tables, by the CTA with the least work (the last one has the fewest chunks)
+    if (blockIdx.x == gridDim.x - 1) {
+        precompute_next_tables(st, tid);
+        if (tid < 32)               // the tables this pass codes with, kept beside its stream for the header
+            reinterpret_cast<unsigned int *>(&st->cand_qtab[c2.x][0][0])[tid] =
+                reinterpret_cast<const unsigned int *>(&st->tab[c2.z].qtab[0][0])[tid];
+    }
 
     const uint32_t zrl0 = s_huf[0xF0], zrl1 = s_huf[256 + 0xF0];
     const uint32_t eob0 = s_huf[0], eob1 = s_huf[256];
     const uint32_t lt_mask = (1u << lane) - 1u;
 
-    // persistent warps: tiles are dealt out statically (no shared cursor a late CTA could overrun)
-    for (int tile = blockIdx.x * ENT_WARPS + warp; tile < p.ntiles; tile += gridDim.x * ENT_WARPS) {
+    // persistent CTAs: chunks of 8 consecutive tiles (one per warp) are dealt out statically (no
+    // shared cursor a late CTA could overrun); nobody ever waits for another CTA
+    int round = 0;
+    // a tile's entry count and first 32 entries are fetched one tile ahead (and together: reading
+    // past the count stays inside the tile's ENT_CAP slots and is masked afterwards)
+    uint32_t n_pf = 0, e_pf = 0;
+    {
+        const int t0 = blockIdx.x * ENT_WARPS + warp;
+        if (t0 < p.ntiles) {
+            n_pf = __ldg(p.ent_cnt + t0);
+            e_pf = __ldg(p.ent + (size_t)t0 * ENT_CAP + lane);
+        }
+    }
+    for (int chunk = blockIdx.x; chunk < p.nchunks; chunk += gridDim.x, round++) {
+      const int tile = chunk * ENT_WARPS + warp;
+      const uint32_t n = n_pf, e_first = e_pf;
+      {
+          const int tn = tile + (int)gridDim.x * ENT_WARPS;
+          if (chunk + (int)gridDim.x < p.nchunks && tn < p.ntiles) {
+              n_pf = __ldg(p.ent_cnt + tn);
+              e_pf = __ldg(p.ent + (size_t)tn * ENT_CAP + lane);
+          }
+      }
+      if (tile < p.ntiles) {
         uint32_t *scr = pb.scratch + (size_t)tile * ENT_SCR_STRIDE;
         const uint32_t *ent = p.ent + (size_t)tile * ENT_CAP;
-        const uint32_t n = __ldg(p.ent_cnt + tile);
         uint32_t running = 0;       // bits produced so far (tile-local)
         uint32_t flushed = 0;       // whole words already copied to scratch
         uint32_t acc0 = 0, acc1 = 0;   // 0xFF counters, 4 x 8 bits each: local start bit s = 0..3 | 4..7
@@ -294,7 +344,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             if (w1) atomicOr(&s_win[a + 1], w1);
         };
 
-        uint32_t e_next = (uint32_t)lane < n ? __ldg(ent + lane) : 0u;
+        uint32_t e_next = (uint32_t)lane < n ? e_first : 0u;
         for (uint32_t i0 = 0; i0 < n; i0 += 32) {
             const uint32_t e = e_next;
             {   // next round's entries are in flight while this one is coded
@@ -393,33 +443,32 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         for (uint32_t w = lane; w < nw + 3; w += 32) s_win[wbase + w] = 0;     // window clean for the next tile
         if (lane == 0) {
             // counters are indexed by the tile's absolute start offset r = (8 - s) & 7
-            pb.ff[tile] = make_uint4(f[0] | (f[7] << 16), f[6] | (f[5] << 16), f[4] | (f[3] << 16),
-                                     f[2] | (f[1] << 16));
+            const uint4 fpk = make_uint4(f[0] | (f[7] << 16), f[6] | (f[5] << 16), f[4] | (f[3] << 16),
+                                         f[2] | (f[1] << 16));
             uint32_t head = min(8u, (uint32_t)__clz(~first_word));
             if (running < 8u) head = min(head, running);
+            const uint32_t on = head | (tail_bits << 8);
+            pb.ff[tile] = fpk;                                  // for k_entropy_emit (next kernel: no fence needed)
             pb.L[tile] = running;
-            pb.ones[tile] = head | (tail_bits << 8);
-            __threadfence();
+            pb.ones[tile] = on;
+            *reinterpret_cast<uint4 *>(&s_rec[round & 1][warp][0]) = fpk;
+            s_rec[round & 1][warp][4] = running;
+            s_rec[round & 1][warp][5] = on;
         }
-        __syncwarp();
+      }
+      __syncthreads();                                          // the chunk's tile records are in shared memory
 
-        // ---- the last warp to finish a group of 32 tiles folds it (no waiting anywhere)
-        const int grp = tile >> 5;
-        const int g_first = grp << 5, g_n = min(32, p.ntiles - g_first);
-        uint32_t arrived = 0;
-        if (lane == 0) arrived = atomicAdd(p.grp_cnt + grp, 1u);
-        arrived = __shfl_sync(0xffffffffu, arrived, 0);
-        if (arrived != (uint32_t)(g_n - 1)) continue;
-        if (lane == 0) p.grp_cnt[grp] = 0;                              // ready for the next pass
-        __threadfence();
-        {
+      // ---- warp 0 folds the chunk (the other warps go on with their next tile)
+      if (warp == 0) {
+            const int g_n = min(ENT_WARPS, p.ntiles - chunk * ENT_WARPS);
             const bool have = lane < g_n;
-            const uint32_t L_l = have ? __ldcg(pb.L + g_first + lane) : 0u;
-            const uint4 f_l = have ? __ldcg(pb.ff + g_first + lane) : make_uint4(0, 0, 0, 0);
-            const uint32_t on_l = have ? __ldcg(pb.ones + g_first + lane) : 0u;
+            const uint32_t *rec = &s_rec[round & 1][lane & (ENT_WARPS - 1)][0];
+            const uint4 f_l = have ? *reinterpret_cast<const uint4 *>(rec) : make_uint4(0, 0, 0, 0);
+            const uint32_t L_l = have ? rec[4] : 0u;
+            const uint32_t on_l = have ? rec[5] : 0u;
             uint32_t inclL = L_l;
 #pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
+            for (int o = 1; o < ENT_WARPS; o <<= 1) {
                 const uint32_t t = __shfl_up_sync(0xffffffffu, inclL, o);
                 if (lane >= o) inclL += t;
             }
@@ -427,103 +476,98 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             const uint32_t on_prev = __shfl_up_sync(0xffffffffu, on_l, 1);
             uint32_t tot8[8];
 #pragma unroll
-            for (uint32_t R = 0; R < 8; R++) {                          // R = the group's absolute start offset mod 8
+            for (uint32_t R = 0; R < 8; R++) {                          // R = the chunk's absolute start offset mod 8
                 const uint32_t r = (R + ex) & 7u;
                 uint32_t c = have ? ff_select(f_l, r) : 0u;
                 if (have && lane > 0) c += span_ff(on_prev, on_l, r);
                 tot8[R] = __reduce_add_sync(0xffffffffu, c);
             }
-            const uint32_t Lg = __shfl_sync(0xffffffffu, inclL, 31);
+            const uint32_t Lc = __shfl_sync(0xffffffffu, inclL, g_n - 1);
             const uint32_t head = __shfl_sync(0xffffffffu, on_l, 0) & 0xffu;
             const uint32_t tail = __shfl_sync(0xffffffffu, on_l, g_n - 1) >> 8;
-            if (lane == 0) {
-                pb.Lg[grp] = Lg;
-                pb.onesg[grp] = head | (tail << 8);
-                pb.ffg[2 * grp] = make_uint4(tot8[0], tot8[1], tot8[2], tot8[3]);
-                pb.ffg[2 * grp + 1] = make_uint4(tot8[4], tot8[5], tot8[6], tot8[7]);
-                __threadfence();
-                arrived = atomicAdd(&st->done_a, 1u);
+            if (lane == 0) {                                    // <= 8 x 6656 stuffed bytes per counter: fits 16 bits
+                pb.crec[2 * chunk] = make_uint4(tot8[0] | (tot8[1] << 16), tot8[2] | (tot8[3] << 16),
+                                                tot8[4] | (tot8[5] << 16), tot8[6] | (tot8[7] << 16));
+                pb.crec[2 * chunk + 1] = make_uint4(Lc, head | (tail << 8), 0u, 0u);
             }
-        }
-        arrived = __shfl_sync(0xffffffffu, arrived, 0);
-        if (arrived != (uint32_t)(p.ngroups - 1)) continue;
-        __threadfence();
-
-        // ---- the last group of the pass: scan the group records into prefixes and the exact size
-        // (lane = group, 128 groups per trip with all their loads in flight together)
-#ifdef ICB_TIMING
-        if (lane == 0) st->dbg_t[dbg_pass][1] = gtime();
-#endif
-        {
-            const int n_g = p.ngroups;
-            unsigned long long base_bits = 0;
-            uint32_t base_ff = 0, carry_on = 0;
-            for (int b0 = 0; b0 < n_g; b0 += 128) {
-                uint32_t Lr[4], onr[4];
-                uint4 fa[4], fb[4];
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const int g = b0 + 32 * u + lane;
-                    const bool hv = g < n_g;
-                    Lr[u] = hv ? __ldcg(pb.Lg + g) : 0u;
-                    onr[u] = hv ? __ldcg(pb.onesg + g) : 0u;
-                    fa[u] = hv ? __ldcg(pb.ffg + 2 * g) : make_uint4(0, 0, 0, 0);
-                    fb[u] = hv ? __ldcg(pb.ffg + 2 * g + 1) : make_uint4(0, 0, 0, 0);
-                }
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const int g0 = b0 + 32 * u;
-                    if (g0 >= n_g) break;
-                    const int g = g0 + lane;
-                    const bool hv = g < n_g;
-                    uint32_t incl = Lr[u];
-#pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) {
-                        const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-                        if (lane >= o) incl += t;
-                    }
-                    const unsigned long long P = base_bits + (incl - Lr[u]);
-                    const uint32_t r = (uint32_t)P & 7u;
-                    uint32_t on_prev = __shfl_up_sync(0xffffffffu, onr[u], 1);
-                    if (lane == 0) on_prev = carry_on;
-                    const uint4 fsel = (r & 4u) ? fb[u] : fa[u];
-                    const uint32_t f2a = (r & 2u) ? fsel.z : fsel.x, f2b = (r & 2u) ? fsel.w : fsel.y;
-                    uint32_t c = (r & 1u) ? f2b : f2a;
-                    if (g > 0) c += span_ff(on_prev, onr[u], r);
-                    if (!hv) c = 0;
-                    uint32_t inclc = c;
-#pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) {
-                        const uint32_t t = __shfl_up_sync(0xffffffffu, inclc, o);
-                        if (lane >= o) inclc += t;
-                    }
-                    if (hv) {
-                        pb.Pg[g] = P;
-                        pb.Fg[g] = base_ff + inclc - c;
-                    }
-                    const int nvalid = min(32, n_g - g0);
-                    carry_on = __shfl_sync(0xffffffffu, onr[u], nvalid - 1);
-                    base_bits += __shfl_sync(0xffffffffu, incl, 31);
-                    base_ff += __shfl_sync(0xffffffffu, inclc, 31);
-                }
-            }
-            const uint32_t rem = (uint32_t)base_bits & 7u;              // jchuff.c flush_bits: last byte padded with 1s
-            if (rem && (carry_on >> 8) >= rem) base_ff++;
-            if (lane == 0) {
-                st->total_bits = base_bits;
-                st->ff_total = base_ff;
-            }
-            __threadfence();
-            __syncwarp();
-        }
-#ifdef ICB_TIMING
-        if (lane == 0) st->dbg_t[dbg_pass][2] = gtime();
-#endif
-        device_step(st, 0);         // :176-189 on the exact size, then the table slot of the next pass
-#ifdef ICB_TIMING
-        if (lane == 0) st->dbg_t[dbg_pass][3] = gtime();
-#endif
+      }
     }
+
+    // ---- this CTA is done: one fence and one ticket per CTA; the last CTA of the pass scans the
+    // chunk records into prefixes and the exact stuffed size, then runs the bisection step
+    if (tid == 0) {
+        __threadfence();
+        s_last = atomicAdd(&st->done_a, 1u) == gridDim.x - 1u ? 1 : 0;
+    }
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+#ifdef ICB_TIMING
+    if (tid == 0) st->dbg_t[dbg_pass][1] = gtime();
+#endif
+    {
+        const int n_c = p.nchunks;
+        const int per = (n_c + ENT_THREADS - 1) / ENT_THREADS;          // consecutive chunk records per thread
+        const int c0 = min(n_c, tid * per), c1 = min(n_c, c0 + per);
+        const uint32_t *rw = reinterpret_cast<const uint32_t *>(pb.crec);
+        // bits in front of this thread's records
+        unsigned long long mine = 0;
+        for (int c = c0; c < c1; c++) mine += __ldcg(rw + 8 * c + 4);
+        unsigned long long incl = mine;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const unsigned long long t = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += t;
+        }
+        if (lane == 31) s_scan[warp] = incl;
+        __syncthreads();
+        unsigned long long P = incl - mine;
+        for (int w = 0; w < warp; w++) P += s_scan[w];
+        __syncthreads();
+        // 0xFF bytes of each record at its alignment; first pass leaves thread-local prefixes in Fc
+        uint32_t on_prev = c0 > 0 && c0 < n_c ? __ldcg(rw + 8 * (c0 - 1) + 5) : 0u;
+        uint32_t nff = 0;
+        for (int c = c0; c < c1; c++) {
+            const uint4 fa = __ldcg(pb.crec + 2 * c);
+            const uint32_t Lc = __ldcg(rw + 8 * c + 4), on = __ldcg(rw + 8 * c + 5);
+            const uint32_t r = (uint32_t)P & 7u;
+            const uint32_t lo = (r & 4u) ? fa.z : fa.x, hi = (r & 4u) ? fa.w : fa.y;
+            const uint32_t w2 = (r & 2u) ? hi : lo;
+            uint32_t cnt = (r & 1u) ? (w2 >> 16) : (w2 & 0xffffu);
+            if (c > 0) cnt += span_ff(on_prev, on, r);
+            pb.Pc[c] = P;
+            pb.Fc[c] = nff;
+            nff += cnt;
+            P += Lc;
+            on_prev = on;
+        }
+        uint32_t inclf = nff;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t t = __shfl_up_sync(0xffffffffu, inclf, o);
+            if (lane >= o) inclf += t;
+        }
+        if (lane == 31) s_scan[warp] = inclf;
+        __syncthreads();
+        uint32_t basef = inclf - nff;
+        for (int w = 0; w < warp; w++) basef += (uint32_t)s_scan[w];
+        pb.Fb[tid] = basef;                                             // Fc of a chunk = Fc[chunk] + Fb[chunk / per]
+        if (c1 == n_c && c0 < n_c) {                                    // owner of the last record
+            uint32_t total_ff = basef + nff;
+            const uint32_t rem = (uint32_t)P & 7u;                      // jchuff.c flush_bits: last byte padded with 1s
+            if (rem && (on_prev >> 8) >= rem) total_ff++;
+            s_total[0] = P;
+            s_total[1] = total_ff;
+        }
+        __syncthreads();
+    }
+#ifdef ICB_TIMING
+    if (tid == 0) st->dbg_t[dbg_pass][2] = gtime();
+#endif
+    if (warp == 0) device_step(st, 0, s_total[0], s_total[1]);      // :176-189 on the exact size, then the next table slot
+#ifdef ICB_TIMING
+    if (tid == 0) st->dbg_t[dbg_pass][3] = gtime();
+#endif
 }
 
 // ---- a tile's bits at their absolute alignment --------------------------------
@@ -587,14 +631,15 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
     const FitState *st = p.st;
     pdl_wait();
     if (st->best_size <= 0 || out == nullptr) return;
-    const PassBufs pb = pick_buf(p, st->best_buf);
+    const int best_buf = st->best_buf;
+    const PassBufs pb = pick_buf(p, best_buf);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (blockIdx.x == 0) {
         for (int i = tid; i < HEADER_BYTES; i += ENT_THREADS) {
             unsigned char b = c_hdr[i];
             if (i == HDR_OFF_MINOR) b = (unsigned char)st->jfif_minor;
-            else if (i >= HDR_OFF_DQT0 && i < HDR_OFF_DQT0 + 64) b = st->best_qtab[0][i - HDR_OFF_DQT0];
-            else if (i >= HDR_OFF_DQT1 && i < HDR_OFF_DQT1 + 64) b = st->best_qtab[1][i - HDR_OFF_DQT1];
+            else if (i >= HDR_OFF_DQT0 && i < HDR_OFF_DQT0 + 64) b = st->cand_qtab[best_buf][0][i - HDR_OFF_DQT0];
+            else if (i >= HDR_OFF_DQT1 && i < HDR_OFF_DQT1 + 64) b = st->cand_qtab[best_buf][1][i - HDR_OFF_DQT1];
             else if (i == HDR_OFF_H) b = (unsigned char)(img_h >> 8);
             else if (i == HDR_OFF_H + 1) b = (unsigned char)img_h;
             else if (i == HDR_OFF_W) b = (unsigned char)(img_w >> 8);
@@ -605,31 +650,32 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
     const int tile = blockIdx.x * ENT_WARPS + warp;
     if (tile >= p.ntiles) return;
 
-    // this tile's bit prefix and the 0xFF bytes completed before it: the group prefixes of the pass
-    // plus the tiles in front of it inside its group of 32 (lane = tile of the group)
-    const int grp = tile >> 5, g_first = grp << 5, me = tile & 31;
-    const bool have = g_first + lane < p.ntiles;
-    const uint32_t L_l = have ? __ldcg(pb.L + g_first + lane) : 0u;
-    const uint4 f_l = have ? __ldcg(pb.ff + g_first + lane) : make_uint4(0, 0, 0, 0);
-    const uint32_t on_l = have ? __ldcg(pb.ones + g_first + lane) : 0u;
+    // this tile's bit prefix and the 0xFF bytes completed before it: the chunk prefixes of the pass
+    // plus the tiles in front of it inside its chunk of 8 (lane = tile of the chunk)
+    const int chunk = tile / ENT_WARPS, t_first = chunk * ENT_WARPS, me = tile - t_first;
+    const bool have = lane < ENT_WARPS && t_first + lane < p.ntiles;
+    const uint32_t L_l = have ? __ldcg(pb.L + t_first + lane) : 0u;
+    const uint4 f_l = have ? __ldcg(pb.ff + t_first + lane) : make_uint4(0, 0, 0, 0);
+    const uint32_t on_l = have ? __ldcg(pb.ones + t_first + lane) : 0u;
     uint32_t inclL = L_l;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
+    for (int o = 1; o < ENT_WARPS; o <<= 1) {
         const uint32_t t = __shfl_up_sync(0xffffffffu, inclL, o);
         if (lane >= o) inclL += t;
     }
-    const unsigned long long P_l = __ldcg(pb.Pg + grp) + (inclL - L_l);
+    const unsigned long long P_l = __ldcg(pb.Pc + chunk) + (inclL - L_l);
     const uint32_t r_l = (uint32_t)P_l & 7u;
     uint32_t on_prev = __shfl_up_sync(0xffffffffu, on_l, 1);
-    if (lane == 0) on_prev = grp > 0 ? __ldcg(pb.onesg + grp - 1) : 0u;
-    const uint32_t c_l = have ? ff_select(f_l, r_l) + ((g_first + lane > 0) ? span_ff(on_prev, on_l, r_l) : 0u) : 0u;
+    if (lane == 0) on_prev = t_first > 0 ? __ldcg(pb.ones + t_first - 1) : 0u;
+    const uint32_t c_l = have ? ff_select(f_l, r_l) + ((t_first + lane > 0) ? span_ff(on_prev, on_l, r_l) : 0u) : 0u;
     uint32_t inclC = c_l;
 #pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
+    for (int o = 1; o < ENT_WARPS; o <<= 1) {
         const uint32_t t = __shfl_up_sync(0xffffffffu, inclC, o);
         if (lane >= o) inclC += t;
     }
-    const uint32_t ffb_l = __ldcg(pb.Fg + grp) + (inclC - c_l);
+    const int per = (p.nchunks + ENT_THREADS - 1) / ENT_THREADS;        // chunk records per thread of the final scan
+    const uint32_t ffb_l = __ldcg(pb.Fc + chunk) + __ldcg(pb.Fb + chunk / per) + (inclC - c_l);
     const unsigned long long P = __shfl_sync(0xffffffffu, P_l, me);
     const uint32_t L = __shfl_sync(0xffffffffu, L_l, me);
     const uint32_t ff_before = __shfl_sync(0xffffffffu, ffb_l, me);
@@ -673,10 +719,10 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
 }
 
 // per-slot arenas
-__host__ __device__ inline size_t ent_pass_bytes(int ntiles, int ngroups)
+__host__ __device__ inline size_t ent_pass_bytes(int ntiles, int nchunks)
 {
-    const size_t n = (size_t)ntiles, c = (size_t)ngroups;
-    return n * ENT_SCR_STRIDE * 4 + n * 4 + n * 16 + n * 4 + c * 4 + c * 32 + c * 4 + c * 8 + c * 4 + 256;
+    const size_t n = (size_t)ntiles, c = (size_t)nchunks;
+    return n * ENT_SCR_STRIDE * 4 + n * 4 + n * 16 + n * 4 + c * 32 + c * 8 + c * 4 + ENT_THREADS * 4 + 256;
 }
 
 }  // namespace icb
