@@ -1007,6 +1007,10 @@ int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q,
 #ifdef ICB_TIMING
             if (r == reps - 1) {
                 const FitState &fs = *s->h_state;
+                fprintf(stderr, "warp timeline (cycles from entry):");
+                for (int i = 1; i < 24; i++)
+                    fprintf(stderr, " %lld", fs.dbg_w[i] >= fs.dbg_w[0] ? (long long)(fs.dbg_w[i] - fs.dbg_w[0]) : -1ll);
+                fprintf(stderr, "\n");
                 for (int i = 0; i < fs.passes && i < 8; i++)
                     fprintf(stderr, "pass %d: tiles %.1f us, scan %.1f us, step %.1f us, gap to next %.1f us\n", i,
                             (fs.dbg_t[i][1] - fs.dbg_t[i][0]) * 1e-3, (fs.dbg_t[i][2] - fs.dbg_t[i][1]) * 1e-3,

@@ -96,6 +96,7 @@ struct FitState {
     long long cur_size, best_size;
     float trace_q[8];
     long long trace_size[8];
+    long long pad_a;        // keeps tab 16-byte aligned (the pass loads table entries in pairs)
     // three table slots: the coming pass reads tab[tsel]; while it runs, block 0 fills the other two
     // with the tables of both possible next midpoints ((tsel+1)%3: this pass fits, (tsel+2)%3: it
     // does not), so the bisection step at the end of the pass only flips tsel
@@ -104,12 +105,14 @@ struct FitState {
     // pass scratch
     unsigned int done_a;            // finished CTAs of k_entropy_pass
     int pad1, pad2, pad3;
+    unsigned long long dbg_w[24];   // ICB_TIMING: clock64 timeline of one warp of the last pass
     unsigned long long dbg_t[8][4]; // per pass: globaltimer at kernel start / tail start / step start / tail end
     unsigned long long ff_total;    // stuffed 0x00 bytes (= number of 0xFF data bytes)
     unsigned long long total_bits;  // entropy-coded bits before padding
 };
 
 static_assert(offsetof(FitState, iter) == 16 && offsetof(FitState, cur_buf) == 32, "k_entropy_pass reads these as int4");
+static_assert(offsetof(FitState, tab) % 16 == 0 && sizeof(QTables) % 16 == 0 && offsetof(FitState, trace_q) == 88, "control block = first 6 int4");
 static_assert(offsetof(FitState, tab) % 8 == 0 && offsetof(FitState, cand_qtab) % 4 == 0, "vector copies of the tables");
 
 // ---- Annex K tables (T.81), natural order; IJG jcparam.c / JDK JPEGQTable ----

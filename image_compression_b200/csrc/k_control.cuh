@@ -69,17 +69,20 @@ __device__ __forceinline__ void precompute_next_tables(FitState *st, int tid)
 // Called by all 32 lanes of ONE warp.  Consumes the pass that just ran (if any),
 // decides, and selects the tables of the next one.  Lane 0 reads every control field
 // first and writes them back at the end, so the global accesses pipeline.
-__device__ void device_step(FitState *st, int first, unsigned long long tbits, unsigned long long ffs)
+__device__ void device_step(FitState *st, const FitState *snap, int first, unsigned long long tbits,
+                            unsigned long long ffs)
 {
     const int lane = threadIdx.x & 31;
     int go = 0, better = 0;
     if (lane == 0) {
-        float lo = st->lo, hi = st->hi, best = st->best, cur_q = st->cur_q;
-        int iter = st->iter, done = st->done, n_trace = st->n_trace, passes = st->passes;
-        int cur_buf = st->cur_buf, best_buf = st->best_buf, tsel = st->tsel;
-        const int cur_valid = st->cur_valid, mode = st->mode;
-        const long long target = st->target;
-        long long best_size = st->best_size, cur_size = st->cur_size;
+        // snap = the control block (first 88 bytes) as it was when the pass started: nothing but this
+        // function writes it, so the pass hands over the copy it made in shared memory
+        float lo = snap->lo, hi = snap->hi, best = snap->best, cur_q = snap->cur_q;
+        int iter = snap->iter, done = snap->done, n_trace = snap->n_trace, passes = snap->passes;
+        int cur_buf = snap->cur_buf, best_buf = snap->best_buf, tsel = snap->tsel;
+        const int cur_valid = snap->cur_valid, mode = snap->mode;
+        const long long target = snap->target;
+        long long best_size = snap->best_size, cur_size = snap->cur_size;
         int fit = 0;
         if (cur_valid) {                                        // consume the pass that just ran
             const long long size = (long long)HEADER_BYTES + (long long)((tbits + 7ull) >> 3) + (long long)ffs + 2;
@@ -171,7 +174,7 @@ __device__ void begin_job(FitState *st, const BeginArgs &b)
     }
     __threadfence();
     __syncwarp();
-    device_step(st, 1, 0ull, 0ull);
+    device_step(st, st, 1, 0ull, 0ull);
     int go = 0;
     float q0 = 0.0f;
     if (lane == 0) { go = st->cur_valid; q0 = st->cur_q; }

@@ -83,7 +83,8 @@ struct BeginArgs {
 };
 
 // a2.1 / :158-200 -- defined in k_control.cuh
-__device__ void device_step(FitState *st, int first, unsigned long long tbits, unsigned long long ffs);
+__device__ void device_step(FitState *st, const FitState *snap, int first, unsigned long long tbits,
+                            unsigned long long ffs);
 __device__ __forceinline__ void precompute_next_tables(FitState *st, int tid);
 __device__ __forceinline__ int scaled_qval(int base, float q, int table_mode);
 __device__ void begin_job(FitState *st, const BeginArgs &b);
@@ -136,13 +137,12 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prepare(const EntParams
     const int g = lane >> 3, j = lane & 7;
     uint32_t *out = p.ent + (size_t)tile * ENT_CAP;
     uint32_t cnt = 0;
-    // all loads of the tile first (8 x 16 B per lane in flight), then the compaction: one memory
-    // round trip per tile instead of one per group of 4 blocks
-    constexpr int NIT = ENT_TILE_BLOCKS / 4;
+    // loads run three groups of 4 blocks ahead of the compaction (the loop is fully unrolled, so
+    // the ring below is plain registers): the L2 round trip overlaps the scans instead of adding up
+    constexpr int NIT = ENT_TILE_BLOCKS / 4, AHEAD = 3;
     uint4 raw_all[NIT];
     int xp_all[NIT];
-#pragma unroll
-    for (int it = 0; it < NIT; it++) {
+    auto fetch = [&](int it) {
         const int b = tile * ENT_TILE_BLOCKS + it * 4 + g;
         const int cidx = b % 6;
         // DC predictor = previous block of the same component in scan order
@@ -156,9 +156,12 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prepare(const EntParams
             raw_all[it] = __ldg(reinterpret_cast<const uint4 *>(p.coef) + (size_t)b * 8 + j);
             if (j == 0 && has_prev) xp_all[it] = (int)__ldg(p.coef + (size_t)prev * 64);
         }
-    }
+    };
+#pragma unroll
+    for (int it = 0; it < AHEAD; it++) fetch(it);
 #pragma unroll
     for (int it = 0; it < NIT; it++) {
+        if (it + AHEAD < NIT) fetch(it + AHEAD);
         const int b = tile * ENT_TILE_BLOCKS + it * 4 + g;
         const bool valid = b < p.nblocks;
         const uint32_t tb = (b % 6) >= 4 ? 1u : 0u;
@@ -221,7 +224,8 @@ __device__ __forceinline__ uint32_t ff_starts(uint32_t a, uint32_t b)
 __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
 {
     __shared__ uint32_t s_huf[512 + 32];            // AC: table * 256 + run * 16 + size;  DC: 512 + table * 16 + size
-    __shared__ uint2 s_qt[128];                     // quantiser by key = 2 * pos + table
+    __shared__ __align__(16) uint2 s_qt[128];       // quantiser by key = 2 * pos + table
+    __shared__ int4 s_ctl[6];                       // control block of FitState as the pass found it
     __shared__ uint32_t s_win[ENT_WARPS * ENT_WSTRIDE];
     __shared__ __align__(16) uint32_t s_rec[2][ENT_WARPS][8];   // tile records of one CTA round: ff (4 words), L, ones
     __shared__ unsigned long long s_scan[ENT_WARPS];
@@ -230,29 +234,54 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
 
     FitState *st = p.st;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+#ifdef ICB_TIMING
+    int dbg_i = 0;
+    const bool dbg_me = blockIdx.x == gridDim.x / 2 && warp == 3 && lane == 0;
+    unsigned long long dbg_early[3] = {0, 0, 0};            // a pass with nothing to do must not overwrite the last real one
+#define ICB_STAMP() do { if (dbg_me && dbg_i < 24) { if (dbg_i < 3) dbg_early[dbg_i++] = clock64(); else st->dbg_w[dbg_i++] = clock64(); } } while (0)
+#else
+#define ICB_STAMP() do { } while (0)
+#endif
+    ICB_STAMP();                    // 0: entry
     pdl_launch_dependents();
     // set-up that does not depend on the previous pass: runs while that pass drains
     for (int i = tid; i < HUF_WORDS; i += ENT_THREADS) s_huf[i] = __ldg(g_huf + i);
     const uint32_t wbase = warp * ENT_WSTRIDE;
     for (int i = lane; i < ENT_WSTRIDE; i += 32) s_win[wbase + i] = 0;
+    ICB_STAMP();                    // 1: tables requested, window zeroed
     pdl_wait();                     // the previous pass ran its bisection step: st is final
-    // one memory round trip: the control words and this thread's entry of all three table slots
-    const int4 c1 = __ldcg(reinterpret_cast<const int4 *>(&st->iter));         // iter, done, cur_valid, mode
-    const int4 c2 = __ldcg(reinterpret_cast<const int4 *>(&st->cur_buf));      // cur_buf, best_buf, tsel, n_trace
-    uint2 q0 = make_uint2(0, 0), q1 = q0, q2 = q0;
-    if (tid < 128) {
-        q0 = __ldcg(&st->tab[0].rh[tid]);
-        q1 = __ldcg(&st->tab[1].rh[tid]);
-        q2 = __ldcg(&st->tab[2].rh[tid]);
+    ICB_STAMP();                    // 2: after griddepcontrol.wait
+    // one memory round trip, few requests: warp 0 alone fetches the control block (lanes 0-5) and
+    // all three table slots, picks the slot and leaves both in shared memory (hundreds of CTAs
+    // start together: every thread asking for the same lines would queue up at one L2 slice)
+    if (warp == 0) {
+        int4 cw = make_int4(0, 0, 0, 0);
+        if (lane < 6) cw = __ldcg(reinterpret_cast<const int4 *>(st) + lane);
+        uint4 ta[3], tb[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            ta[k] = __ldcg(reinterpret_cast<const uint4 *>(st->tab[k].rh) + lane);
+            tb[k] = __ldcg(reinterpret_cast<const uint4 *>(st->tab[k].rh) + 32 + lane);
+        }
+        if (lane < 6) s_ctl[lane] = cw;
+        const int tsel = __shfl_sync(0xffffffffu, cw.z, 2);                 // int4 #2 = cur_buf, best_buf, tsel, n_trace
+        reinterpret_cast<uint4 *>(s_qt)[lane] = tsel == 0 ? ta[0] : (tsel == 1 ? ta[1] : ta[2]);
+        reinterpret_cast<uint4 *>(s_qt)[32 + lane] = tsel == 0 ? tb[0] : (tsel == 1 ? tb[1] : tb[2]);
     }
+    ICB_STAMP();                    // 3: control + tables arrived
+    __syncthreads();
+    ICB_STAMP();                    // 4: after the prologue barrier
+    const int4 c1 = s_ctl[1];       // iter, done, cur_valid, mode
+    const int4 c2 = s_ctl[2];       // cur_buf, best_buf, tsel, n_trace
     if (!c1.z) return;
+#ifdef ICB_TIMING
+    if (dbg_me) { st->dbg_w[0] = dbg_early[0]; st->dbg_w[1] = dbg_early[1]; st->dbg_w[2] = dbg_early[2]; }
+#endif
     const PassBufs pb = pick_buf(p, c2.x);
 #ifdef ICB_TIMING
     const int dbg_pass = (c1.x - 1) & 7;
     if (blockIdx.x == 0 && threadIdx.x == 0) st->dbg_t[dbg_pass][0] = gtime();
 #endif
-    if (tid < 128) s_qt[tid] = c2.z == 0 ? q0 : (c2.z == 1 ? q1 : q2);
-    __syncthreads();
     // both possible next tables, by the CTA with the least work (the last one has the fewest chunks)
     if (blockIdx.x == gridDim.x - 1) {
         precompute_next_tables(st, tid);
@@ -288,6 +317,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
               e_pf = __ldg(p.ent + (size_t)tn * ENT_CAP + lane);
           }
       }
+      ICB_STAMP();                  // 5 / 10: tile start
       if (tile < p.ntiles) {
         uint32_t *scr = pb.scratch + (size_t)tile * ENT_SCR_STRIDE;
         const uint32_t *ent = p.ent + (size_t)tile * ENT_CAP;
@@ -344,13 +374,8 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             if (w1) atomicOr(&s_win[a + 1], w1);
         };
 
-        uint32_t e_next = (uint32_t)lane < n ? e_first : 0u;
-        for (uint32_t i0 = 0; i0 < n; i0 += 32) {
-            const uint32_t e = e_next;
-            {   // next round's entries are in flight while this one is coded
-                const uint32_t ni = i0 + 32 + lane;
-                e_next = ni < n ? __ldg(ent + ni) : 0u;
-            }
+        // one round = 32 consecutive entries, one per lane
+        auto code_round = [&](const uint32_t e) {
             const bool isdc = (e & ENTRY_DC) != 0u;
             const uint32_t key = (e >> 17) & (isdc ? 1u : 127u);         // 2 * pos + table
             const int x = (int)(short)(e & 0xffffu);
@@ -365,7 +390,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             }
             const bool live = isdc || v != 0;                    // lanes past n hold e = 0: dead
             const uint32_t bal = __ballot_sync(0xffffffffu, live);
-            if (bal == 0u) continue;
+            if (bal == 0u) return;
             const uint32_t below = bal & lt_mask;
             uint32_t pk = __shfl_sync(0xffffffffu, key, (31 - __clz(below)) & 31);
             if (!below) pk = carry;                              // key of the previous live entry
@@ -407,7 +432,31 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             if (len) put(sym, len, off);
             carry = __shfl_sync(0xffffffffu, key, 31 - __clz(bal));
             if ((running >> 5) - flushed > (uint32_t)(ENT_WIN - 64)) flush_some();   // a round adds <= 59 words
+        };
+
+        // entries are fetched four rounds (128 entries) ahead: the L2 round trip of a load is longer
+        // than a round of coding, so a one-round look-ahead leaves every round waiting for its entries
+        uint32_t eb[4];
+        eb[0] = (uint32_t)lane < n ? e_first : 0u;
+#pragma unroll
+        for (int k = 1; k < 4; k++) {
+            const uint32_t ni = 32u * k + lane;
+            eb[k] = ni < n ? __ldg(ent + ni) : 0u;
         }
+        ICB_STAMP();                // 6 / 11: first entries requested
+        for (uint32_t i0 = 0; i0 < n; i0 += 128) {
+            uint32_t cur[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                cur[k] = eb[k];
+                const uint32_t ni = i0 + 128u + 32u * k + lane;
+                eb[k] = ni < n ? __ldg(ent + ni) : 0u;
+            }
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                if (i0 + 32u * k < n) code_round(cur[k]);
+        }
+        ICB_STAMP();                // 7 / 12: rounds done
         if (carry < 126u) {                                     // EOB of the tile's last block
             const uint32_t z = (carry & 1u) ? eob1 : eob0;
             if (lane == 0) put(z >> 8, z & 0xffu, running);
@@ -456,7 +505,9 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             s_rec[round & 1][warp][5] = on;
         }
       }
+      ICB_STAMP();                  // 8 / 13: tile record written
       __syncthreads();                                          // the chunk's tile records are in shared memory
+      ICB_STAMP();                  // 9 / 14: after the chunk barrier
 
       // ---- warp 0 folds the chunk (the other warps go on with their next tile)
       if (warp == 0) {
@@ -500,6 +551,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         s_last = atomicAdd(&st->done_a, 1u) == gridDim.x - 1u ? 1 : 0;
     }
     __syncthreads();
+    ICB_STAMP();                    // 15: CTA ticket drawn
     if (!s_last) return;
     __threadfence();
 #ifdef ICB_TIMING
@@ -512,7 +564,8 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         const uint32_t *rw = reinterpret_cast<const uint32_t *>(pb.crec);
         // bits in front of this thread's records
         unsigned long long mine = 0;
-        for (int c = c0; c < c1; c++) mine += __ldcg(rw + 8 * c + 4);
+        for (int c = c0; c < c1; c++) mine += rw[8 * c + 4];             // L1 was invalidated by the fence above;
+                                                                        // the second sweep below hits it
         unsigned long long incl = mine;
 #pragma unroll
         for (int o = 1; o < 32; o <<= 1) {
@@ -525,11 +578,11 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         for (int w = 0; w < warp; w++) P += s_scan[w];
         __syncthreads();
         // 0xFF bytes of each record at its alignment; first pass leaves thread-local prefixes in Fc
-        uint32_t on_prev = c0 > 0 && c0 < n_c ? __ldcg(rw + 8 * (c0 - 1) + 5) : 0u;
+        uint32_t on_prev = c0 > 0 && c0 < n_c ? rw[8 * (c0 - 1) + 5] : 0u;
         uint32_t nff = 0;
         for (int c = c0; c < c1; c++) {
-            const uint4 fa = __ldcg(pb.crec + 2 * c);
-            const uint32_t Lc = __ldcg(rw + 8 * c + 4), on = __ldcg(rw + 8 * c + 5);
+            const uint4 fa = pb.crec[2 * c];
+            const uint32_t Lc = rw[8 * c + 4], on = rw[8 * c + 5];
             const uint32_t r = (uint32_t)P & 7u;
             const uint32_t lo = (r & 4u) ? fa.z : fa.x, hi = (r & 4u) ? fa.w : fa.y;
             const uint32_t w2 = (r & 2u) ? hi : lo;
@@ -564,7 +617,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
 #ifdef ICB_TIMING
     if (tid == 0) st->dbg_t[dbg_pass][2] = gtime();
 #endif
-    if (warp == 0) device_step(st, 0, s_total[0], s_total[1]);      // :176-189 on the exact size, then the next table slot
+    if (warp == 0) device_step(st, reinterpret_cast<const FitState *>(s_ctl), 0, s_total[0], s_total[1]);      // :176-189 on the exact size, then the next table slot
 #ifdef ICB_TIMING
     if (tid == 0) st->dbg_t[dbg_pass][3] = gtime();
 #endif
