@@ -18,7 +18,8 @@ ICB_ERR_CAPACITY, ICB_ERR_NO_DEVICE, ICB_ERR_TICKET = -5, -6, -7
 FMT_RGB8, FMT_BGR8, FMT_RGBA8, FMT_ABGR8 = 0, 1, 2, 3
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "libimgcomp_b200.so")
+# IMGCOMP_B200_LIB: load another build of the SAME library (A/B runs of kernel variants); never a fallback
+_LIB_PATH = os.environ.get("IMGCOMP_B200_LIB") or os.path.join(_HERE, "libimgcomp_b200.so")
 
 # every symbol include/imgcomp_b200.h declares (checked by tests/test_abi.py)
 ABI_SYMBOLS = [

@@ -65,6 +65,7 @@ constexpr int ENT_THREADS = ENT_WARPS * 32;
 constexpr int ENT_SCR_STRIDE = (ENT_TILE_BLOCKS * 208) / 4 + 4;    // scratch words per tile
 constexpr int ENT_WIN = 128;                        // shared-memory bit window per warp (words)
 constexpr int ENT_WSTRIDE = ENT_WIN + 4;
+constexpr int ENT_RING = 16;                        // CTA rounds whose tile records fit in shared memory at once
 constexpr int ENT_CAP = ENT_TILE_BLOCKS * 64;       // survivor entries per tile, worst case
 
 constexpr int HEADER_BYTES = 623;                   // a2.8, 3-component JFIF

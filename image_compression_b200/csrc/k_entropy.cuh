@@ -137,36 +137,22 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prepare(const EntParams
     const int g = lane >> 3, j = lane & 7;
     uint32_t *out = p.ent + (size_t)tile * ENT_CAP;
     uint32_t cnt = 0;
-    // loads run three groups of 4 blocks ahead of the compaction (the loop is fully unrolled, so
-    // the ring below is plain registers): the L2 round trip overlaps the scans instead of adding up
-    constexpr int NIT = ENT_TILE_BLOCKS / 4, AHEAD = 3;
-    uint4 raw_all[NIT];
-    int xp_all[NIT];
-    auto fetch = [&](int it) {
+    for (int it = 0; it < ENT_TILE_BLOCKS / 4; it++) {
         const int b = tile * ENT_TILE_BLOCKS + it * 4 + g;
+        const bool valid = b < p.nblocks;
         const int cidx = b % 6;
+        const uint32_t tb = cidx >= 4 ? 1u : 0u;
         // DC predictor = previous block of the same component in scan order
         int prev = b - 1;
         bool has_prev = true;
         if (cidx == 0) { prev = b - 3; has_prev = b >= 6; }
         else if (cidx >= 4) { prev = b - 6; has_prev = b >= 6; }
-        raw_all[it] = make_uint4(0, 0, 0, 0);
-        xp_all[it] = 0;
-        if (b < p.nblocks) {
-            raw_all[it] = __ldg(reinterpret_cast<const uint4 *>(p.coef) + (size_t)b * 8 + j);
-            if (j == 0 && has_prev) xp_all[it] = (int)__ldg(p.coef + (size_t)prev * 64);
+        uint4 raw = make_uint4(0, 0, 0, 0);
+        int xp = 0;
+        if (valid) {
+            raw = __ldg(reinterpret_cast<const uint4 *>(p.coef) + (size_t)b * 8 + j);
+            if (j == 0 && has_prev) xp = (int)__ldg(p.coef + (size_t)prev * 64);
         }
-    };
-#pragma unroll
-    for (int it = 0; it < AHEAD; it++) fetch(it);
-#pragma unroll
-    for (int it = 0; it < NIT; it++) {
-        if (it + AHEAD < NIT) fetch(it + AHEAD);
-        const int b = tile * ENT_TILE_BLOCKS + it * 4 + g;
-        const bool valid = b < p.nblocks;
-        const uint32_t tb = (b % 6) >= 4 ? 1u : 0u;
-        const uint4 raw = raw_all[it];
-        const int xp = xp_all[it];
         const uint4 tt = *reinterpret_cast<const uint4 *>(&s_thr[tb][8 * j]);
         const uint32_t rw[4] = {raw.x, raw.y, raw.z, raw.w};
         const uint32_t tw[4] = {tt.x, tt.y, tt.z, tt.w};
@@ -227,7 +213,8 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
     __shared__ __align__(16) uint2 s_qt[128];       // quantiser by key = 2 * pos + table
     __shared__ int4 s_ctl[6];                       // control block of FitState as the pass found it
     __shared__ uint32_t s_win[ENT_WARPS * ENT_WSTRIDE];
-    __shared__ __align__(16) uint32_t s_rec[2][ENT_WARPS][8];   // tile records of one CTA round: ff (4 words), L, ones
+    __shared__ __align__(16) uint32_t s_rec[ENT_RING][ENT_WARPS][8];    // tile records by CTA round: ff (4 words), L, ones
+    __shared__ unsigned int s_arr[ENT_RING];        // warps of the round's chunk that have finished their tile
     __shared__ unsigned long long s_scan[ENT_WARPS];
     __shared__ unsigned long long s_total[2];
     __shared__ int s_last;
@@ -248,6 +235,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
     for (int i = tid; i < HUF_WORDS; i += ENT_THREADS) s_huf[i] = __ldg(g_huf + i);
     const uint32_t wbase = warp * ENT_WSTRIDE;
     for (int i = lane; i < ENT_WSTRIDE; i += 32) s_win[wbase + i] = 0;
+    if (tid < ENT_RING) s_arr[tid] = 0;
     ICB_STAMP();                    // 1: tables requested, window zeroed
     pdl_wait();                     // the previous pass ran its bisection step: st is final
     ICB_STAMP();                    // 2: after griddepcontrol.wait
@@ -297,26 +285,15 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
     // persistent CTAs: chunks of 8 consecutive tiles (one per warp) are dealt out statically (no
     // shared cursor a late CTA could overrun); nobody ever waits for another CTA
     int round = 0;
-    // a tile's entry count and first 32 entries are fetched one tile ahead (and together: reading
-    // past the count stays inside the tile's ENT_CAP slots and is masked afterwards)
-    uint32_t n_pf = 0, e_pf = 0;
-    {
-        const int t0 = blockIdx.x * ENT_WARPS + warp;
-        if (t0 < p.ntiles) {
-            n_pf = __ldg(p.ent_cnt + t0);
-            e_pf = __ldg(p.ent + (size_t)t0 * ENT_CAP + lane);
-        }
-    }
     for (int chunk = blockIdx.x; chunk < p.nchunks; chunk += gridDim.x, round++) {
       const int tile = chunk * ENT_WARPS + warp;
-      const uint32_t n = n_pf, e_first = e_pf;
-      {
-          const int tn = tile + (int)gridDim.x * ENT_WARPS;
-          if (chunk + (int)gridDim.x < p.nchunks && tn < p.ntiles) {
-              n_pf = __ldg(p.ent_cnt + tn);
-              e_pf = __ldg(p.ent + (size_t)tn * ENT_CAP + lane);
-          }
-      }
+      const int slot = round & (ENT_RING - 1);
+      if (round && slot == 0) __syncthreads();                  // the record ring starts a new lap (rare: > 16 rounds)
+      // count and first 32 entries together: reading past the count stays inside the tile's ENT_CAP
+      // slots and is masked afterwards.  (Deeper look-ahead -- four rounds, or one tile ahead -- was
+      // measured slower, alone and with several fits sharing the GPU: the loop is issue bound.)
+      uint32_t n = 0, e_first = 0;
+      if (tile < p.ntiles) { n = __ldg(p.ent_cnt + tile); e_first = __ldg(p.ent + (size_t)tile * ENT_CAP + lane); }
       ICB_STAMP();                  // 5 / 10: tile start
       if (tile < p.ntiles) {
         uint32_t *scr = pb.scratch + (size_t)tile * ENT_SCR_STRIDE;
@@ -434,27 +411,12 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             if ((running >> 5) - flushed > (uint32_t)(ENT_WIN - 64)) flush_some();   // a round adds <= 59 words
         };
 
-        // entries are fetched four rounds (128 entries) ahead: the L2 round trip of a load is longer
-        // than a round of coding, so a one-round look-ahead leaves every round waiting for its entries
-        uint32_t eb[4];
-        eb[0] = (uint32_t)lane < n ? e_first : 0u;
-#pragma unroll
-        for (int k = 1; k < 4; k++) {
-            const uint32_t ni = 32u * k + lane;
-            eb[k] = ni < n ? __ldg(ent + ni) : 0u;
-        }
-        ICB_STAMP();                // 6 / 11: first entries requested
-        for (uint32_t i0 = 0; i0 < n; i0 += 128) {
-            uint32_t cur[4];
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                cur[k] = eb[k];
-                const uint32_t ni = i0 + 128u + 32u * k + lane;
-                eb[k] = ni < n ? __ldg(ent + ni) : 0u;
-            }
-#pragma unroll
-            for (int k = 0; k < 4; k++)
-                if (i0 + 32u * k < n) code_round(cur[k]);
+        uint32_t e_next = (uint32_t)lane < n ? e_first : 0u;
+        for (uint32_t i0 = 0; i0 < n; i0 += 32) {
+            const uint32_t e = e_next;
+            const uint32_t ni = i0 + 32 + lane;                 // next round's entries fly while this one is coded
+            e_next = ni < n ? __ldg(ent + ni) : 0u;
+            code_round(e);
         }
         ICB_STAMP();                // 7 / 12: rounds done
         if (carry < 126u) {                                     // EOB of the tile's last block
@@ -500,21 +462,27 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             pb.ff[tile] = fpk;                                  // for k_entropy_emit (next kernel: no fence needed)
             pb.L[tile] = running;
             pb.ones[tile] = on;
-            *reinterpret_cast<uint4 *>(&s_rec[round & 1][warp][0]) = fpk;
-            s_rec[round & 1][warp][4] = running;
-            s_rec[round & 1][warp][5] = on;
+            *reinterpret_cast<uint4 *>(&s_rec[slot][warp][0]) = fpk;
+            s_rec[slot][warp][4] = running;
+            s_rec[slot][warp][5] = on;
         }
-      }
-      ICB_STAMP();                  // 8 / 13: tile record written
-      __syncthreads();                                          // the chunk's tile records are in shared memory
-      ICB_STAMP();                  // 9 / 14: after the chunk barrier
+        ICB_STAMP();                // 8 / 12: tile record written
 
-      // ---- warp 0 folds the chunk (the other warps go on with their next tile)
-      if (warp == 0) {
-            const int g_n = min(ENT_WARPS, p.ntiles - chunk * ENT_WARPS);
+        // ---- the last warp of the chunk to finish folds it; nobody waits (the warps of a CTA drift
+        // apart freely: a barrier here costs throughput when several fits share the GPU)
+        const int g_n = min(ENT_WARPS, p.ntiles - chunk * ENT_WARPS);
+        uint32_t arrived = 0;
+        if (lane == 0) {
+            __threadfence_block();
+            arrived = atomicAdd(&s_arr[slot], 1u);
+            if (arrived == (uint32_t)(g_n - 1)) s_arr[slot] = 0;       // ready for the ring's next lap
+            __threadfence_block();
+        }
+        arrived = __shfl_sync(0xffffffffu, arrived, 0);
+        if (arrived == (uint32_t)(g_n - 1)) {
             const bool have = lane < g_n;
-            const uint32_t *rec = &s_rec[round & 1][lane & (ENT_WARPS - 1)][0];
-            const uint4 f_l = have ? *reinterpret_cast<const uint4 *>(rec) : make_uint4(0, 0, 0, 0);
+            const volatile uint32_t *rec = &s_rec[slot][lane & (ENT_WARPS - 1)][0];
+            const uint4 f_l = have ? make_uint4(rec[0], rec[1], rec[2], rec[3]) : make_uint4(0, 0, 0, 0);
             const uint32_t L_l = have ? rec[4] : 0u;
             const uint32_t on_l = have ? rec[5] : 0u;
             uint32_t inclL = L_l;
@@ -541,17 +509,20 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
                                                 tot8[4] | (tot8[5] << 16), tot8[6] | (tot8[7] << 16));
                 pb.crec[2 * chunk + 1] = make_uint4(Lc, head | (tail << 8), 0u, 0u);
             }
+        }
       }
     }
 
-    // ---- this CTA is done: one fence and one ticket per CTA; the last CTA of the pass scans the
-    // chunk records into prefixes and the exact stuffed size, then runs the bisection step
+    // ---- this CTA is done: one fence and one ticket per CTA (the barrier makes every warp's chunk
+    // records part of what thread 0 releases); the last CTA of the pass scans the chunk records
+    // into prefixes and the exact stuffed size, then runs the bisection step
+    __syncthreads();
     if (tid == 0) {
         __threadfence();
         s_last = atomicAdd(&st->done_a, 1u) == gridDim.x - 1u ? 1 : 0;
     }
     __syncthreads();
-    ICB_STAMP();                    // 15: CTA ticket drawn
+    ICB_STAMP();                    // CTA ticket drawn
     if (!s_last) return;
     __threadfence();
 #ifdef ICB_TIMING
