@@ -63,7 +63,7 @@ constexpr int ENT_WARPS = 8;
 constexpr int ENT_THREADS = ENT_WARPS * 32;
 // worst case per block: DC 9+11 bits, 63 x (16+10) bits = 1658 bits -> 208 B
 constexpr int ENT_SCR_STRIDE = (ENT_TILE_BLOCKS * 208) / 4 + 4;    // scratch words per tile
-constexpr int ENT_WIN = 128;                        // shared-memory bit window per warp (words)
+constexpr int ENT_WIN = 256;                        // shared-memory bit window per warp (words)
 constexpr int ENT_WSTRIDE = ENT_WIN + 4;
 constexpr int ENT_RING = 16;                        // CTA rounds whose tile records fit in shared memory at once
 constexpr int ENT_CAP = ENT_TILE_BLOCKS * 64;       // survivor entries per tile, worst case

@@ -289,11 +289,15 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
       const int tile = chunk * ENT_WARPS + warp;
       const int slot = round & (ENT_RING - 1);
       if (round && slot == 0) __syncthreads();                  // the record ring starts a new lap (rare: > 16 rounds)
-      // count and first 32 entries together: reading past the count stays inside the tile's ENT_CAP
+      // count and first 64 entries together: reading past the count stays inside the tile's ENT_CAP
       // slots and is masked afterwards.  (Deeper look-ahead -- four rounds, or one tile ahead -- was
       // measured slower, alone and with several fits sharing the GPU: the loop is issue bound.)
-      uint32_t n = 0, e_first = 0;
-      if (tile < p.ntiles) { n = __ldg(p.ent_cnt + tile); e_first = __ldg(p.ent + (size_t)tile * ENT_CAP + lane); }
+      uint32_t n = 0;
+      uint2 e_first = make_uint2(0u, 0u);
+      if (tile < p.ntiles) {
+          n = __ldg(p.ent_cnt + tile);
+          e_first = __ldg(reinterpret_cast<const uint2 *>(p.ent + (size_t)tile * ENT_CAP) + lane);
+      }
       ICB_STAMP();                  // 5 / 10: tile start
       if (tile < p.ntiles) {
         uint32_t *scr = pb.scratch + (size_t)tile * ENT_SCR_STRIDE;
@@ -351,46 +355,76 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             if (w1) atomicOr(&s_win[a + 1], w1);
         };
 
-        // one round = 32 consecutive entries, one per lane
-        auto code_round = [&](const uint32_t e) {
-            const bool isdc = (e & ENTRY_DC) != 0u;
-            const uint32_t key = (e >> 17) & (isdc ? 1u : 127u);         // 2 * pos + table
+        // OR `len` (1..64) bits of sym into the window at tile bit offset off (two symbols of a lane)
+        auto put64 = [&](unsigned long long sym, uint32_t len, uint32_t off) {
+            const unsigned long long V = sym << (64u - len);
+            const uint32_t hi = (uint32_t)(V >> 32), lo = (uint32_t)V;
+            const uint32_t a = wbase + (off >> 5) - flushed, sh = off & 31u;
+            const uint32_t w0 = hi >> sh, w1 = __funnelshift_r(lo, hi, sh), w2 = __funnelshift_r(0u, lo, sh);
+            if (w0) atomicOr(&s_win[a], w0);
+            if (w1) atomicOr(&s_win[a + 1], w1);
+            if (w2) atomicOr(&s_win[a + 2], w2);
+        };
+
+        // a2.5 quantise one survivor at the current tables: sign(x) * ((|x| + 4q) / 8q), the division
+        // as a multiply-high; a DC entry becomes the difference against its predictor block
+        auto quant = [&](uint32_t e, bool &isdc, uint32_t &key) -> int {
+            isdc = (e & ENTRY_DC) != 0u;
+            key = (e >> 17) & (isdc ? 1u : 127u);                        // 2 * pos + table
             const int x = (int)(short)(e & 0xffffu);
             const uint2 qt = s_qt[key];
-            // a2.5 quantise: sign(x) * ((|x| + 4q) / 8q), division as a multiply-high
             const uint32_t qa = __umulhi((uint32_t)abs(x) + qt.y, qt.x);
             int v = x < 0 ? -(int)qa : (int)qa;
-            if (isdc) {                                          // DC difference against the predictor block
+            if (isdc) {
                 const int xp = (int)e >> 18;
                 const uint32_t qp = __umulhi((uint32_t)abs(xp) + qt.y, qt.x);
                 v -= xp < 0 ? -(int)qp : (int)qp;
             }
-            const bool live = isdc || v != 0;                    // lanes past n hold e = 0: dead
-            const uint32_t bal = __ballot_sync(0xffffffffu, live);
-            if (bal == 0u) return;
-            const uint32_t below = bal & lt_mask;
-            uint32_t pk = __shfl_sync(0xffffffffu, key, (31 - __clz(below)) & 31);
-            if (!below) pk = carry;                              // key of the previous live entry
+            return v;
+        };
+        // a2.7 the code of one live entry whose previous live entry had key pk: symbol bits, their
+        // length, and the ZRL codes (16-zero runs) that go in front of it
+        auto mksym = [&](bool isdc, uint32_t key, int v, uint32_t pk, uint32_t &sym, uint32_t &len, uint32_t &nz) {
             const uint32_t nb = 32u - (uint32_t)__clz(abs(v));
             const uint32_t vbits = (uint32_t)(v + (v >> 31)) & ((1u << nb) - 1u);
-            const uint32_t r = ((key - pk) >> 1) - 1u;           // zero run in front of an AC coefficient
+            const uint32_t r = ((key - pk) >> 1) - 1u;                   // zero run in front of an AC coefficient
             const uint32_t hidx = isdc ? 512u + (key << 4) + nb : ((key & 1u) << 8) | ((r & 15u) << 4) | nb;
             const uint32_t code = s_huf[hidx];
-            uint32_t sym = ((code >> 8) << nb) | vbits;
-            uint32_t len = (code & 0xffu) + nb;
-            uint32_t nz = 0, zlen = 0;
+            sym = ((code >> 8) << nb) | vbits;
+            len = (code & 0xffu) + nb;
+            nz = 0;
             if (isdc) {
-                if (pk < 126u) {                                 // previous block ended early: its EOB goes first
+                if (pk < 126u) {                                         // previous block ended early: its EOB goes first
                     const uint32_t z = (pk & 1u) ? eob1 : eob0;
                     sym |= (z >> 8) << len;
                     len += z & 0xffu;
                 }
             } else {
-                nz = r >> 4;                                     // runs of 16 zeros: ZRL codes in front
-                zlen = nz * (((key & 1u) ? zrl1 : zrl0) & 0xffu);
+                nz = r >> 4;
             }
-            if (!live) { len = 0; nz = 0; zlen = 0; }
-            const uint32_t tot = len + zlen;
+        };
+
+        // one round = 64 consecutive entries, two per lane (lane l: entries 2l, 2l+1): the scan of the
+        // code lengths, the look-up of the previous live key and the window bookkeeping are paid once
+        // per pair, and a pair's two codes usually go into the window as one 64-bit field
+        auto code_round = [&](const uint2 ee) {
+            bool dc_a, dc_b;
+            uint32_t key_a, key_b;
+            const int v_a = quant(ee.x, dc_a, key_a), v_b = quant(ee.y, dc_b, key_b);
+            const bool live_a = dc_a || v_a != 0, live_b = dc_b || v_b != 0;   // entries past n are 0: dead
+            const uint32_t bal = __ballot_sync(0xffffffffu, live_a || live_b);
+            if (bal == 0u) return;
+            const uint32_t last_key = live_b ? key_b : key_a;           // of this lane, if it has a live entry
+            const uint32_t below = bal & lt_mask;
+            uint32_t pk_a = __shfl_sync(0xffffffffu, last_key, (31 - __clz(below)) & 31);
+            if (!below) pk_a = carry;                                   // key of the previous live entry
+            const uint32_t pk_b = live_a ? key_a : pk_a;
+            uint32_t sym_a = 0, len_a = 0, nz_a = 0, sym_b = 0, len_b = 0, nz_b = 0;
+            if (live_a) mksym(dc_a, key_a, v_a, pk_a, sym_a, len_a, nz_a);
+            if (live_b) mksym(dc_b, key_b, v_b, pk_b, sym_b, len_b, nz_b);
+            const uint32_t zl_a = nz_a * (((key_a & 1u) ? zrl1 : zrl0) & 0xffu);
+            const uint32_t zl_b = nz_b * (((key_b & 1u) ? zrl1 : zrl0) & 0xffu);
+            const uint32_t tot = len_a + zl_a + len_b + zl_b;
             uint32_t incl = tot;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) {
@@ -399,23 +433,30 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             }
             uint32_t off = running + incl - tot;
             running += __shfl_sync(0xffffffffu, incl, 31);
-            if (nz) {
-                const uint32_t z = (key & 1u) ? zrl1 : zrl0;
-                for (uint32_t k = 0; k < nz; k++) {
-                    put(z >> 8, z & 0xffu, off);
-                    off += z & 0xffu;
-                }
+            if (nz_a | nz_b) {                                          // rare: a run of 16+ zeros
+                const uint32_t za = (key_a & 1u) ? zrl1 : zrl0, zb = (key_b & 1u) ? zrl1 : zrl0;
+                for (uint32_t k = 0; k < nz_a; k++) { put(za >> 8, za & 0xffu, off); off += za & 0xffu; }
+                if (len_a) { put(sym_a, len_a, off); off += len_a; }
+                for (uint32_t k = 0; k < nz_b; k++) { put(zb >> 8, zb & 0xffu, off); off += zb & 0xffu; }
+                if (len_b) put(sym_b, len_b, off);
+            } else if (len_a + len_b) {
+                put64(((unsigned long long)sym_a << len_b) | sym_b, len_a + len_b, off);
             }
-            if (len) put(sym, len, off);
-            carry = __shfl_sync(0xffffffffu, key, 31 - __clz(bal));
-            if ((running >> 5) - flushed > (uint32_t)(ENT_WIN - 64)) flush_some();   // a round adds <= 59 words
+            carry = __shfl_sync(0xffffffffu, last_key, 31 - __clz(bal));
+            if ((running >> 5) - flushed > (uint32_t)(ENT_WIN - 128)) flush_some();   // a round adds <= 118 words
         };
 
-        uint32_t e_next = (uint32_t)lane < n ? e_first : 0u;
-        for (uint32_t i0 = 0; i0 < n; i0 += 32) {
-            const uint32_t e = e_next;
-            const uint32_t ni = i0 + 32 + lane;                 // next round's entries fly while this one is coded
-            e_next = ni < n ? __ldg(ent + ni) : 0u;
+        const uint2 *ent2 = reinterpret_cast<const uint2 *>(ent);
+        auto mask2 = [&](uint2 v, uint32_t i) {                         // entries i, i + 1 of the tile, 0 past the count
+            if (i >= n) v.x = 0u;
+            if (i + 1u >= n) v.y = 0u;
+            return v;
+        };
+        uint2 e_next = mask2(e_first, 2u * lane);
+        for (uint32_t i0 = 0; i0 < n; i0 += 64) {
+            const uint2 e = e_next;
+            const uint32_t ni = i0 + 64u + 2u * lane;                   // next round's entries fly while this one is coded
+            e_next = ni < n ? mask2(__ldg(ent2 + (ni >> 1)), ni) : make_uint2(0u, 0u);
             code_round(e);
         }
         ICB_STAMP();                // 7 / 12: rounds done
