@@ -275,7 +275,8 @@ int enqueue_transform(icb_handle *h, Slot *s, const unsigned char *d_px, int w, 
     if (cr != CUDA_SUCCESS) return fail(h, ICB_ERR_CUDA, "cuTensorMapEncodeTiled failed");
     const int tiles_per_row = (g.mcu_cols + TILE_MCUS - 1) / TILE_MCUS;
     const int ntiles = tiles_per_row * g.mcu_rows;
-    const int grid = std::min(ntiles, h->devs[s->devi].sms * 4);
+    static const int xf_cps = [] { const char *e = getenv("ICB_XF_CPS"); return e ? atoi(e) : 4; }();   // tuning knob
+    const int grid = std::min(ntiles, h->devs[s->devi].sms * std::max(1, std::min(4, xf_cps)));
     if (g.bgr)
         k_transform<true><<<grid, XF_THREADS, XF_SMEM_BYTES, s->stream>>>(tmap, g, s->d_coef, tiles_per_row, ntiles);
     else
@@ -285,14 +286,21 @@ int enqueue_transform(icb_handle *h, Slot *s, const unsigned char *d_px, int w, 
     return ICB_OK;
 }
 
-// number of bisection iterations Java can start for this initial quality (path-independent
-// up to float rounding: hi-lo halves every iteration; +1 for safety, capped at 8)
+// Number of bisection iterations Java can start for this initial quality (:167-189): hi - lo halves
+// every iteration whatever the path, and the loop stops once it is below 0.01f.  Midpoints can round
+// (by an ulp) when init_q is not dyadic, so one more pass is queued -- it finds cur_valid == 0 and
+// returns at once -- only if some q / 2^k comes that close to the 0.01f threshold.
 int max_search_iters(float init_q)
 {
     int n = 0;
+    bool near = false;
     float d = init_q;
-    while (n < 8 && !(d < 0.01f)) { d *= 0.5f; n++; }
-    return std::min(8, n + 1);
+    while (n < 8 && !(d < 0.01f)) {
+        d *= 0.5f;
+        n++;
+        if (d > 0.0099f && d < 0.0101f) near = true;
+    }
+    return std::min(8, n + (near ? 1 : 0));
 }
 
 // persistent grid of the entropy pass: c CTAs per SM (c <= 4 by registers) such that the statically
@@ -605,6 +613,20 @@ int icb_init(const int *devices, int n_devices, int slots_per_gpu, int max_w, in
 void icb_shutdown(icb_handle *h)
 {
     if (!h) return;
+#ifdef ICB_TIMING
+    if (getenv("ICB_DUMP_TIMELINE")) {          // the last job of every slot, on the GPU's global timer
+        unsigned long long t0 = ~0ull;
+        for (Slot &s : h->slots) if (s.h_state && s.h_state->dbg_k[0] && s.h_state->dbg_k[0] < t0) t0 = s.h_state->dbg_k[0];
+        for (Slot &s : h->slots) {
+            if (!s.h_state || !s.h_state->dbg_k[0]) continue;
+            const FitState &fs = *s.h_state;
+            fprintf(stderr, "slot %d: prepare@%.1f", s.index, (fs.dbg_k[0] - t0) * 1e-3);
+            for (int i = 0; i < fs.passes && i < 8; i++)
+                fprintf(stderr, " | pass%d %.1f..%.1f", i, (fs.dbg_t[i][0] - t0) * 1e-3, (fs.dbg_t[i][3] - t0) * 1e-3);
+            fprintf(stderr, " | emit %.1f..%.1f\n", (fs.dbg_k[1] - t0) * 1e-3, (fs.dbg_k[2] - t0) * 1e-3);
+        }
+    }
+#endif
     for (Slot &s : h->slots) {
         if (s.devi < (int)h->devs.size()) cudaSetDevice(h->devs[s.devi].dev);
         if (s.stream) { cudaStreamSynchronize(s.stream); cudaStreamDestroy(s.stream); }

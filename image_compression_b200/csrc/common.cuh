@@ -106,6 +106,7 @@ struct FitState {
     // pass scratch
     unsigned int done_a;            // finished CTAs of k_entropy_pass
     int pad1, pad2, pad3;
+    unsigned long long dbg_k[4];    // ICB_TIMING: globaltimer at survivor-kernel start / emit start / emit end (block 0)
     unsigned long long dbg_w[24];   // ICB_TIMING: clock64 timeline of one warp of the last pass
     unsigned long long dbg_t[8][4]; // per pass: globaltimer at kernel start / tail start / step start / tail end
     unsigned long long ff_total;    // stuffed 0x00 bytes (= number of 0xFF data bytes)

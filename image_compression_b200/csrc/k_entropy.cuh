@@ -38,6 +38,13 @@
 
 namespace icb {
 
+__device__ __forceinline__ unsigned long long gtime()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 struct PassBufs {
     uint32_t *scratch;              // [ntiles][ENT_SCR_STRIDE] tile-local bit streams, big-endian words
     unsigned int *L;                // [ntiles] bits per tile
@@ -129,6 +136,9 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prepare(const EntParams
     }
     // the job's search state and first tables (consumed by the pass kernels that follow)
     // (nothing of the previous kernel of the stream, the transform, is touched by this)
+#ifdef ICB_TIMING
+    if (blockIdx.x == 0 && tid == 0) p.st->dbg_k[0] = gtime();
+#endif
     if (blockIdx.x == 0 && warp == ENT_WARPS - 1) begin_job(p.st, ba);
     __syncthreads();
     pdl_wait();                     // the coefficients are complete and visible from here on
@@ -191,12 +201,6 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prepare(const EntParams
     if (lane == 0) p.ent_cnt[tile] = cnt;
 }
 
-__device__ __forceinline__ unsigned long long gtime()
-{
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
 
 // run-of-8 detector: bit (31 - p) of the result is set iff bits p .. p+7 of the 64-bit
 // big-endian pair (a, b) are all ones, for starts p = 0..31 inside a
@@ -696,6 +700,9 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
     const FitState *st = p.st;
     pdl_wait();
     if (st->best_size <= 0 || out == nullptr) return;
+#ifdef ICB_TIMING
+    if (blockIdx.x == 0 && threadIdx.x == 0) const_cast<FitState *>(st)->dbg_k[1] = gtime();
+#endif
     const int best_buf = st->best_buf;
     const PassBufs pb = pick_buf(p, best_buf);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -776,6 +783,9 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
         }
         ff_run += __shfl_sync(0xffffffffu, incl, 31);
     }
+#ifdef ICB_TIMING
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) const_cast<FitState *>(st)->dbg_k[2] = gtime();
+#endif
     if (v.last && lane == 0) {                                  // EOI
         const long long e = st->best_size - 2;
         if (e >= 0 && e < cap) out[e] = 0xff;
