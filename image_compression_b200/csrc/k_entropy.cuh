@@ -378,17 +378,17 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             const int x = (int)(short)(e & 0xffffu);
             const uint2 qt = s_qt[key];
             const uint32_t qa = __umulhi((uint32_t)abs(x) + qt.y, qt.x);
-            int v = x < 0 ? -(int)qa : (int)qa;
-            if (isdc) {
-                const int xp = (int)e >> 18;
-                const uint32_t qp = __umulhi((uint32_t)abs(xp) + qt.y, qt.x);
-                v -= xp < 0 ? -(int)qp : (int)qp;
-            }
-            return v;
+            const int v = x < 0 ? -(int)qa : (int)qa;
+            // straight-line on purpose (DC and AC lanes share every round: a branch would run both sides)
+            const int xp = (int)e >> 18;                                 // predictor DC; position bits on an AC entry
+            const uint32_t qp = __umulhi((uint32_t)abs(xp) + qt.y, qt.x);
+            const int vp = xp < 0 ? -(int)qp : (int)qp;
+            return isdc ? v - vp : v;
         };
-        // a2.7 the code of one live entry whose previous live entry had key pk: symbol bits, their
-        // length, and the ZRL codes (16-zero runs) that go in front of it
-        auto mksym = [&](bool isdc, uint32_t key, int v, uint32_t pk, uint32_t &sym, uint32_t &len, uint32_t &nz) {
+        // a2.7 the code of one entry whose previous live entry had key pk: symbol bits, their length
+        // (0 for a dead entry), and the number of ZRL codes (16-zero runs) that go in front of it
+        auto mksym = [&](bool live, bool isdc, uint32_t key, int v, uint32_t pk, uint32_t &sym, uint32_t &len,
+                         uint32_t &nz) {
             const uint32_t nb = 32u - (uint32_t)__clz(abs(v));
             const uint32_t vbits = (uint32_t)(v + (v >> 31)) & ((1u << nb) - 1u);
             const uint32_t r = ((key - pk) >> 1) - 1u;                   // zero run in front of an AC coefficient
@@ -396,16 +396,14 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             const uint32_t code = s_huf[hidx];
             sym = ((code >> 8) << nb) | vbits;
             len = (code & 0xffu) + nb;
-            nz = 0;
-            if (isdc) {
-                if (pk < 126u) {                                         // previous block ended early: its EOB goes first
-                    const uint32_t z = (pk & 1u) ? eob1 : eob0;
-                    sym |= (z >> 8) << len;
-                    len += z & 0xffu;
-                }
-            } else {
-                nz = r >> 4;
-            }
+            // a DC entry whose previous block ended early carries that block's EOB in front
+            const uint32_t z = (pk & 1u) ? eob1 : eob0;
+            const bool eob = isdc && pk < 126u;
+            sym |= eob ? (z >> 8) << len : 0u;
+            len += eob ? z & 0xffu : 0u;
+            nz = (isdc || !live) ? 0u : r >> 4;
+            len = live ? len : 0u;
+            sym = live ? sym : 0u;
         };
 
         // one round = 64 consecutive entries, two per lane (lane l: entries 2l, 2l+1): the scan of the
@@ -423,9 +421,9 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             uint32_t pk_a = __shfl_sync(0xffffffffu, last_key, (31 - __clz(below)) & 31);
             if (!below) pk_a = carry;                                   // key of the previous live entry
             const uint32_t pk_b = live_a ? key_a : pk_a;
-            uint32_t sym_a = 0, len_a = 0, nz_a = 0, sym_b = 0, len_b = 0, nz_b = 0;
-            if (live_a) mksym(dc_a, key_a, v_a, pk_a, sym_a, len_a, nz_a);
-            if (live_b) mksym(dc_b, key_b, v_b, pk_b, sym_b, len_b, nz_b);
+            uint32_t sym_a, len_a, nz_a, sym_b, len_b, nz_b;
+            mksym(live_a, dc_a, key_a, v_a, pk_a, sym_a, len_a, nz_a);
+            mksym(live_b, dc_b, key_b, v_b, pk_b, sym_b, len_b, nz_b);
             const uint32_t zl_a = nz_a * (((key_a & 1u) ? zrl1 : zrl0) & 0xffu);
             const uint32_t zl_b = nz_b * (((key_b & 1u) ? zrl1 : zrl0) & 0xffu);
             const uint32_t tot = len_a + zl_a + len_b + zl_b;
