@@ -30,5 +30,6 @@ from .api import (  # noqa: F401
     library_path,
     load_library,
     png_target_dims,
+    subsample_factor,
     resize_dims,
 )

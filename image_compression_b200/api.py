@@ -26,6 +26,7 @@ ABI_SYMBOLS = [
     "icb_init", "icb_shutdown", "icb_device_count", "icb_last_error", "icb_set_profile",
     "icb_alloc_pinned", "icb_free_pinned", "icb_jpg_fit", "icb_jpg_encode", "icb_jpg_sizes",
     "icb_jpg_coefficients", "icb_resize_dims", "icb_resize_bilinear", "icb_png_fit", "icb_png_target_dims",
+    "icb_subsample_factor", "icb_subsample",
     "icb_submit_jpg_fit", "icb_wait", "icb_image_upload", "icb_image_free",
     "icb_submit_jpg_fit_image", "icb_submit_resize_image", "icb_stats", "icb_profile_jpg_fit_image",
     "icb_mark", "icb_elapsed_ms",
@@ -96,6 +97,8 @@ def load_library(build_if_missing: bool = True):
                               C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.icb_png_target_dims.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int),
                                       C.POINTER(C.c_double)]
+    L.icb_subsample_factor.argtypes = [C.c_int, C.c_int]
+    L.icb_subsample.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int]
     L.icb_submit_jpg_fit.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int64, C.c_int,
                                      C.c_float, C.c_double, vp, C.c_size_t, C.POINTER(C.c_int64)]
     L.icb_wait.argtypes = [vp, C.c_int64, C.POINTER(_Result)]
@@ -175,6 +178,12 @@ def resize_dims(w: int, h: int, scale: float) -> Tuple[int, int]:
     a, b = C.c_int(0), C.c_int(0)
     L.icb_resize_dims(w, h, C.c_double(scale), C.byref(a), C.byref(b))
     return a.value, b.value
+
+
+def subsample_factor(w: int, h: int) -> int:
+    """core/ImageCompression.java:140-153: the integer source subsampling the reference decodes
+    with (1 when the longer side is at most 4096); host arithmetic, no device needed."""
+    return load_library().icb_subsample_factor(w, h)
 
 
 def png_target_dims(w: int, h: int, min_w: int, min_h: int):
@@ -358,6 +367,16 @@ class Engine:
             raise self._err(rc)
         return dst
 
+    # ---- input staging: core/ImageCompression.java:148-153 setSourceSubsampling(s, s, 0, 0) ----
+    def subsample(self, image: np.ndarray, s: int, fmt: Optional[int] = None) -> np.ndarray:
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        c = image.shape[2]
+        dst = np.empty(((h + s - 1) // s, (w + s - 1) // s, c), np.uint8)
+        rc = self._L.icb_subsample(self._h, image.ctypes.data, w, h, pitch, fmt, s, dst.ctypes.data, dst.strides[0])
+        if rc:
+            raise self._err(rc)
+        return dst
+
     # ---- core/ImageCompressionPng.java:37-75 (PNG file write stays with the caller) ----
     def compress_png_with_target_size(self, original_image: np.ndarray, output_file, params: CompressionParams,
                                       fmt: Optional[int] = None):
@@ -411,10 +430,11 @@ class Engine:
         self._inflight[t.value] = (None, out)
         return t.value
 
-    def submit_resize_image(self, img_handle, dw: int, dh: int, dst: np.ndarray) -> int:
+    def submit_resize_image(self, img_handle, dw: int, dh: int, dst: Optional[np.ndarray]) -> int:
+        """dst=None leaves the resized pixels in HBM (no device-to-host copy)."""
         t = C.c_int64(0)
-        rc = self._L.icb_submit_resize_image(self._h, img_handle, dw, dh, dst.ctypes.data, dst.strides[0],
-                                             C.byref(t))
+        rc = self._L.icb_submit_resize_image(self._h, img_handle, dw, dh, dst.ctypes.data if dst is not None else None,
+                                             dst.strides[0] if dst is not None else 0, C.byref(t))
         if rc:
             raise self._err(rc)
         self._inflight[t.value] = (None, dst)

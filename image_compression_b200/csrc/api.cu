@@ -700,15 +700,15 @@ int icb_submit_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q, 
 int icb_submit_resize_image(icb_handle *h, const icb_image *img, int dw, int dh, uint8_t *dst, int dpitch,
                             int64_t *ticket)
 {
-    if (!h || !img || !ticket || !dst || dw < 1 || dh < 1) return ICB_ERR_INVALID;
+    if (!h || !img || !ticket || dw < 1 || dh < 1) return ICB_ERR_INVALID;
     const int bpp = bpp_of(img->fmt);
-    if (dpitch < dw * bpp) return fail(h, ICB_ERR_INVALID, "dpitch smaller than a row");
+    if (dst && dpitch < dw * bpp) return fail(h, ICB_ERR_INVALID, "dpitch smaller than a row");
     Slot *s = acquire_slot(h, img->devi);
     CK(cudaSetDevice(h->devs[s->devi].dev));
     const int np = (int)round_up((size_t)dw * bpp, 16);
     int rc = ensure(h, s->d_rgb2, s->rgb2_cap, (size_t)np * dh + 16);
     if (!rc) rc = enqueue_resize(h, s, img->d_px, img->w, img->h, img->pitch, img->fmt, s->d_rgb2, dw, dh, np);
-    if (!rc) {
+    if (!rc && dst) {                            // dst == NULL: the resized pixels stay in HBM (kernel-only timing)
         cudaError_t e = cudaMemcpy2DAsync(dst, dpitch, s->d_rgb2, np, (size_t)dw * bpp, dh, cudaMemcpyDeviceToHost,
                                           s->stream);
         if (e != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "D2H", e);
@@ -901,6 +901,53 @@ int icb_resize_bilinear(icb_handle *h, const uint8_t *src, int w, int hgt, int p
                                           s->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
         if (e != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "resize", e);
+        h->d2h += (uint64_t)dw * bpp * dh;
+    } while (0);
+    if (rc) cudaStreamSynchronize(s->stream);
+    h->images_done++;
+    release_slot(h, s);
+    return rc;
+}
+
+int icb_subsample_factor(int w, int hgt)
+{
+    const int max_dim = w > hgt ? w : hgt;                          // core/ImageCompression.java:142
+    if (max_dim <= 4096) return 1;                                  // :143-144 PREFERRED_MAX_DIM
+    const int f = (int)((double)max_dim / 4096);                    // :145 (int) Math.floor
+    int s = 1;
+    while (s * 2 <= f) s *= 2;                                      // :151 Integer.highestOneBit
+    return s;
+}
+
+int icb_subsample(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt, int sfac, uint8_t *dst,
+                  int dpitch)
+{
+    if (!h) return ICB_ERR_INVALID;
+    if (!src || !dst || w < 1 || hgt < 1 || sfac < 1) return fail(h, ICB_ERR_INVALID, "bad subsample arguments");
+    if (fmt < ICB_FMT_RGB8 || fmt > ICB_FMT_ABGR8) return fail(h, ICB_ERR_UNSUPPORTED, "format");
+    const int bpp = bpp_of(fmt);
+    const int dw = (w + sfac - 1) / sfac, dh = (hgt + sfac - 1) / sfac;
+    if (pitch < w * bpp || dpitch < dw * bpp) return fail(h, ICB_ERR_INVALID, "pitch smaller than a row");
+    Slot *s = acquire_slot(h);
+    int rc = ICB_OK;
+    do {
+        if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess) { rc = ICB_ERR_CUDA; break; }
+        const int sp = (int)round_up((size_t)w * bpp, 16), np = (int)round_up((size_t)dw * bpp, 16);
+        rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)sp * hgt + 16);
+        if (rc) break;
+        rc = ensure(h, s->d_rgb2, s->rgb2_cap, (size_t)np * dh + 16);
+        if (rc) break;
+        rc = upload(h, s->stream, s->d_rgb, sp, src, w, hgt, pitch, bpp);
+        if (rc) break;
+        dim3 grid((dw + 31) / 32, (dh + 7) / 8);
+        if (bpp == 4) k_subsample<4><<<grid, 256, 0, s->stream>>>(s->d_rgb, sp, sfac, s->d_rgb2, dw, dh, np);
+        else k_subsample<3><<<grid, 256, 0, s->stream>>>(s->d_rgb, sp, sfac, s->d_rgb2, dw, dh, np);
+        h->kernels++;
+        cudaError_t e = cudaGetLastError();
+        if (e == cudaSuccess)
+            e = cudaMemcpy2DAsync(dst, dpitch, s->d_rgb2, np, (size_t)dw * bpp, dh, cudaMemcpyDeviceToHost, s->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+        if (e != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "subsample", e);
         h->d2h += (uint64_t)dw * bpp * dh;
     } while (0);
     if (rc) cudaStreamSynchronize(s->stream);

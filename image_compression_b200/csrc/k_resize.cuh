@@ -92,4 +92,21 @@ __global__ void __launch_bounds__(256) k_resize(const ResizeParams p)
     }
 }
 
+// f2 (input staging): ImageReadParam.setSourceSubsampling(s, s, 0, 0) as the reference's decode rule
+// applies it (core/ImageCompression.java:140-153) -- source pixel (x*s, y*s) for every destination
+// pixel, point sampling.  One thread per destination pixel; HBM-bound gather (a 32-byte sector is
+// fetched for every BPP bytes kept when s*BPP >= 32).
+template <int BPP>
+__global__ void __launch_bounds__(256) k_subsample(const unsigned char *__restrict__ src, int pitch, int s,
+                                                   unsigned char *__restrict__ dst, int dw, int dh, int dpitch)
+{
+    const int dx = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int dy = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (dx >= dw || dy >= dh) return;
+    const unsigned char *p = src + (size_t)dy * s * pitch + (size_t)dx * s * BPP;
+    unsigned char *o = dst + (size_t)dy * dpitch + (size_t)dx * BPP;
+#pragma unroll
+    for (int c = 0; c < BPP; c++) o[c] = __ldg(p + c);
+}
+
 }  // namespace icb

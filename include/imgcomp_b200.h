@@ -116,6 +116,15 @@ int icb_png_fit(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, in
  * with the target size and the double scale = min(min_w / w, min_h / h). */
 int icb_png_target_dims(int w, int hgt, int min_w, int min_h, int *dw, int *dh, double *scale);
 
+/* Input staging.  core/ImageCompression.java:140-153: when the longer side
+ * exceeds 4096 the reference decodes with setSourceSubsampling(s, s, 0, 0),
+ * s = highestOneBit(floor(maxDim / 4096)).  icb_subsample_factor is that rule (host
+ * arithmetic); icb_subsample is the decimation itself for callers that decode at full
+ * resolution: dst gets source pixels (x*s, y*s), ceil(w/s) x ceil(h/s) of them. */
+int icb_subsample_factor(int w, int hgt);
+int icb_subsample(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt, int s,
+                  uint8_t *dst, int dpitch);
+
 /* Asynchronous form = the per-GPU stream work queue that replaces the executor
  * (CompressionBatch.java:77-88 submit, :97-107 await).  submit blocks only while
  * every slot is busy; wait returns that job's status and releases the slot.
@@ -143,6 +152,7 @@ void icb_image_free(icb_handle *h, icb_image *img);
 int icb_submit_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q, int64_t target,
                              int has_cached, float cached_q, double cached_scale,
                              uint8_t *out, size_t out_cap, int64_t *ticket);
+/* dst == NULL leaves the resized pixels in the slot's HBM buffer (no D2H: kernel-only timing) */
 int icb_submit_resize_image(icb_handle *h, const icb_image *img, int dw, int dh,
                             uint8_t *dst, int dpitch, int64_t *ticket);
 

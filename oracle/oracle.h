@@ -99,6 +99,14 @@ int orc_resize_bilinear(const uint8_t *src, int w, int h, int pitch, int fmt,
 int orc_resize_bilinear_f64(const uint8_t *src, int w, int h, int pitch, int fmt,
                             uint8_t *dst, int dw, int dh, int dpitch);
 
+/* f2 (input staging): the decode rule of core/ImageCompression.java:140-153 and what
+ * javax.imageio's ImageReadParam.setSourceSubsampling(s, s, 0, 0) hands back: source
+ * pixels (x*s, y*s), ceil(w/s) x ceil(h/s) of them -- point sampling, no averaging
+ * [JDK-mem: IIOParam javadoc]. */
+int orc_subsample_factor(int w, int h);
+int orc_subsample(const uint8_t *src, int w, int h, int pitch, int bpp, int s,
+                  uint8_t *dst, int dpitch);
+
 /* a7: ImageCompressionPng.java:49-61.  Returns 0 and the new dims when a resize
  * is due, 1 when the image already fits (reference returns false). */
 int orc_png_target_dims(int w, int h, int min_w, int min_h, int *nw, int *nh, double *scale);

@@ -70,6 +70,8 @@ def lib():
         L.orc_resize_dims.restype = None
         for f in (L.orc_resize_bilinear, L.orc_resize_bilinear_f64):
             f.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, u8p, C.c_int, C.c_int, C.c_int]
+        L.orc_subsample_factor.argtypes = [C.c_int, C.c_int]
+        L.orc_subsample.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u8p, C.c_int]
         L.orc_png_target_dims.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int),
                                           C.POINTER(C.c_int), C.POINTER(C.c_double)]
     return _lib
@@ -174,6 +176,19 @@ def png_target_dims(w: int, h: int, min_w: int, min_h: int):
     a, b, s = C.c_int(0), C.c_int(0), C.c_double(0)
     rc = lib().orc_png_target_dims(w, h, min_w, min_h, C.byref(a), C.byref(b), C.byref(s))
     return rc, a.value, b.value, s.value
+
+
+def subsample_factor(w: int, h: int) -> int:
+    return lib().orc_subsample_factor(w, h)
+
+
+def subsample(img: np.ndarray, s: int) -> np.ndarray:
+    img, w, h, pitch = _img(img)
+    c = img.shape[2]
+    dst = np.zeros(((h + s - 1) // s, (w + s - 1) // s, c), np.uint8)
+    rc = lib().orc_subsample(_u8(img), w, h, pitch, c, s, _u8(dst), dst.strides[0])
+    assert rc == 0, rc
+    return dst
 
 
 def resize(img: np.ndarray, dw: int, dh: int, fmt: int = FMT_RGB8, f64: bool = False) -> np.ndarray:

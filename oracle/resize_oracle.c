@@ -31,6 +31,30 @@ void orc_resize_dims(int w, int h, double scale, int *nw, int *nh)
     *nh = b > 1 ? b : 1;
 }
 
+/* core/ImageCompression.java:140-153: subsampling = highestOneBit(floor(maxDim / 4096)) when
+ * the longer side exceeds PREFERRED_MAX_DIM = 4096, else 1 */
+int orc_subsample_factor(int w, int h)
+{
+    int max_dim = w > h ? w : h, s = 1;
+    if (max_dim > 4096) {
+        int f = (int)floor((double)max_dim / 4096);
+        if (f > 1) { s = 1; while (s * 2 <= f) s *= 2; }      /* Integer.highestOneBit */
+    }
+    return s;
+}
+
+/* ImageReadParam.setSourceSubsampling(s, s, 0, 0): every s-th pixel of every s-th row */
+int orc_subsample(const uint8_t *src, int w, int h, int pitch, int bpp, int s, uint8_t *dst, int dpitch)
+{
+    if (!src || !dst || s < 1 || bpp < 1) return -1;
+    int dw = (w + s - 1) / s, dh = (h + s - 1) / s;
+    for (int y = 0; y < dh; y++)
+        for (int x = 0; x < dw; x++)
+            memcpy(dst + (size_t)y * dpitch + (size_t)x * bpp, src + (size_t)(y * s) * pitch + (size_t)(x * s) * bpp,
+                   (size_t)bpp);
+    return 0;
+}
+
 /* ImageCompressionPng.java:49-61 */
 int orc_png_target_dims(int w, int h, int min_w, int min_h, int *nw, int *nh, double *scale)
 {

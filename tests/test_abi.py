@@ -65,6 +65,10 @@ def test_host_only_entry_points_need_no_device():
     assert pkg.png_target_dims(7680, 4320, 1920, 1920) == (1920, 1080, 0.25)
     with pytest.raises(pkg.IcbError):
         pkg.png_target_dims(0, 10, 5, 5)
+    # core/ImageCompression.java:140-153: highestOneBit(floor(maxDim / 4096)) above 4096
+    for (w, h), s in {(4000, 3000): 1, (4096, 4096): 1, (6000, 4000): 1, (8191, 100): 1, (8192, 6000): 2,
+                      (11548, 8660): 2, (12288, 100): 2, (16384, 16384): 4, (30000, 20000): 4, (40000, 1): 8}.items():
+        assert pkg.subsample_factor(w, h) == s, (w, h)
 
 
 def test_null_handle_is_an_error_not_a_crash():

@@ -138,6 +138,19 @@ def test_cfg3_png_downscale(engine, oracle, w, h, ch):
         assert np.abs(out.astype(int) - f64.astype(int)).max() <= 1
 
 
+# ---- input staging: the 100 MP source of configs[4] decimated like the reference's decoder does ----
+def test_subsample_matches_the_decode_rule(engine, oracle):
+    import image_compression_b200 as pkg
+    assert pkg.subsample_factor(11548, 8660) == 2
+    rng = np.random.default_rng(11)
+    for (w, h, c, s) in [(1001, 777, 3, 2), (640, 480, 4, 4), (333, 251, 3, 3), (4097, 64, 3, 1)]:
+        img = rng.integers(0, 256, (h, w, c), dtype=np.uint8)
+        got = engine.subsample(img, s)
+        assert np.array_equal(got, oracle.subsample(img, s)) and np.array_equal(got, img[::s, ::s])
+    big = synth.natural_image(500, 5000, 3000)
+    assert np.array_equal(engine.subsample(big, 2), big[::2, ::2])
+
+
 # ---- CompressionBatch.java:68,77 -- the seams are called from many pool threads at once ----------
 def test_concurrent_callers(engine, oracle):
     imgs = [synth.natural_image(400 + i, 640 + 16 * i, 480 + 8 * i) for i in range(8)]

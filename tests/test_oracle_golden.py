@@ -173,3 +173,15 @@ def test_dummy_block_geometry(oracle):
     assert not c[:, 2, 1, 1:].any() and not c[0, 2, 3, 1:].any()   # right luma column of MCU col 2
     assert c[0, 2, 1, 0] == c[0, 2, 0, 0]           # dummy DC = DC of the block to its left
     assert c[0, 0, 0, 1:].any()
+
+
+def test_subsample_rule_and_pixels(oracle):
+    """core/ImageCompression.java:140-153 + ImageReadParam.setSourceSubsampling(s, s, 0, 0): the
+    oracle against plain numpy slicing (an independent statement of "every s-th pixel")."""
+    assert [oracle.subsample_factor(w, h) for w, h in [(4096, 10), (4097, 10), (8191, 8191), (8192, 1), (11548, 8660),
+                                                        (16383, 5), (16384, 5), (70000, 3)]] == [1, 1, 1, 2, 2, 2, 4, 16]
+    rng = np.random.default_rng(3)
+    for (w, h, c) in [(17, 9, 3), (64, 48, 4), (101, 77, 3)]:
+        img = rng.integers(0, 256, (h, w, c), dtype=np.uint8)
+        for s in (1, 2, 3, 4, 8):
+            assert np.array_equal(oracle.subsample(img, s), img[::s, ::s])
