@@ -460,6 +460,88 @@ def run_gpu_png(args):
     return 0
 
 
+def run_gpu_mixed(args):
+    """BASELINE configs[3]: a mixed JPG/PNG file list with a WARM learned cache.  70 % JPG pixels
+    (12 MP and 24 MP, half each, 1 MB target) and 30 % PNG pixels (4K and 8K RGBA8 into the
+    1920x1920 box), interleaved.  The H2 cache stays a host-side map (here a dict keyed like
+    tools/CacheTools.java:14-21); it is warmed by one search per distinct key, so every timed JPG
+    takes the cache-hit path of core/ImageCompressionJpg.java:82-89, 216-238 (ONE encode at the
+    learned quality).  Host pixels in, bytes / resized pixels out: this is an e2e-only workload."""
+    rank, local, world, dist = dist_setup(args.gpus)
+    import image_compression_b200 as pkg
+    from image_compression_b200 import synth, LearnedParams
+    slots, batch = args.slots, args.batch
+    eng = pkg.Engine(devices=[local], slots_per_gpu=slots, max_w=6000, max_h=4000)
+    target, q = 1048576, 0.25
+    kinds = []                                       # (kind, pinned pixels, learned params or (dw, dh))
+    for i, (w, h) in enumerate([(4000, 3000), (6000, 4000)]):
+        img = synth.natural_image(3000 + 10 * rank + i, w, h)
+        pin = eng.alloc_pinned((h, w, 3))
+        pin[...] = img
+        r = eng.jpg_fit(img, q, target)              # the warm-up search that fills the cache
+        assert r.status == 0
+        kinds.append(("jpg", pin, LearnedParams(r.best_q, r.scale)))
+    for i, (w, h) in enumerate([(3840, 2160), (7680, 4320)]):
+        img = synth.natural_image(3100 + 10 * rank + i, w, h, channels=4)
+        pin = eng.alloc_pinned((h, w, 4))
+        pin[...] = img
+        dw, dh, _ = pkg.png_target_dims(w, h, 1920, 1920)
+        kinds.append(("png", pin, (dw, dh)))
+    order = [0, 1, 2, 0, 1, 3, 0, 1, 0, 2]           # 7 JPG : 3 PNG per ten lines
+    outs = [eng.alloc_pinned((target + 16,)) for _ in range(slots)]
+    png_out = eng.alloc_pinned((1080, 1920, 4))
+
+    def step():
+        inflight, hits, n_jpg = [], 0, 0
+        for i in range(batch):
+            kind, pin, extra = kinds[order[i % len(order)]]
+            if kind == "jpg":
+                if len(inflight) == slots:
+                    hits += int(eng.wait(inflight.pop(0)).used_cache)
+                inflight.append(eng.submit_jpg_fit(pin, q, target, outs[i % slots], cached=extra))
+                n_jpg += 1
+            else:                                    # synchronous seam (the PNG write that follows is host work);
+                if len(inflight) == slots:           # it needs a free slot: this thread holds them all until it waits
+                    hits += int(eng.wait(inflight.pop(0)).used_cache)
+                eng.resize_to_into(pin, png_out[: extra[1], : extra[0]])
+        while inflight:
+            hits += int(eng.wait(inflight.pop(0)).used_cache)
+        assert hits == n_jpg, "a cached fit fell back to the search"
+
+    for _ in range(args.warmup):
+        step()
+    st0 = eng.stats()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms, _ = timed_region(eng, dist, local, args.steps, lambda s: step())
+    clocks = sampler.stop()
+    st1 = eng.stats()
+    n_img = batch * args.steps
+    ips = n_img * world / (ms * 1e-3)
+    mp_step = sum(kinds[order[i % len(order)]][1].shape[0] * kinds[order[i % len(order)]][1].shape[1]
+                  for i in range(batch)) / 1e6
+    mps = mp_step * args.steps * world / (ms * 1e-3)
+    if rank == 0:
+        print(json.dumps({
+            "metric": "megapixels_per_s", "value": mps, "unit": "MP/s", "images_per_s": ips, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "int32", "data": "synthetic",
+            "config": {"workload": "BASELINE configs[3]: mixed list, 70% JPG (12/24 MP, cache hit: one encode at the "
+                                   "learned quality) + 30% PNG (4K/8K RGBA8 -> 1920x1080), warm host-side cache",
+                       "images_per_gpu_per_step": batch, "slots_per_gpu": slots,
+                       "note": "e2e only: value == e2e (host pixels in, bytes / pixels out)"},
+            "clocks": clocks,
+            "e2e": {"value": mps, "unit": "MP/s", "images_per_s": ips,
+                    "h2d_bytes_per_step": (st1["h2d_bytes"] - st0["h2d_bytes"]) / args.steps,
+                    "d2h_bytes_per_step": (st1["d2h_bytes"] - st0["d2h_bytes"]) / args.steps},
+            "gpu_launches": int(st1["kernels_launched"] - st0["kernels_launched"]),
+            "roofline": None, "cpu_baseline": None}), flush=True)
+    eng.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
 def run_gpu_latency(args):
     """BASELINE configs[4]: ONE 100 MP source (decoded 5774x4330 after the s=2 subsampling of
     core/ImageCompression.java:140-153), 256 KB target, -q 1.0 = the full 7-level sweep and the
@@ -525,7 +607,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="cfg1", choices=sorted(WORKLOADS) + ["png4k", "png8k", "cfg5"])
+    ap.add_argument("--workload", default="cfg1", choices=sorted(WORKLOADS) + ["png4k", "png8k", "cfg4", "cfg5"])
     ap.add_argument("--batch", type=int, default=64, help="images per GPU per step")
     ap.add_argument("--slots", type=int, default=6, help="stream work-queue slots per GPU")
     ap.add_argument("--threads", type=int, default=1, help="caller threads per GPU (each drives slots/threads)")
@@ -538,6 +620,8 @@ def main():
         return run_reference(args)
     if args.workload in ("png4k", "png8k"):
         return run_gpu_png(args)
+    if args.workload == "cfg4":
+        return run_gpu_mixed(args)
     if args.workload == "cfg5":
         return run_gpu_latency(args)
     return run_gpu(args)

@@ -144,6 +144,9 @@ int icb_submit_jpg_fit(icb_handle *h, const uint8_t *px, int w, int hgt, int pit
                        int has_cached, float cached_q, double cached_scale,
                        uint8_t *out, size_t out_cap, int64_t *ticket);
 int icb_wait(icb_handle *h, int64_t ticket, icb_result *res);
+/* A submitted job holds its work slot until icb_wait returns.  Every entry point takes a slot, so a
+ * thread that has slots_per_gpu * n_devices tickets outstanding must wait on one of them before it
+ * calls anything else (the call would block for a slot only that thread can free). */
 
 /* Device-resident inputs (bench `value`: pixels already in HBM when timing starts). */
 int icb_image_upload(icb_handle *h, int device_index, const uint8_t *px, int w, int hgt, int pitch,
