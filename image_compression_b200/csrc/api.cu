@@ -345,7 +345,7 @@ int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, 
         unsigned char *base = s->d_pass + (size_t)b * per;
         const size_t n = (size_t)g.ntiles, c = (size_t)nchunks;
         ep.buf[b].ff = reinterpret_cast<uint4 *>(base);                 base += n * 16;
-        ep.buf[b].crec = reinterpret_cast<uint4 *>(base);               base += c * 32;
+        ep.buf[b].crec = reinterpret_cast<uint4 *>(base);               base += c * 48;
         ep.buf[b].Pc = reinterpret_cast<unsigned long long *>(base);    base += c * 8;
         ep.buf[b].scratch = reinterpret_cast<uint32_t *>(base);         base += n * ENT_SCR_STRIDE * 4;
         ep.buf[b].L = reinterpret_cast<unsigned int *>(base);           base += n * 4;

@@ -32,7 +32,7 @@ struct Geom {
     int yblk_w, yblk_h;     // real luma block counts
     int crows_real;         // ceil(h/2): downsampled rows that come from pixels
     int nblocks;            // 6 * mcu_cols * mcu_rows
-    int ntiles;             // entropy tiles = ceil(nblocks / 32)
+    int ntiles;             // entropy tiles = ceil(nblocks / 64)
 };
 
 __host__ __device__ inline Geom make_geom(int w, int h, int pitch, int bgr)
@@ -45,7 +45,7 @@ __host__ __device__ inline Geom make_geom(int w, int h, int pitch, int bgr)
     g.yblk_h = (h + 7) >> 3;
     g.crows_real = (h + 1) >> 1;
     g.nblocks = 6 * g.mcu_cols * g.mcu_rows;
-    g.ntiles = (g.nblocks + 31) >> 5;
+    g.ntiles = (g.nblocks + 63) >> 6;       // ENT_TILE_BLOCKS = 64
     return g;
 }
 
@@ -58,13 +58,14 @@ constexpr int XF_THREADS = 128;
 constexpr int XF_STAGES = 2;
 
 // ---- entropy pass tiling ----
-constexpr int ENT_TILE_BLOCKS = 32;                 // blocks per warp tile
+constexpr int ENT_TILE_BLOCKS = 64;                 // blocks per warp tile
 constexpr int ENT_WARPS = 8;
 constexpr int ENT_THREADS = ENT_WARPS * 32;
 // worst case per block: DC 9+11 bits, 63 x (16+10) bits = 1658 bits -> 208 B
 constexpr int ENT_SCR_STRIDE = (ENT_TILE_BLOCKS * 208) / 4 + 4;    // scratch words per tile
 constexpr int ENT_WIN = 256;                        // shared-memory bit window per warp (words)
 constexpr int ENT_WSTRIDE = ENT_WIN + 4;
+static_assert(ENT_TILE_BLOCKS == 64, "make_geom computes ntiles with a shift by 6");
 constexpr int ENT_RING = 16;                        // CTA rounds whose tile records fit in shared memory at once
 constexpr int ENT_CAP = ENT_TILE_BLOCKS * 64;       // survivor entries per tile, worst case
 

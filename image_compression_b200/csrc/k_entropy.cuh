@@ -15,7 +15,7 @@
 //       left in HBM/L2 and keeps only the "survivors" -- coefficients that are
 //       non-zero at the HIGHEST quality any pass of this job can use
 //       (|x| >= 4*q_table, tables are monotone in quality) -- as compact 32-bit
-//       entries in scan order, one list per tile of 32 blocks.  Every block
+//       entries in scan order, one list per tile of 64 blocks.  Every block
 //       contributes a DC entry that also carries its predictor's raw DC.
 //   k_entropy_pass     once per search step: one warp per tile, one survivor per
 //       lane: quantise at the current tables, drop what became zero, run length =
@@ -50,8 +50,8 @@ struct PassBufs {
     unsigned int *L;                // [ntiles] bits per tile
     uint4 *ff;                      // [ntiles] 8 x u16: 0xFF bytes inside the tile per absolute start offset mod 8
     unsigned int *ones;             // [ntiles] leading 1-bits | trailing 1-bits << 8 (each capped at 8)
-    uint4 *crec;                    // [nchunks][2] chunk record: the same 8 counters folded over the chunk's
-                                    //              tiles | bits, ones, 0, 0      (chunk = the 8 tiles of one CTA round)
+    uint4 *crec;                    // [nchunks][3] chunk record: the same 8 counters (u32) folded over the chunk's
+                                    //              tiles (2 x uint4) | bits, ones, 0, 0    (chunk = the 8 tiles of a CTA round)
     unsigned long long *Pc;         // [nchunks] exclusive bit prefix            (last CTA of the pass)
     unsigned int *Fc;               // [nchunks] exclusive prefix of 0xFF bytes, relative to Fb  (last CTA of the pass)
     unsigned int *Fb;               // [ENT_THREADS] base of Fc for the chunks thread t of the last CTA scanned
@@ -308,7 +308,8 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         const uint32_t *ent = p.ent + (size_t)tile * ENT_CAP;
         uint32_t running = 0;       // bits produced so far (tile-local)
         uint32_t flushed = 0;       // whole words already copied to scratch
-        uint32_t acc0 = 0, acc1 = 0;   // 0xFF counters, 4 x 8 bits each: local start bit s = 0..3 | 4..7
+        uint32_t acc[4] = {0, 0, 0, 0};     // 0xFF counters, 2 x 16 bits each: local start bit s = 0,1 | 2,3 | 4,5 | 6,7
+                                            // (a lane sees <= 104 words of a 64-block tile, <= 4 starts per word and s)
         uint32_t carry = 126u;      // key of the last live entry (126 = pos 63: no EOB owed)
         uint32_t first_word = 0;    // word 0 of the tile stream (for the leading-ones count)
 
@@ -323,8 +324,8 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
                 if (m) {
 #pragma unroll
                     for (uint32_t s = 0; s < 4; s++) {
-                        acc0 += __popc(m & (0x80808080u >> s)) << (8 * s);
-                        acc1 += __popc(m & (0x08080808u >> s)) << (8 * s);
+                        acc[s >> 1] += __popc(m & (0x80808080u >> s)) << (16 * (s & 1));
+                        acc[2 + (s >> 1)] += __popc(m & (0x08080808u >> s)) << (16 * (s & 1));
                     }
                 }
             }
@@ -474,10 +475,10 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         count_ff(nw, running);
         for (uint32_t w = lane; w < nw + 1; w += 32) scr[flushed + w] = s_win[wbase + w];
         uint32_t f[8];
-        if (__any_sync(0xffffffffu, (acc0 | acc1) != 0u)) {
+        if (__any_sync(0xffffffffu, (acc[0] | acc[1] | acc[2] | acc[3]) != 0u)) {
 #pragma unroll
             for (int s = 0; s < 8; s++) {
-                const uint32_t a = s < 4 ? (acc0 >> (8 * s)) & 0xffu : (acc1 >> (8 * (s - 4))) & 0xffu;
+                const uint32_t a = (acc[s >> 1] >> (16 * (s & 1))) & 0xffffu;
                 f[s] = __reduce_add_sync(0xffffffffu, a);
             }
         } else {
@@ -547,10 +548,10 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             const uint32_t Lc = __shfl_sync(0xffffffffu, inclL, g_n - 1);
             const uint32_t head = __shfl_sync(0xffffffffu, on_l, 0) & 0xffu;
             const uint32_t tail = __shfl_sync(0xffffffffu, on_l, g_n - 1) >> 8;
-            if (lane == 0) {                                    // <= 8 x 6656 stuffed bytes per counter: fits 16 bits
-                pb.crec[2 * chunk] = make_uint4(tot8[0] | (tot8[1] << 16), tot8[2] | (tot8[3] << 16),
-                                                tot8[4] | (tot8[5] << 16), tot8[6] | (tot8[7] << 16));
-                pb.crec[2 * chunk + 1] = make_uint4(Lc, head | (tail << 8), 0u, 0u);
+            if (lane == 0) {                                    // up to 8 x 13312 stuffed bytes per counter: 32 bits
+                pb.crec[3 * chunk] = make_uint4(tot8[0], tot8[1], tot8[2], tot8[3]);
+                pb.crec[3 * chunk + 1] = make_uint4(tot8[4], tot8[5], tot8[6], tot8[7]);
+                pb.crec[3 * chunk + 2] = make_uint4(Lc, head | (tail << 8), 0u, 0u);
             }
         }
       }
@@ -578,7 +579,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         const uint32_t *rw = reinterpret_cast<const uint32_t *>(pb.crec);
         // bits in front of this thread's records
         unsigned long long mine = 0;
-        for (int c = c0; c < c1; c++) mine += rw[8 * c + 4];             // L1 was invalidated by the fence above;
+        for (int c = c0; c < c1; c++) mine += rw[12 * c + 8];            // L1 was invalidated by the fence above;
                                                                         // the second sweep below hits it
         unsigned long long incl = mine;
 #pragma unroll
@@ -592,15 +593,12 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         for (int w = 0; w < warp; w++) P += s_scan[w];
         __syncthreads();
         // 0xFF bytes of each record at its alignment; first pass leaves thread-local prefixes in Fc
-        uint32_t on_prev = c0 > 0 && c0 < n_c ? rw[8 * (c0 - 1) + 5] : 0u;
+        uint32_t on_prev = c0 > 0 && c0 < n_c ? rw[12 * (c0 - 1) + 9] : 0u;
         uint32_t nff = 0;
         for (int c = c0; c < c1; c++) {
-            const uint4 fa = pb.crec[2 * c];
-            const uint32_t Lc = rw[8 * c + 4], on = rw[8 * c + 5];
+            const uint32_t Lc = rw[12 * c + 8], on = rw[12 * c + 9];
             const uint32_t r = (uint32_t)P & 7u;
-            const uint32_t lo = (r & 4u) ? fa.z : fa.x, hi = (r & 4u) ? fa.w : fa.y;
-            const uint32_t w2 = (r & 2u) ? hi : lo;
-            uint32_t cnt = (r & 1u) ? (w2 >> 16) : (w2 & 0xffffu);
+            uint32_t cnt = rw[12 * c + r];                              // the counter for this alignment
             if (c > 0) cnt += span_ff(on_prev, on, r);
             pb.Pc[c] = P;
             pb.Fc[c] = nff;
@@ -795,7 +793,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
 __host__ __device__ inline size_t ent_pass_bytes(int ntiles, int nchunks)
 {
     const size_t n = (size_t)ntiles, c = (size_t)nchunks;
-    return n * ENT_SCR_STRIDE * 4 + n * 4 + n * 16 + n * 4 + c * 32 + c * 8 + c * 4 + ENT_THREADS * 4 + 256;
+    return n * ENT_SCR_STRIDE * 4 + n * 4 + n * 16 + n * 4 + c * 48 + c * 8 + c * 4 + ENT_THREADS * 4 + 256;
 }
 
 }  // namespace icb
