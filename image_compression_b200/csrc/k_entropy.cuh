@@ -17,16 +17,18 @@
 //       (|x| >= 4*q_table, tables are monotone in quality) -- as compact 32-bit
 //       entries in scan order, one list per tile of 64 blocks.  Every block
 //       contributes a DC entry that also carries its predictor's raw DC.
-//   k_entropy_pass     once per search step: one warp per tile, one survivor per
-//       lane: quantise at the current tables, drop what became zero, run length =
-//       distance to the previous live entry, Huffman lookup, ZRL prefixes, the
-//       end-of-block code as a prefix of the next block's DC symbol, warp scan of
-//       code lengths, OR into a shared-memory bit window flushed to a per-tile
-//       scratch stream (tile-local alignment 0).  While flushing, 0xFF bytes are
-//       counted for all 8 possible start alignments; the last warp to finish a
-//       group of 32 tiles folds the group, and the last group to finish scans the
-//       group records into the exact stuffed size and runs the reference's
-//       bisection step (k_control.cuh).  Warps are persistent and never wait.
+//   k_entropy_pass     once per search step: one warp per tile, two survivors per
+//       lane and round: quantise at the current tables, drop what became zero, run
+//       length = distance to the previous live entry, Huffman lookup, ZRL prefixes,
+//       the end-of-block code as a prefix of the next block's DC symbol, ONE warp
+//       scan of code lengths per 64 entries, OR into a shared-memory bit window
+//       flushed to a per-tile scratch stream (tile-local alignment 0).  While
+//       flushing, 0xFF bytes are counted for all 8 possible start alignments.  The
+//       last warp of a chunk (the 8 tiles a CTA takes per round) to finish folds the
+//       chunk from shared memory; a CTA draws one ticket when it is done and the last
+//       CTA scans the chunk records into the exact stuffed size and runs the
+//       reference's bisection step (k_control.cuh).  CTAs are persistent and nobody
+//       waits for another CTA.
 //   k_entropy_emit     once per image, for the chosen pass only: re-reads the
 //       tile streams through a funnel shift at their absolute alignment, writes
 //       the stuffed bytes at their final offsets, the 623-byte header and EOI.
