@@ -355,7 +355,12 @@ int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, 
     }
     BeginArgs ba;
     ba.mode = mode; ba.q = q; ba.target = target; ba.table_mode = h->table_mode; ba.jfif_minor = h->jfif_minor;
-    CK(launch(k_entropy_prepare, dim3(nctas), dim3(ENT_THREADS), 0, s->stream, true, ep, ba));
+    {
+        const int need = (g.ntiles + PREP_WARPS - 1) / PREP_WARPS;
+        const int wave = h->devs[s->devi].sms * PREP_CTAS_PER_SM;
+        const int rounds = (need + wave - 1) / wave;             // tiles a warp takes
+        CK(launch(k_entropy_prepare, dim3((need + rounds - 1) / rounds), dim3(PREP_THREADS), 0, s->stream, true, ep, ba));
+    }
     h->kernels += 1;
     const int pgrid = pass_grid(g.ntiles, h->devs[s->devi].sms);
     for (int i = 0; i < npasses; i++) {

@@ -16,7 +16,8 @@
 //       non-zero at the HIGHEST quality any pass of this job can use
 //       (|x| >= 4*q_table, tables are monotone in quality) -- as compact 32-bit
 //       entries in scan order, one list per tile of 64 blocks.  Every block
-//       contributes a DC entry that also carries its predictor's raw DC.
+//       contributes a DC entry that also carries its predictor's raw DC.  One warp
+//       per tile, one lane per block (half a tile staged in shared memory at a time).
 //   k_entropy_pass     once per search step: one warp per tile, two survivors per
 //       lane and round: quantise at the current tables, drop what became zero, run
 //       length = distance to the previous live entry, Huffman lookup, ZRL prefixes,
@@ -123,84 +124,127 @@ __device__ __forceinline__ uint32_t span_ff(uint32_t ones_prev, uint32_t ones_cu
     return (r != 0u && (ones_prev >> 8) >= r && (ones_cur & 0xffu) >= 8u - r) ? 1u : 0u;
 }
 
-__global__ void __launch_bounds__(ENT_THREADS) k_entropy_prepare(const EntParams p, const BeginArgs ba)
+// Survivor extraction.  One warp per tile of 64 blocks, taken as two halves of 32: a half (4 KB of
+// zigzag int16) is staged in shared memory with coalesced 16-byte loads, rows padded to 144 bytes
+// so that the 16-byte reads of 32 lanes standing on 32 different rows touch every bank once.  Each
+// lane then owns one whole block: 64 threshold compares into a 64-bit mask, one warp scan for the
+// run starts, and a pop-lowest-bit loop that writes the block's entries.  The grid is one wave of
+// resident warps; a warp strides over tiles when the image has more tiles than that.
+constexpr int PREP_WARPS = 4;
+constexpr int PREP_THREADS = PREP_WARPS * 32;
+constexpr int PREP_CTAS_PER_SM = 8;
+constexpr int PREP_ROW = 144;
+
+__global__ void __launch_bounds__(PREP_THREADS, PREP_CTAS_PER_SM) k_entropy_prepare(const EntParams p, const BeginArgs ba)
 {
-    __shared__ __align__(16) unsigned short s_thr[2][64];
+    // thresholds as [chunk of 8][table][8]: both tables' 16-byte chunks sit in different banks
+    __shared__ __align__(16) unsigned short s_thr[8][2][8];
+    __shared__ __align__(16) unsigned char s_half[PREP_WARPS][32 * PREP_ROW];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     pdl_launch_dependents();
     // survivor thresholds: a coefficient is non-zero at quality q iff |x| >= 4 * table(q), and
     // table(q) never grows with q, so the tables of the highest quality this job can reach (ba.q:
     // every midpoint lies below hi <= q) bound them all.  Zigzag order, computed by every CTA.
-    if (tid < 128) {
+    {
         const int tb = tid >> 6, k = tid & 63;
         const int nat = c_zigzag[k];
-        s_thr[tb][k] = (unsigned short)(scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], ba.q, ba.table_mode) << 2);
+        s_thr[k >> 3][tb][k & 7] =
+            (unsigned short)(scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], ba.q, ba.table_mode) << 2);
     }
     // the job's search state and first tables (consumed by the pass kernels that follow)
     // (nothing of the previous kernel of the stream, the transform, is touched by this)
 #ifdef ICB_TIMING
     if (blockIdx.x == 0 && tid == 0) p.st->dbg_k[0] = gtime();
 #endif
-    if (blockIdx.x == 0 && warp == ENT_WARPS - 1) begin_job(p.st, ba);
+    if (blockIdx.x == 0 && warp == PREP_WARPS - 1) begin_job(p.st, ba);
     __syncthreads();
     pdl_wait();                     // the coefficients are complete and visible from here on
-    const int tile = blockIdx.x * ENT_WARPS + warp;
-    if (tile >= p.ntiles) return;
-    const int g = lane >> 3, j = lane & 7;
-    uint32_t *out = p.ent + (size_t)tile * ENT_CAP;
-    uint32_t cnt = 0;
-    for (int it = 0; it < ENT_TILE_BLOCKS / 4; it++) {
-        const int b = tile * ENT_TILE_BLOCKS + it * 4 + g;
-        const bool valid = b < p.nblocks;
-        const int cidx = b % 6;
-        const uint32_t tb = cidx >= 4 ? 1u : 0u;
-        // DC predictor = previous block of the same component in scan order
-        int prev = b - 1;
-        bool has_prev = true;
-        if (cidx == 0) { prev = b - 3; has_prev = b >= 6; }
-        else if (cidx >= 4) { prev = b - 6; has_prev = b >= 6; }
-        uint4 raw = make_uint4(0, 0, 0, 0);
-        int xp = 0;
-        if (valid) {
-            raw = __ldg(reinterpret_cast<const uint4 *>(p.coef) + (size_t)b * 8 + j);
-            if (j == 0 && has_prev) xp = (int)__ldg(p.coef + (size_t)prev * 64);
-        }
-        const uint4 tt = *reinterpret_cast<const uint4 *>(&s_thr[tb][8 * j]);
-        const uint32_t rw[4] = {raw.x, raw.y, raw.z, raw.w};
-        const uint32_t tw[4] = {tt.x, tt.y, tt.z, tt.w};
-        int x[8];
-        uint32_t m8 = 0;
+    unsigned char *ts = s_half[warp];
+    const unsigned char *rp = ts + lane * PREP_ROW;
+    for (int tile = blockIdx.x * PREP_WARPS + warp; tile < p.ntiles; tile += gridDim.x * PREP_WARPS) {
+        uint32_t *out = p.ent + (size_t)tile * ENT_CAP;
+        uint32_t base = 0;
+#pragma unroll 1
+        for (int half = 0; half < 2; half++) {
+            const int b0 = tile * ENT_TILE_BLOCKS + half * 32;
+            const int nb = p.nblocks - b0;              // rows of this half that exist (may be <= 0)
+            if (nb <= 0) break;
+            {
+                const uint4 *src = reinterpret_cast<const uint4 *>(p.coef) + (size_t)b0 * 8;
+                uint4 v[8];
 #pragma unroll
-        for (int i = 0; i < 8; i++) {
-            x[i] = (i & 1) ? ((int)rw[i >> 1] >> 16) : ((int)(rw[i >> 1] << 16) >> 16);
-            const uint32_t thr = (i & 1) ? (tw[i >> 1] >> 16) : (tw[i >> 1] & 0xffffu);
-            m8 |= ((uint32_t)abs(x[i]) >= thr ? 1u : 0u) << i;
-        }
-        if (j == 0) m8 |= 1u;                               // DC always codes a symbol
-        if (!valid) m8 = 0;
-        const uint32_t npop = __popc(m8);
-        uint32_t incl = npop;
+                for (int r = 0; r < 8; r++) {
+                    const int idx = r * 32 + lane;
+                    v[r] = (idx >> 3) < nb ? __ldg(src + idx) : make_uint4(0, 0, 0, 0);
+                }
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
-            if (lane >= o) incl += t;
-        }
-        uint32_t rank = cnt + incl - npop;
-        cnt += __shfl_sync(0xffffffffu, incl, 31);
-        const uint32_t tag = (tb << 17) | ((uint32_t)(8 * j) << 18);
-#pragma unroll
-        for (int i = 0; i < 8; i++) {
-            if ((m8 >> i) & 1u) {
-                uint32_t e;
-                if (i == 0 && j == 0)
-                    e = ENTRY_DC | (tb << 17) | ((uint32_t)xp << 18) | ((uint32_t)x[0] & 0xffffu);
-                else
-                    e = ((uint32_t)x[i] & 0xffffu) | (tag + ((uint32_t)i << 18));
-                out[rank++] = e;
+                for (int r = 0; r < 8; r++) {
+                    const int idx = r * 32 + lane;
+                    *reinterpret_cast<uint4 *>(ts + (idx >> 3) * PREP_ROW + (idx & 7) * 16) = v[r];
+                }
             }
+            __syncwarp();
+            const int b = b0 + lane;
+            const int cidx = b % 6;
+            const uint32_t tb = cidx >= 4 ? 1u : 0u;
+            uint32_t lo = 0, hi = 0;
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const uint4 raw = *reinterpret_cast<const uint4 *>(rp + 16 * j);
+                const uint4 tt = *reinterpret_cast<const uint4 *>(&s_thr[j][tb][0]);
+                const uint32_t rw[4] = {raw.x, raw.y, raw.z, raw.w};
+                const uint32_t tw[4] = {tt.x, tt.y, tt.z, tt.w};
+#pragma unroll
+                for (int i = 0; i < 8; i++) {
+                    const int x = (i & 1) ? ((int)rw[i >> 1] >> 16) : ((int)(rw[i >> 1] << 16) >> 16);
+                    const uint32_t thr = (i & 1) ? (tw[i >> 1] >> 16) : (tw[i >> 1] & 0xffffu);
+                    const int bit = 8 * j + i;
+                    if ((uint32_t)abs(x) >= thr) {
+                        if (bit < 32) lo |= 1u << bit; else hi |= 1u << (bit - 32);
+                    }
+                }
+            }
+            lo |= 1u;                                       // DC always codes a symbol
+            if (lane >= nb) { lo = 0; hi = 0; }
+            const uint32_t cnt = __popc(lo) + __popc(hi);
+            uint32_t incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t t = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += t;
+            }
+            uint32_t rank = base + incl - cnt;
+            base += __shfl_sync(0xffffffffu, incl, 31);
+            if (lane < nb) {
+                const uint32_t tag = tb << 17;
+                // DC predictor = previous block of the same component in scan order
+                int prev = b - 1;
+                bool has_prev = true;
+                if (cidx == 0) { prev = b - 3; has_prev = b >= 6; }
+                else if (cidx >= 4) { prev = b - 6; has_prev = b >= 6; }
+                int xp = 0;
+                if (has_prev)
+                    xp = prev >= b0 ? (int)*reinterpret_cast<const short *>(ts + (prev - b0) * PREP_ROW)
+                                    : (int)__ldg(p.coef + (size_t)prev * 64);
+                out[rank++] = ENTRY_DC | tag | ((uint32_t)xp << 18) |
+                              (uint32_t)*reinterpret_cast<const unsigned short *>(rp);
+                uint32_t m = lo & ~1u;
+                while (m) {
+                    const uint32_t k = __ffs(m) - 1;
+                    m &= m - 1;
+                    out[rank++] = (uint32_t)*reinterpret_cast<const unsigned short *>(rp + 2 * k) | tag | (k << 18);
+                }
+                m = hi;
+                while (m) {
+                    const uint32_t k = __ffs(m) + 31;
+                    m &= m - 1;
+                    out[rank++] = (uint32_t)*reinterpret_cast<const unsigned short *>(rp + 2 * k) | tag | (k << 18);
+                }
+            }
+            __syncwarp();                                   // the rows are free for the next half
         }
+        if (lane == 0) p.ent_cnt[tile] = base;
     }
-    if (lane == 0) p.ent_cnt[tile] = cnt;
 }
 
 
