@@ -363,11 +363,18 @@ int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, 
     }
     h->kernels += 1;
     const int pgrid = pass_grid(g.ntiles, h->devs[s->devi].sms);
+    // searches that start high walk hi down by halves: prune the survivor lists between passes
+    static const float prune_from = [] { const char *e = getenv("ICB_PRUNE_FROM"); return e ? (float)atof(e) : 0.45f; }();
+    const bool prune = mode == MODE_SEARCH && q >= prune_from;
     for (int i = 0; i < npasses; i++) {
         if (pass_ev) cudaEventRecord(pass_ev[2 * i], s->stream);
         CK(launch(k_entropy_pass, dim3(pgrid), dim3(ENT_THREADS), 0, s->stream, pass_ev == nullptr, ep));
         if (pass_ev) cudaEventRecord(pass_ev[2 * i + 1], s->stream);
         h->kernels += 1;
+        if (prune && i + 1 < npasses) {
+            CK(launch(k_entropy_prune, dim3(nctas), dim3(ENT_THREADS), 0, s->stream, pass_ev == nullptr, ep, i));
+            h->kernels += 1;
+        }
     }
     if (emit) {
         CK(launch(k_entropy_emit, dim3(nctas), dim3(ENT_THREADS), 0, s->stream, pass_ev == nullptr, ep, s->d_out,

@@ -112,6 +112,9 @@ struct FitState {
     unsigned long long dbg_t[8][4]; // per pass: globaltimer at kernel start / tail start / step start / tail end
     unsigned long long ff_total;    // stuffed 0x00 bytes (= number of 0xFF data bytes)
     unsigned long long total_bits;  // entropy-coded bits before padding
+    // quality whose tables bound the survivor lists as they stand after the k-th pass of a search
+    // (k_entropy_prune number k reads [k] and writes [k + 1])
+    float list_q[12];
 };
 
 static_assert(offsetof(FitState, iter) == 16 && offsetof(FitState, cur_buf) == 32, "k_entropy_pass reads these as int4");

@@ -153,6 +153,7 @@ __device__ void begin_job(FitState *st, const BeginArgs &b)
 {
     const int lane = threadIdx.x & 31;
     if (lane == 0) {
+        st->list_q[0] = b.q;
         st->lo = 0.0f;
         st->hi = b.q;
         st->best = -1.0f;
@@ -182,6 +183,53 @@ __device__ void begin_job(FitState *st, const BeginArgs &b)
     q0 = __shfl_sync(0xffffffffu, q0, 0);
     if (go)
         for (int t = lane; t < 128; t += 32) table_entry(&st->tab[0], t, q0, b.table_mode);
+}
+
+// Between two passes of a long search: when the upper end of the bracket has dropped well below
+// the quality the survivor lists were built for, every midpoint still to come quantises with
+// tables at least as coarse as those of hi, so entries below the thresholds of hi are dead for the
+// rest of the job.  One warp per tile compacts its list in place (DC entries always stay: they
+// carry the block boundaries).  A no-op otherwise; only enqueued for searches that start high.
+constexpr float PRUNE_RATIO = 0.8f;
+
+__global__ void __launch_bounds__(ENT_THREADS) k_entropy_prune(const EntParams p, int k)
+{
+    __shared__ unsigned short s_thr[2][64];
+    __shared__ float s_hi;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    pdl_launch_dependents();
+    pdl_wait();                                     // the step of the pass before this is visible
+    FitState *st = p.st;
+    if (tid == 0) {
+        const float hi = st->hi, lq = st->list_q[k];
+        const bool go = !st->done && st->cur_valid && hi <= lq * PRUNE_RATIO;
+        s_hi = go ? hi : -1.0f;
+        if (blockIdx.x == 0) st->list_q[k + 1] = go ? hi : lq;
+    }
+    __syncthreads();
+    const float hi = s_hi;
+    if (hi < 0.0f) return;
+    if (tid < 128) {
+        const int tb = tid >> 6, z = tid & 63;
+        const int nat = c_zigzag[z];
+        s_thr[tb][z] = (unsigned short)(scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], hi, st->table_mode) << 2);
+    }
+    __syncthreads();
+    const int tile = blockIdx.x * ENT_WARPS + warp;
+    if (tile >= p.ntiles) return;
+    uint32_t *list = p.ent + (size_t)tile * ENT_CAP;
+    const uint32_t n = p.ent_cnt[tile];
+    uint32_t w = 0;
+    for (uint32_t i0 = 0; i0 < n; i0 += 32) {
+        const uint32_t i = i0 + lane;
+        const uint32_t e = i < n ? list[i] : 0u;
+        const int x = (int)(short)(e & 0xffffu);
+        const bool keep = i < n && ((e & ENTRY_DC) != 0u || (uint32_t)abs(x) >= s_thr[(e >> 17) & 1u][(e >> 18) & 63u]);
+        const uint32_t m = __ballot_sync(0xffffffffu, keep);    // every lane holds its entry before any store
+        if (keep) list[w + __popc(m & ((1u << lane) - 1u))] = e;
+        w += __popc(m);
+    }
+    if (lane == 0) p.ent_cnt[tile] = w;
 }
 
 }  // namespace icb
