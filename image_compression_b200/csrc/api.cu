@@ -353,26 +353,33 @@ int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, 
         ep.buf[b].Fc = reinterpret_cast<unsigned int *>(base);          base += c * 4;
         ep.buf[b].Fb = reinterpret_cast<unsigned int *>(base);
     }
+    // searches that start high walk hi down by halves: the first lists are built for the first
+    // midpoint only (rebuilt for hi if that pass fits) and pruned between passes as hi drops
+    static const float prune_from = [] { const char *e = getenv("ICB_PRUNE_FROM"); return e ? (float)atof(e) : 0.45f; }();
+    const bool prune = mode == MODE_SEARCH && q >= prune_from && npasses > 1;
     BeginArgs ba;
     ba.mode = mode; ba.q = q; ba.target = target; ba.table_mode = h->table_mode; ba.jfif_minor = h->jfif_minor;
-    {
-        const int need = (g.ntiles + PREP_WARPS - 1) / PREP_WARPS;
-        const int wave = h->devs[s->devi].sms * PREP_CTAS_PER_SM;
-        const int rounds = (need + wave - 1) / wave;             // tiles a warp takes
-        CK(launch(k_entropy_prepare, dim3((need + rounds - 1) / rounds), dim3(PREP_THREADS), 0, s->stream, true, ep, ba));
-    }
+    ba.list_q = prune ? (0.0f + q) / 2.0f : q;                   // = the first midpoint (:168)
+    ba.pad = 0;
+    const int pneed = (g.ntiles + PREP_WARPS - 1) / PREP_WARPS;
+    const int pwave = h->devs[s->devi].sms * PREP_CTAS_PER_SM;
+    const int prounds = (pneed + pwave - 1) / pwave;             // tiles a warp takes
+    const dim3 prep_grid((pneed + prounds - 1) / prounds);
+    CK(launch(k_entropy_prepare<false>, prep_grid, dim3(PREP_THREADS), 0, s->stream, true, ep, ba));
     h->kernels += 1;
     const int pgrid = pass_grid(g.ntiles, h->devs[s->devi].sms);
-    // searches that start high walk hi down by halves: prune the survivor lists between passes
-    static const float prune_from = [] { const char *e = getenv("ICB_PRUNE_FROM"); return e ? (float)atof(e) : 0.45f; }();
-    const bool prune = mode == MODE_SEARCH && q >= prune_from;
+    const bool pdl = pass_ev == nullptr;
     for (int i = 0; i < npasses; i++) {
         if (pass_ev) cudaEventRecord(pass_ev[2 * i], s->stream);
-        CK(launch(k_entropy_pass, dim3(pgrid), dim3(ENT_THREADS), 0, s->stream, pass_ev == nullptr, ep));
+        CK(launch(k_entropy_pass, dim3(pgrid), dim3(ENT_THREADS), 0, s->stream, pdl, ep));
         if (pass_ev) cudaEventRecord(pass_ev[2 * i + 1], s->stream);
         h->kernels += 1;
         if (prune && i + 1 < npasses) {
-            CK(launch(k_entropy_prune, dim3(nctas), dim3(ENT_THREADS), 0, s->stream, pass_ev == nullptr, ep, i));
+            if (i == 0) {
+                CK(launch(k_entropy_prepare<true>, prep_grid, dim3(PREP_THREADS), 0, s->stream, pdl, ep, ba));
+                h->kernels += 1;
+            }
+            CK(launch(k_entropy_prune, dim3(nctas), dim3(ENT_THREADS), 0, s->stream, pdl, ep, i + 1));
             h->kernels += 1;
         }
     }

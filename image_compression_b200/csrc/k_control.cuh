@@ -153,7 +153,7 @@ __device__ void begin_job(FitState *st, const BeginArgs &b)
 {
     const int lane = threadIdx.x & 31;
     if (lane == 0) {
-        st->list_q[0] = b.q;
+        st->list_q[0] = b.list_q;
         st->lo = 0.0f;
         st->hi = b.q;
         st->best = -1.0f;
@@ -220,14 +220,25 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prune(const EntParams p
     uint32_t *list = p.ent + (size_t)tile * ENT_CAP;
     const uint32_t n = p.ent_cnt[tile];
     uint32_t w = 0;
-    for (uint32_t i0 = 0; i0 < n; i0 += 32) {
-        const uint32_t i = i0 + lane;
-        const uint32_t e = i < n ? list[i] : 0u;
-        const int x = (int)(short)(e & 0xffffu);
-        const bool keep = i < n && ((e & ENTRY_DC) != 0u || (uint32_t)abs(x) >= s_thr[(e >> 17) & 1u][(e >> 18) & 63u]);
-        const uint32_t m = __ballot_sync(0xffffffffu, keep);    // every lane holds its entry before any store
-        if (keep) list[w + __popc(m & ((1u << lane) - 1u))] = e;
-        w += __popc(m);
+    // four chunks of 32 in flight; a chunk's stores land at or below its own first slot, and every
+    // lane holds its entry of that chunk (it went into the ballot) before any of them
+    for (uint32_t i0 = 0; i0 < n; i0 += 128) {
+        uint32_t e[4];
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const uint32_t i = i0 + 32 * c + lane;
+            e[c] = i < n ? list[i] : 0u;
+        }
+#pragma unroll
+        for (int c = 0; c < 4; c++) {
+            const uint32_t i = i0 + 32 * c + lane;
+            const int x = (int)(short)(e[c] & 0xffffu);
+            const bool keep = i < n && ((e[c] & ENTRY_DC) != 0u ||
+                                        (uint32_t)abs(x) >= s_thr[(e[c] >> 17) & 1u][(e[c] >> 18) & 63u]);
+            const uint32_t m = __ballot_sync(0xffffffffu, keep);
+            if (keep) list[w + __popc(m & ((1u << lane) - 1u))] = e[c];
+            w += __popc(m);
+        }
     }
     if (lane == 0) p.ent_cnt[tile] = w;
 }

@@ -90,6 +90,8 @@ struct BeginArgs {
     float q;                        // initial quality (search) or the quality to encode at (single)
     long long target;
     int table_mode, jfif_minor;
+    float list_q;                   // quality the first survivor lists are built for (>= that of the first pass)
+    int pad;
 };
 
 // a2.1 / :158-200 -- defined in k_control.cuh
@@ -135,6 +137,13 @@ constexpr int PREP_THREADS = PREP_WARPS * 32;
 constexpr int PREP_CTAS_PER_SM = 8;
 constexpr int PREP_ROW = 144;
 
+//
+// REBUILD = false: the first kernel of a job (also starts the search state).  REBUILD = true: run once
+// after the first pass of a search whose lists were built for that pass's quality only (searches that
+// start high: the first midpoint usually does not fit, and then no later pass looks above it); if
+// the pass did fit, the coming midpoints lie above the lists' quality and the lists are rebuilt
+// from the dense coefficients for hi, otherwise this is a no-op.
+template <bool REBUILD>
 __global__ void __launch_bounds__(PREP_THREADS, PREP_CTAS_PER_SM) k_entropy_prepare(const EntParams p, const BeginArgs ba)
 {
     // thresholds as [chunk of 8][table][8]: both tables' 16-byte chunks sit in different banks
@@ -142,23 +151,38 @@ __global__ void __launch_bounds__(PREP_THREADS, PREP_CTAS_PER_SM) k_entropy_prep
     __shared__ __align__(16) unsigned char s_half[PREP_WARPS][32 * PREP_ROW];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     pdl_launch_dependents();
+    float tq = ba.list_q;
+    if (REBUILD) {
+        __shared__ float s_q;
+        pdl_wait();                 // the step of the first pass is visible
+        if (tid == 0) {
+            FitState *st = p.st;
+            const float lq = st->list_q[0], hi = st->hi;
+            const bool go = !st->done && st->cur_valid && st->cur_q > lq;
+            s_q = go ? hi : -1.0f;
+            if (blockIdx.x == 0) st->list_q[1] = go ? hi : lq;
+        }
+        __syncthreads();
+        tq = s_q;
+        if (tq < 0.0f) return;
+    }
     // survivor thresholds: a coefficient is non-zero at quality q iff |x| >= 4 * table(q), and
-    // table(q) never grows with q, so the tables of the highest quality this job can reach (ba.q:
-    // every midpoint lies below hi <= q) bound them all.  Zigzag order, computed by every CTA.
+    // table(q) never grows with q, so the tables of the highest quality the coming passes can reach
+    // (every midpoint lies below hi) bound them all.  Zigzag order, computed by every CTA.
     {
         const int tb = tid >> 6, k = tid & 63;
         const int nat = c_zigzag[k];
         s_thr[k >> 3][tb][k & 7] =
-            (unsigned short)(scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], ba.q, ba.table_mode) << 2);
+            (unsigned short)(scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], tq, ba.table_mode) << 2);
     }
     // the job's search state and first tables (consumed by the pass kernels that follow)
     // (nothing of the previous kernel of the stream, the transform, is touched by this)
 #ifdef ICB_TIMING
     if (blockIdx.x == 0 && tid == 0) p.st->dbg_k[0] = gtime();
 #endif
-    if (blockIdx.x == 0 && warp == PREP_WARPS - 1) begin_job(p.st, ba);
+    if (!REBUILD && blockIdx.x == 0 && warp == PREP_WARPS - 1) begin_job(p.st, ba);
     __syncthreads();
-    pdl_wait();                     // the coefficients are complete and visible from here on
+    if (!REBUILD) pdl_wait();       // the coefficients are complete and visible from here on
     unsigned char *ts = s_half[warp];
     const unsigned char *rp = ts + lane * PREP_ROW;
     for (int tile = blockIdx.x * PREP_WARPS + warp; tile < p.ntiles; tile += gridDim.x * PREP_WARPS) {

@@ -1,0 +1,61 @@
+"""-m gpu parity on seeded random cases: odd shapes, every starting quality class (lists built
+for q, lists built for the first midpoint and pruned / rebuilt), targets on both sides of every
+candidate size.  The oracle decides what is right; nothing here is shape- or quality-specific."""
+import numpy as np
+import pytest
+
+from image_compression_b200 import synth, LearnedParams
+
+pytestmark = pytest.mark.gpu
+
+QS = [1.0, 0.9, 0.75, 0.6, 0.5, 0.45, 0.44, 0.3, 0.25, 0.1, 0.05, 0.02]
+
+
+def _case(seed):
+    rng = np.random.default_rng(9000 + seed)
+    w = int(rng.integers(1, 700))
+    h = int(rng.integers(1, 500))
+    kind = seed % 3
+    if kind == 0:
+        img = synth.natural_image(seed, w, h)
+    elif kind == 1:
+        img = synth.noise_image(seed, w, h)
+    else:                                   # flat areas with a few hard edges: long zero runs, EOB-only blocks
+        img = np.full((h, w, 3), int(rng.integers(0, 256)), np.uint8)
+        for _ in range(4):
+            x0, y0 = int(rng.integers(0, w)), int(rng.integers(0, h))
+            img[y0: y0 + int(rng.integers(1, 64)), x0: x0 + int(rng.integers(1, 64))] = rng.integers(0, 256, 3)
+    q = QS[int(rng.integers(0, len(QS)))]
+    return rng, img, q
+
+
+@pytest.mark.parametrize("seed", range(36))
+def test_random_fit_matches_oracle(engine, oracle, seed):
+    rng, img, q = _case(seed)
+    # a target between the smallest and the largest size the search can see, or just outside
+    lo = oracle.encoded_size(img, 0.015625)
+    hi = oracle.encoded_size(img, q)
+    pick = int(rng.integers(0, 4))
+    if pick == 0:
+        target = int(rng.integers(lo, max(lo + 1, hi + 1)))
+    elif pick == 1:
+        target = hi + int(rng.integers(0, 50))            # everything fits: the search climbs to the top
+    elif pick == 2:
+        target = max(1, lo - int(rng.integers(1, 200)))   # nothing fits at scale 1: the scale loop runs
+    else:
+        target = oracle.encoded_size(img, q / 2) - int(rng.integers(0, 2))   # on the edge of the first midpoint
+    rc, ref, rq, rs, _, _ = oracle.jpg_fit(img, q, target)
+    r = engine.jpg_fit(img, q, target)
+    assert (r.status, r.best_q, r.scale) == (rc, rq, rs), (img.shape, q, target)
+    if rc == 0:
+        assert r.data == ref and len(r.data) <= target
+        # the learned parameters replay it in one encode (core/ImageCompressionJpg.java:216-238)
+        c = engine.jpg_fit(img, q, target, cached=LearnedParams(r.best_q, r.scale))
+        assert c.used_cache and c.data == ref
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_random_sizes_match_oracle(engine, oracle, seed):
+    rng, img, _ = _case(100 + seed)
+    qs = [float(k) / 128.0 for k in rng.integers(2, 128, 6)]
+    assert list(engine.jpg_sizes(img, qs)) == [oracle.encoded_size(img, q) for q in qs]
