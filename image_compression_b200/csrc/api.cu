@@ -100,6 +100,9 @@ struct icb_handle {
     std::atomic<uint64_t> images_done{0}, kernels{0}, passes{0}, h2d{0}, d2h{0};
     float last_xf_ms = 0, last_ent_ms = 0, last_total_ms = 0;
     int last_xf_launches = 0, last_ent_launches = 0;
+    // what the first midpoint of earlier searches of the same (w, h, q, target) did: key << 1 | failed
+    std::atomic<uint64_t> first_pass_seen[256];
+    icb_handle() { for (auto &e : first_pass_seen) e.store(0); }
 };
 
 namespace {
@@ -322,8 +325,40 @@ int pass_grid(int ntiles, int sms)
     return best_grid;
 }
 
+// Will the first midpoint (q / 2) of this search overshoot the target?  If so every later pass
+// looks below it, and the survivor lists are built for q / 2 and pruned as hi walks down; if not,
+// they are built for q once.  Only time depends on the answer, never a byte of the result: a wrong
+// guess costs one list rebuild.  The guess is what the same (w, h, q, target) did last time --
+// batches are runs of like images, the reason the reference keeps its LearnedParams cache
+// (CacheTools.java:14-21) -- else a bytes-per-pixel rule of thumb.
+uint64_t first_pass_key(int w, int hgt, float q, long long target)
+{
+    uint32_t qb;
+    memcpy(&qb, &q, 4);
+    uint64_t k = ((uint64_t)(uint32_t)w << 32 | (uint32_t)hgt) * 0x9E3779B97F4A7C15ull;
+    k ^= ((uint64_t)qb << 32 | (uint64_t)(target & 0xffffffffll)) * 0xC2B2AE3D27D4EB4Full;
+    k ^= k >> 29;
+    return (k | 1ull) & 0x7fffffffffffffffull;
+}
+
+bool expect_first_pass_fails(icb_handle *h, int w, int hgt, float q, long long target)
+{
+    static const int forced = [] { const char *e = getenv("ICB_PRUNE"); return e ? atoi(e) : -1; }();   // tuning knob
+    if (forced >= 0) return forced != 0;
+    const uint64_t k = first_pass_key(w, hgt, q, target);
+    const uint64_t v = h->first_pass_seen[k & 255].load(std::memory_order_relaxed);
+    if ((v >> 1) == k) return (v & 1) != 0;
+    return 0.4 * (double)(q * 0.5f) * (double)w * (double)hgt > (double)target;
+}
+
+void note_first_pass(icb_handle *h, int w, int hgt, float q, long long target, bool failed)
+{
+    const uint64_t k = first_pass_key(w, hgt, q, target);
+    h->first_pass_seen[k & 255].store(k << 1 | (failed ? 1u : 0u), std::memory_order_relaxed);
+}
+
 int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, int npasses, bool emit,
-                   long long dev_cap, cudaEvent_t *pass_ev = nullptr)
+                   long long dev_cap, cudaEvent_t *pass_ev = nullptr, bool expect_fail = false)
 {
     const Geom &g = s->geom;
     const int nctas = (g.ntiles + ENT_WARPS - 1) / ENT_WARPS;
@@ -353,10 +388,10 @@ int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, 
         ep.buf[b].Fc = reinterpret_cast<unsigned int *>(base);          base += c * 4;
         ep.buf[b].Fb = reinterpret_cast<unsigned int *>(base);
     }
-    // searches that start high walk hi down by halves: the first lists are built for the first
-    // midpoint only (rebuilt for hi if that pass fits) and pruned between passes as hi drops
-    static const float prune_from = [] { const char *e = getenv("ICB_PRUNE_FROM"); return e ? (float)atof(e) : 0.45f; }();
-    const bool prune = mode == MODE_SEARCH && q >= prune_from && npasses > 1;
+    // searches expected to overshoot at their first midpoint walk hi down from there: the first
+    // lists are built for that midpoint only (rebuilt for hi if the pass fits after all) and pruned
+    // between passes as hi drops
+    const bool prune = mode == MODE_SEARCH && expect_fail && npasses > 1;
     BeginArgs ba;
     ba.mode = mode; ba.q = q; ba.target = target; ba.table_mode = h->table_mode; ba.jfif_minor = h->jfif_minor;
     ba.list_q = prune ? (0.0f + q) / 2.0f : q;                   // = the first midpoint (:168)
@@ -481,7 +516,8 @@ int fit_enqueue_phase(icb_handle *h, Slot *s)
     if (j.phase == PH_CACHED)
         rc = enqueue_passes(h, s, MODE_SINGLE, j.cached_q, j.target, 1, true, cap);
     else
-        rc = enqueue_passes(h, s, MODE_SEARCH, j.init_q, j.target, max_search_iters(j.init_q), true, cap);
+        rc = enqueue_passes(h, s, MODE_SEARCH, j.init_q, j.target, max_search_iters(j.init_q), true, cap, nullptr,
+                            scale < 1.0 || expect_first_pass_fails(h, j.w, j.h, j.init_q, j.target));
     if (rc) return rc;
     CK(cudaMemcpyAsync(s->h_state, s->d_state, sizeof(FitState), cudaMemcpyDeviceToHost, s->stream));
     const size_t ncopy = (size_t)std::min<long long>((long long)j.out_cap, cap);
@@ -514,6 +550,7 @@ int fit_advance(icb_handle *h, Slot *s)
             j.scale = 1.0;
         }
     } else {
+        if (j.scale == 1.0) note_first_pass(h, j.w, j.h, j.init_q, j.target, !(st.best >= (0.0f + j.init_q) / 2.0f));
         if (st.best > 0.0f) {                            // :109-113
             ok = true;
             j.res.best_q = st.best;
@@ -1074,7 +1111,8 @@ int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q,
             rc = ensure_out(h, s, cap);
             if (rc) break;
             const int npairs = max_search_iters(init_q);
-            rc = enqueue_passes(h, s, MODE_SEARCH, init_q, target, npairs, true, cap, pe);
+            rc = enqueue_passes(h, s, MODE_SEARCH, init_q, target, npairs, true, cap, pe,
+                                expect_first_pass_fails(h, img->w, img->h, init_q, target));
             if (rc) break;
             cudaEventRecord(e2, s->stream);
             cudaError_t e = cudaMemcpyAsync(s->h_state, s->d_state, sizeof(FitState), cudaMemcpyDeviceToHost,

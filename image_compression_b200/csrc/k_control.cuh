@@ -189,7 +189,8 @@ __device__ void begin_job(FitState *st, const BeginArgs &b)
 // the quality the survivor lists were built for, every midpoint still to come quantises with
 // tables at least as coarse as those of hi, so entries below the thresholds of hi are dead for the
 // rest of the job.  One warp per tile compacts its list in place (DC entries always stay: they
-// carry the block boundaries).  A no-op otherwise; only enqueued for searches that start high.
+// carry the block boundaries).  A no-op otherwise; only enqueued for searches the host expects to
+// overshoot at their first midpoint (api.cu expect_first_pass_fails).
 constexpr float PRUNE_RATIO = 0.8f;
 
 __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prune(const EntParams p, int k)

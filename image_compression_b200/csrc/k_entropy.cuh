@@ -139,8 +139,8 @@ constexpr int PREP_ROW = 144;
 
 //
 // REBUILD = false: the first kernel of a job (also starts the search state).  REBUILD = true: run once
-// after the first pass of a search whose lists were built for that pass's quality only (searches that
-// start high: the first midpoint usually does not fit, and then no later pass looks above it); if
+// after the first pass of a search whose lists were built for that pass's quality only (the host
+// expects the first midpoint not to fit, and then no later pass looks above it); if
 // the pass did fit, the coming midpoints lie above the lists' quality and the lists are rebuilt
 // from the dense coefficients for hi, otherwise this is a no-op.
 template <bool REBUILD>

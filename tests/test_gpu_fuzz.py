@@ -59,3 +59,38 @@ def test_random_sizes_match_oracle(engine, oracle, seed):
     rng, img, _ = _case(100 + seed)
     qs = [float(k) / 128.0 for k in rng.integers(2, 128, 6)]
     assert list(engine.jpg_sizes(img, qs)) == [oracle.encoded_size(img, q) for q in qs]
+
+
+_FORCED = r"""
+import sys
+sys.path.insert(0, %r)
+import numpy as np
+import image_compression_b200 as pkg
+from image_compression_b200 import synth
+from oracle import oracle
+bad = 0
+with pkg.Engine(slots_per_gpu=2) as eng:
+    for seed, (w, h, q) in enumerate([(640, 480, 1.0), (333, 251, 0.25), (801, 603, 0.75), (97, 1025, 0.5)]):
+        img = synth.natural_image(700 + seed, w, h)
+        for frac in (0.02, 0.3, 0.7, 1.1):
+            target = int(oracle.encoded_size(img, q) * frac)
+            rc, ref, rq, rs, _, _ = oracle.jpg_fit(img, q, target)
+            r = eng.jpg_fit(img, q, target)
+            ok = (r.status, r.best_q, r.scale) == (rc, rq, rs) and (rc != 0 or r.data == ref)
+            bad += 0 if ok else 1
+print("BAD", bad)
+"""
+
+
+@pytest.mark.parametrize("forced", ["0", "1"])
+def test_both_list_strategies_give_the_same_bytes(forced):
+    """The host only guesses which way the first midpoint goes (api.cu expect_first_pass_fails); force
+    the guess both ways (ICB_PRUNE is read once per process) and compare every result with the oracle."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, ICB_PRUNE=forced)
+    out = subprocess.run([sys.executable, "-c", _FORCED % root], env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert "BAD 0" in out.stdout, out.stdout[-500:]
