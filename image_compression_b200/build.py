@@ -11,7 +11,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libimgcomp_b200.so")
 SOURCES = ["api.cu"]
-DEPS = ["api.cu", "common.cuh", "k_transform.cuh", "k_entropy.cuh", "k_control.cuh", "k_resize.cuh",
+DEPS = ["api.cu", "common.cuh", "xf_arith.cuh", "k_transform.cuh", "k_entropy.cuh", "k_control.cuh", "k_resize.cuh",
         os.path.join("..", "..", "include", "imgcomp_b200.h")]
 
 
