@@ -29,6 +29,7 @@ ABI_SYMBOLS = [
     "icb_subsample_factor", "icb_subsample",
     "icb_submit_jpg_fit", "icb_wait", "icb_image_upload", "icb_image_free",
     "icb_submit_jpg_fit_image", "icb_submit_resize_image", "icb_stats", "icb_profile_jpg_fit_image",
+    "icb_profile_transform_series",
     "icb_mark", "icb_elapsed_ms",
 ]
 
@@ -112,6 +113,8 @@ def load_library(build_if_missing: bool = True):
     L.icb_profile_jpg_fit_image.argtypes = [vp, vp, C.c_float, C.c_int64, C.c_int, C.POINTER(C.c_float),
                                             C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float),
                                             C.POINTER(C.c_int)]
+    L.icb_profile_transform_series.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int, C.POINTER(C.c_float),
+                                               C.POINTER(C.c_int)]
     L.icb_mark.argtypes = [vp, C.c_int, C.c_int]
     L.icb_elapsed_ms.argtypes = [vp, C.c_int, C.POINTER(C.c_float)]
     _lib = L
@@ -470,6 +473,15 @@ class Engine:
             raise self._err(rc)
         return dict(transform_ms=float(a.value), search_ms=float(b.value), total_ms=float(c.value),
                     entropy_kernel_ms=float(d.value), entropy_kernel_launches=int(n.value))
+
+    def profile_transform_series(self, img_handles, reps: int = 4):
+        """-> (ms per transform launch, launches timed): the images' transforms back to back on one stream"""
+        arr = (C.c_void_p * len(img_handles))(*[getattr(x, "value", x) for x in img_handles])
+        ms, n = C.c_float(0), C.c_int(0)
+        rc = self._L.icb_profile_transform_series(self._h, arr, len(img_handles), reps, C.byref(ms), C.byref(n))
+        if rc:
+            raise self._err(rc)
+        return float(ms.value), int(n.value)
 
     def mark(self, device_index: int, which: int):
         rc = self._L.icb_mark(self._h, device_index, which)

@@ -278,8 +278,8 @@ int enqueue_transform(icb_handle *h, Slot *s, const unsigned char *d_px, int w, 
     if (cr != CUDA_SUCCESS) return fail(h, ICB_ERR_CUDA, "cuTensorMapEncodeTiled failed");
     const int tiles_per_row = (g.mcu_cols + TILE_MCUS - 1) / TILE_MCUS;
     const int ntiles = tiles_per_row * g.mcu_rows;
-    static const int xf_cps = [] { const char *e = getenv("ICB_XF_CPS"); return e ? atoi(e) : 4; }();   // tuning knob
-    const int grid = std::min(ntiles, h->devs[s->devi].sms * std::max(1, std::min(4, xf_cps)));
+    static const int xf_cps = [] { const char *e = getenv("ICB_XF_CPS"); return e ? atoi(e) : XF_CTAS; }();   // tuning knob
+    const int grid = std::min(ntiles, h->devs[s->devi].sms * std::max(1, std::min(XF_CTAS, xf_cps)));
     if (g.bgr)
         k_transform<true><<<grid, XF_THREADS, XF_SMEM_BYTES, s->stream>>>(tmap, g, s->d_coef, tiles_per_row, ntiles);
     else
@@ -1082,6 +1082,41 @@ int icb_stats(icb_handle *h, icb_stats_t *out)
     out->last_transform_launches = h->last_xf_launches;
     out->last_entropy_launches = h->last_ent_launches;
     return ICB_OK;
+}
+
+int icb_profile_transform_series(icb_handle *h, const icb_image *const *imgs, int n, int reps, float *ms_per_launch,
+                                 int *launches)
+{
+    if (!h || !imgs || n < 1 || reps < 1) return ICB_ERR_INVALID;
+    for (int i = 0; i < n; i++) {
+        if (!imgs[i] || imgs[i]->devi != imgs[0]->devi) return ICB_ERR_INVALID;
+        if (imgs[i]->fmt != ICB_FMT_RGB8 && imgs[i]->fmt != ICB_FMT_BGR8) return fail(h, ICB_ERR_UNSUPPORTED, "format");
+    }
+    Slot *s = acquire_slot(h, imgs[0]->devi);
+    int rc = ICB_OK;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    do {
+        if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess || cudaEventCreate(&e0) != cudaSuccess ||
+            cudaEventCreate(&e1) != cudaSuccess) { rc = ICB_ERR_CUDA; break; }
+        for (int r = -1; r < reps && !rc; r++) {            // round -1 is the untimed warm-up
+            if (r == 0) cudaEventRecord(e0, s->stream);
+            for (int i = 0; i < n && !rc; i++)
+                rc = enqueue_transform(h, s, imgs[i]->d_px, imgs[i]->w, imgs[i]->h, imgs[i]->pitch, imgs[i]->fmt);
+        }
+        if (rc) break;
+        cudaEventRecord(e1, s->stream);
+        cudaError_t e = cudaStreamSynchronize(s->stream);
+        if (e != cudaSuccess) { rc = fail(h, ICB_ERR_CUDA, "profile", e); break; }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (ms_per_launch) *ms_per_launch = ms / (float)(n * reps);
+        if (launches) *launches = n * reps;
+    } while (0);
+    if (rc) cudaStreamSynchronize(s->stream);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    release_slot(h, s);
+    return rc;
 }
 
 int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q, int64_t target, int reps,

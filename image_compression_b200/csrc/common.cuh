@@ -9,6 +9,10 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#ifndef ICB_ENT_TILE
+#define ICB_ENT_TILE 128        // blocks per entropy tile (build knob for A/B runs; a power of two >= 32)
+#endif
+
 namespace icb {
 
 // ---- programmatic dependent launch (sm_90+): the kernels of one fit form a chain on one stream;
@@ -32,7 +36,7 @@ struct Geom {
     int yblk_w, yblk_h;     // real luma block counts
     int crows_real;         // ceil(h/2): downsampled rows that come from pixels
     int nblocks;            // 6 * mcu_cols * mcu_rows
-    int ntiles;             // entropy tiles = ceil(nblocks / 64)
+    int ntiles;             // entropy tiles = ceil(nblocks / ENT_TILE_BLOCKS)
 };
 
 __host__ __device__ inline Geom make_geom(int w, int h, int pitch, int bgr)
@@ -45,7 +49,7 @@ __host__ __device__ inline Geom make_geom(int w, int h, int pitch, int bgr)
     g.yblk_h = (h + 7) >> 3;
     g.crows_real = (h + 1) >> 1;
     g.nblocks = 6 * g.mcu_cols * g.mcu_rows;
-    g.ntiles = (g.nblocks + 63) >> 6;       // ENT_TILE_BLOCKS = 64
+    g.ntiles = (g.nblocks + ICB_ENT_TILE - 1) / ICB_ENT_TILE;
     return g;
 }
 
@@ -55,17 +59,25 @@ constexpr int TILE_ROW_BYTES = TILE_MCUS * 48;      // 768 B of RGB per pixel ro
 constexpr int TILE_IN_BYTES = TILE_ROW_BYTES * 16;  // 12 KB per TMA box
 constexpr int TILE_BLOCKS = TILE_MCUS * 6;          // 96 blocks
 constexpr int XF_THREADS = 128;
-constexpr int XF_STAGES = 2;
+#ifndef ICB_XF_STAGES
+#define ICB_XF_STAGES 2
+#endif
+#ifndef ICB_XF_CTAS
+#define ICB_XF_CTAS 6
+#endif
+constexpr int XF_STAGES = ICB_XF_STAGES;            // TMA boxes in flight per CTA
+constexpr int XF_CTAS = ICB_XF_CTAS;                // resident CTAs per SM the kernel is compiled for (register cap)
 
 // ---- entropy pass tiling ----
-constexpr int ENT_TILE_BLOCKS = 64;                 // blocks per warp tile
+constexpr int ENT_TILE_BLOCKS = ICB_ENT_TILE;       // blocks per warp tile (a multiple of 32)
+constexpr int ENT_TILE_SHIFT = ENT_TILE_BLOCKS == 32 ? 5 : ENT_TILE_BLOCKS == 64 ? 6 : ENT_TILE_BLOCKS == 128 ? 7 : 8;
 constexpr int ENT_WARPS = 8;
 constexpr int ENT_THREADS = ENT_WARPS * 32;
 // worst case per block: DC 9+11 bits, 63 x (16+10) bits = 1658 bits -> 208 B
 constexpr int ENT_SCR_STRIDE = (ENT_TILE_BLOCKS * 208) / 4 + 4;    // scratch words per tile
 constexpr int ENT_WIN = 256;                        // shared-memory bit window per warp (words)
 constexpr int ENT_WSTRIDE = ENT_WIN + 4;
-static_assert(ENT_TILE_BLOCKS == 64, "make_geom computes ntiles with a shift by 6");
+static_assert(ENT_TILE_BLOCKS == 1 << ENT_TILE_SHIFT && ENT_TILE_BLOCKS * 208 < 65536, "tile: power of two; 0xFF bytes of a tile fit 16 bits");
 constexpr int ENT_RING = 16;                        // CTA rounds whose tile records fit in shared memory at once
 constexpr int ENT_CAP = ENT_TILE_BLOCKS * 64;       // survivor entries per tile, worst case
 
@@ -175,6 +187,6 @@ __constant__ unsigned char c_ac_vals[2][162] = {
 // Global memory, not __constant__: every CTA of the entropy pass copies the table into shared
 // memory with one coalesced load per thread (an indexed constant load replays 32 times per warp).
 constexpr int HUF_WORDS = 512 + 32;
-__device__ unsigned int g_huf[HUF_WORDS];
+__device__ __align__(16) unsigned int g_huf[HUF_WORDS];
 
 }  // namespace icb

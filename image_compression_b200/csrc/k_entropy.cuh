@@ -189,7 +189,7 @@ __global__ void __launch_bounds__(PREP_THREADS, PREP_CTAS_PER_SM) k_entropy_prep
         uint32_t *out = p.ent + (size_t)tile * ENT_CAP;
         uint32_t base = 0;
 #pragma unroll 1
-        for (int half = 0; half < 2; half++) {
+        for (int half = 0; half < ENT_TILE_BLOCKS / 32; half++) {
             const int b0 = tile * ENT_TILE_BLOCKS + half * 32;
             const int nb = p.nblocks - b0;              // rows of this half that exist (may be <= 0)
             if (nb <= 0) break;
@@ -283,10 +283,10 @@ __device__ __forceinline__ uint32_t ff_starts(uint32_t a, uint32_t b)
 
 __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
 {
-    __shared__ uint32_t s_huf[512 + 32];            // AC: table * 256 + run * 16 + size;  DC: 512 + table * 16 + size
+    __shared__ __align__(16) uint32_t s_huf[512 + 32];          // AC: table * 256 + run * 16 + size;  DC: 512 + table * 16 + size
     __shared__ __align__(16) uint2 s_qt[128];       // quantiser by key = 2 * pos + table
     __shared__ int4 s_ctl[6];                       // control block of FitState as the pass found it
-    __shared__ uint32_t s_win[ENT_WARPS * ENT_WSTRIDE];
+    __shared__ __align__(16) uint32_t s_win[ENT_WARPS * ENT_WSTRIDE];
     __shared__ __align__(16) uint32_t s_rec[ENT_RING][ENT_WARPS][8];    // tile records by CTA round: ff (4 words), L, ones
     __shared__ unsigned int s_arr[ENT_RING];        // warps of the round's chunk that have finished their tile
     __shared__ unsigned long long s_scan[ENT_WARPS];
@@ -306,9 +306,10 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
     ICB_STAMP();                    // 0: entry
     pdl_launch_dependents();
     // set-up that does not depend on the previous pass: runs while that pass drains
-    for (int i = tid; i < HUF_WORDS; i += ENT_THREADS) s_huf[i] = __ldg(g_huf + i);
+    static_assert(HUF_WORDS % 4 == 0 && HUF_WORDS / 4 <= ENT_THREADS && ENT_WSTRIDE % 4 == 0, "16-byte set-up copies");
+    if (tid < HUF_WORDS / 4) reinterpret_cast<uint4 *>(s_huf)[tid] = __ldg(reinterpret_cast<const uint4 *>(g_huf) + tid);
     const uint32_t wbase = warp * ENT_WSTRIDE;
-    for (int i = lane; i < ENT_WSTRIDE; i += 32) s_win[wbase + i] = 0;
+    for (int i = lane; i < ENT_WSTRIDE / 4; i += 32) reinterpret_cast<uint4 *>(s_win + wbase)[i] = make_uint4(0, 0, 0, 0);
     if (tid < ENT_RING) s_arr[tid] = 0;
     ICB_STAMP();                    // 1: tables requested, window zeroed
     pdl_wait();                     // the previous pass ran its bisection step: st is final
@@ -413,7 +414,8 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
                 const uint32_t c0 = s_win[wbase + nf], c1 = s_win[wbase + nf + 1], c2 = s_win[wbase + nf + 2];
                 for (uint32_t w = lane; w < nf; w += 32) scr[flushed + w] = s_win[wbase + w];
                 __syncwarp();
-                for (uint32_t w = lane; w < nf + 3; w += 32) s_win[wbase + w] = 0;
+                for (uint32_t w = 4 * lane; w < nf + 3; w += 128)           // (words past nf + 2 are zero already)
+                    *reinterpret_cast<uint4 *>(s_win + wbase + w) = make_uint4(0, 0, 0, 0);
                 __syncwarp();
                 if (lane == 0) { s_win[wbase] = c0; s_win[wbase + 1] = c1; s_win[wbase + 2] = c2; }
                 flushed += nf;
@@ -565,7 +567,8 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             tail_bits = min(nbv, (uint32_t)(__ffs(~last) - 1));
         }
         __syncwarp();
-        for (uint32_t w = lane; w < nw + 3; w += 32) s_win[wbase + w] = 0;     // window clean for the next tile
+        for (uint32_t w = 4 * lane; w < nw + 3; w += 128)                      // window clean for the next tile
+            *reinterpret_cast<uint4 *>(s_win + wbase + w) = make_uint4(0, 0, 0, 0);   // (rounds up: the stride has room)
         if (lane == 0) {
             // counters are indexed by the tile's absolute start offset r = (8 - s) & 7
             const uint4 fpk = make_uint4(f[0] | (f[7] << 16), f[6] | (f[5] << 16), f[4] | (f[3] << 16),

@@ -99,7 +99,7 @@ __device__ __forceinline__ int samp_chunk(int blk, int chunk)     // in 16-byte 
 }
 
 template <bool BGR>
-__global__ void __launch_bounds__(XF_THREADS, 4)
+__global__ void __launch_bounds__(XF_THREADS, XF_CTAS)
 k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__restrict__ coef,
             int tiles_per_row, int ntiles)
 {
@@ -128,6 +128,7 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
         }
     }
 
+    const int cta_slot = blockIdx.x / max(1, (int)(gridDim.x + XF_CTAS - 1) / XF_CTAS);    // CTAs of one SM are gridDim / XF_CTAS apart
     int k = 0;
     for (int t = blockIdx.x; t < ntiles; t += gridDim.x, k++) {
         const int s = k % XF_STAGES;
@@ -137,9 +138,12 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
         unsigned char *tile = in_buf + s * TILE_IN_BYTES;
         mbar_wait(&full[s], parity);
 
+#ifndef ICB_XF_DBG
+#define ICB_XF_DBG 0        // experiments only: 1 = no arithmetic (TMA in, barriers, copy-out), 2 = no global stores
+#endif
         // ---- stage A: colour conversion + 4:2:0 downsample, 8x2-pixel strips ----
 #pragma unroll
-        for (int round = 0; round < 2; round++) {
+        for (int round = 0; round < ((ICB_XF_DBG & 1) ? 0 : 2); round++) {
             const int sid = tid + round * XF_THREADS;
             const int sc = sid & 31, sr = sid >> 5;
             const int m = sc >> 1, xi = sc & 1;
@@ -197,9 +201,14 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
         }
         __syncthreads();            // samples complete; the RGB tile is dead
 
-        // ---- stage B: one thread = one 8x8 block, 16 butterflies in registers ----
-        if (tid < TILE_BLOCKS) {
-            const int blk = tid;
+        // ---- stage B: one thread = one 8x8 block, both DCT passes in registers ----
+        // 96 blocks on 4 warps: one warp sits a tile out.  Which one rotates with the tile count
+        // and with the CTA's position among the CTAs sharing the SM, so that every SM
+        // sub-partition (warp w of each CTA lands on sub-partition w) carries 3/4 of the DCT work
+        // instead of three of them carrying all of it.
+        const int vt = (tid + 32 * ((k + cta_slot) & 3)) & (XF_THREADS - 1);
+        if (!(ICB_XF_DBG & 1) && vt < TILE_BLOCKS) {
+            const int blk = vt;
             const int m = blk / 6, c = blk - m * 6;
             const int gx = mcu0 + m;
             if (gx < g.mcu_cols) {
@@ -221,6 +230,7 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
                     const uint4 v = samp[samp_chunk(src, ch)];
                     sw[4 * ch] = v.x; sw[4 * ch + 1] = v.y; sw[4 * ch + 2] = v.z; sw[4 * ch + 3] = v.w;
                 }
+#ifdef ICB_XF_ROWMAJOR      // kept for A/B: all 64 intermediates alive between the passes (122 registers)
                 int d[64];
 #pragma unroll
                 for (int r = 0; r < 8; r++) fdct_row_bytes(sw[2 * r], sw[2 * r + 1], &d[8 * r]);
@@ -243,6 +253,21 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
                     o.w = __byte_perm(d[kZZ[8 * kk + 6]], d[kZZ[8 * kk + 7]], 0x7632);
                     outp[kk ^ (blk & 7)] = o;
                 }
+#else
+                uint32_t P[32];
+                fdct_block_bytes(sw, P);
+                if (dummy) {
+                    P[0] &= 0xffffu;
+#pragma unroll
+                    for (int i = 1; i < 32; i++) P[i] = 0;
+                }
+                // zigzag + int16 pack into the (now free) RGB stage buffer, swizzled chunks
+                uint4 *outp = reinterpret_cast<uint4 *>(tile + blk * 128);
+                uint4 o;
+#define ICB_CHUNK(KK) fdct_zz_chunk<KK>(P, o.x, o.y, o.z, o.w); outp[KK ^ (blk & 7)] = o;
+                ICB_CHUNK(0) ICB_CHUNK(1) ICB_CHUNK(2) ICB_CHUNK(3) ICB_CHUNK(4) ICB_CHUNK(5) ICB_CHUNK(6) ICB_CHUNK(7)
+#undef ICB_CHUNK
+#endif
             }
         }
         __syncthreads();            // coefficients staged
@@ -255,7 +280,7 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
             for (int i = 0; i < (TILE_BLOCKS * 8) / XF_THREADS; i++) {
                 const int idx = tid + i * XF_THREADS;
                 const int blk = idx >> 3, kk = idx & 7;
-                if (mcu0 + blk / 6 < g.mcu_cols) {
+                if (!(ICB_XF_DBG & 2) && mcu0 + blk / 6 < g.mcu_cols) {
                     uint4 v = reinterpret_cast<const uint4 *>(tile + blk * 128)[kk ^ (blk & 7)];
                     gout[idx] = v;
                 }

@@ -180,6 +180,13 @@ int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q,
                               int reps, float *transform_ms, float *entropy_ms, float *total_ms,
                               float *entropy_kernel_ms, int *entropy_kernel_launches);
 
+/* Average duration of the transform kernel alone: the transforms of n resident images (all on one
+ * GPU) are enqueued back to back on one slot's stream, reps rounds, between two CUDA events after
+ * one untimed round (so neither the launch gap after an idle stream nor the event pair of a single
+ * launch is in the figure).  *launches = kernels timed. */
+int icb_profile_transform_series(icb_handle *h, const icb_image *const *imgs, int n, int reps,
+                                 float *ms_per_launch, int *launches);
+
 /* Device-side stopwatch over all slot streams of one GPU (bench timing with CUDA
  * events although the work runs on library-owned streams): icb_mark(.., 0) before
  * the first submit, icb_mark(.., 1) after the last wait, then icb_elapsed_ms. */

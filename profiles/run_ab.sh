@@ -1,13 +1,7 @@
-# A/B of the in-tree library against variants_tmp/*.so on the aggregate bench value
-timeout 600 python -m pytest tests -m gpu -x -q > gpurun_out/ab_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/ab_pytest.log
-tail -3 gpurun_out/ab_pytest.log
-for rep in 1 2; do
-  timeout 200 python bench.py > gpurun_out/ab_new_$rep.json 2> gpurun_out/ab_new_$rep.err
-  for v in variants_tmp/*.so; do
-    n=$(basename $v .so)
-    IMGCOMP_B200_LIB=$PWD/$v timeout 200 python bench.py > gpurun_out/ab_${n}_$rep.json 2> gpurun_out/ab_${n}_$rep.err
-  done
-done
-timeout 200 python bench.py --workload cfg2 --batch 32 > gpurun_out/ab_new_cfg2.json 2>&1
-timeout 200 python bench.py --workload cfg5 --steps 10 > gpurun_out/ab_new_cfg5.json 2>&1
-grep -h -o '"value": [0-9.]*' gpurun_out/ab_*.json | head -20
+# quick A/B pass: parity subset, cfg1 bench without the CPU leg, launch list
+timeout 600 python -m pytest tests/test_gpu_parity.py tests/test_gpu_edges.py -m gpu -x -q 2>&1 | tail -2
+timeout 300 python bench.py --no-cpu > gpurun_out/bench_ab.json 2> gpurun_out/bench_ab.err; python profiles/summ.py gpurun_out/bench_ab.json
+CMD="python bench.py --steps 1 --warmup 1 --batch 8 --no-cpu --no-check"
+ncu --metrics gpu__time_duration.sum --clock-control none -s 120 -c 120 --csv --log-file gpurun_out/launches_ab.csv $CMD > gpurun_out/ncu_launches_ab.log 2>&1
+python profiles/launch_summary.py gpurun_out/launches_ab.csv
+[ -x profiles/micro/pipe_rates ] && profiles/micro/pipe_rates | tee gpurun_out/pipe_rates.txt

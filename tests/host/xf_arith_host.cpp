@@ -55,6 +55,15 @@ static long run(const uint8_t *px, int w, int h, int pitch, const int16_t *ref)
                     const uint32_t pk = prmt((uint32_t)d[kZZ[k]], (uint32_t)d[kZZ[k + 1]], 0x7632);
                     if ((int16_t)(pk & 0xffff) != rb[k] || (int16_t)(pk >> 16) != rb[k + 1]) bad++;
                 }
+                // the column-at-a-time form the kernel runs (packed int16 columns, zigzag picked by PRMT)
+                uint32_t P[32], o[32];
+                fdct_block_bytes(samp[b], P);
+                fdct_zz_chunk<0>(P, o[0], o[1], o[2], o[3]);     fdct_zz_chunk<1>(P, o[4], o[5], o[6], o[7]);
+                fdct_zz_chunk<2>(P, o[8], o[9], o[10], o[11]);   fdct_zz_chunk<3>(P, o[12], o[13], o[14], o[15]);
+                fdct_zz_chunk<4>(P, o[16], o[17], o[18], o[19]); fdct_zz_chunk<5>(P, o[20], o[21], o[22], o[23]);
+                fdct_zz_chunk<6>(P, o[24], o[25], o[26], o[27]); fdct_zz_chunk<7>(P, o[28], o[29], o[30], o[31]);
+                for (int k = 0; k < 32; k++)
+                    if ((int16_t)(o[k] & 0xffff) != rb[2 * k] || (int16_t)(o[k] >> 16) != rb[2 * k + 1]) bad++;
             }
         }
     return bad;
