@@ -263,7 +263,8 @@ void release_slot(icb_handle *h, Slot *s)
 
 int enqueue_transform(icb_handle *h, Slot *s, const unsigned char *d_px, int w, int hgt, int pitch, int fmt)
 {
-    const Geom g = make_geom(w, hgt, pitch, fmt == ICB_FMT_BGR8);
+    static const int forced_tile = [] { const char *e = getenv("ICB_ENT_TILE"); return e ? atoi(e) : 0; }();   // tests / A-B runs
+    const Geom g = make_geom(w, hgt, pitch, fmt == ICB_FMT_BGR8, forced_tile);
     s->geom = g;
     int rc = ensure(h, s->d_coef, s->coef_cap, (size_t)g.nblocks * 128);
     if (rc) return rc;
@@ -363,16 +364,18 @@ int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, 
     const Geom &g = s->geom;
     const int nctas = (g.ntiles + ENT_WARPS - 1) / ENT_WARPS;
     const int nchunks = nctas;                       // chunk = the 8 tiles one CTA takes per round
-    const size_t per = round_up(ent_pass_bytes(g.ntiles, nchunks), 256);
+    const int cap_t = ent_cap(g.tile_blocks), stride_t = ent_scr_stride(g.tile_blocks);
+    const size_t per = round_up(ent_pass_bytes(g.ntiles, nchunks, stride_t), 256);
     int rc = ensure(h, s->d_pass, s->pass_cap, 2 * per + 256);
     if (rc) return rc;
-    rc = ensure(h, s->d_ent, s->ent_cap, ((size_t)g.ntiles * ENT_CAP + (size_t)g.ntiles) * 4 + 256);
+    rc = ensure(h, s->d_ent, s->ent_cap, ((size_t)g.ntiles * cap_t + (size_t)g.ntiles) * 4 + 256);
     if (rc) return rc;
     EntParams ep;
     ep.coef = s->d_coef;
     ep.st = s->d_state;
     ep.ent = s->d_ent;
-    ep.ent_cnt = s->d_ent + (size_t)g.ntiles * ENT_CAP;
+    ep.ent_cnt = s->d_ent + (size_t)g.ntiles * cap_t;
+    ep.tile_blocks = g.tile_blocks; ep.ent_cap = cap_t; ep.scr_stride = stride_t;
     ep.nblocks = g.nblocks;
     ep.ntiles = g.ntiles;
     ep.nchunks = nchunks;
@@ -382,7 +385,7 @@ int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, 
         ep.buf[b].ff = reinterpret_cast<uint4 *>(base);                 base += n * 16;
         ep.buf[b].crec = reinterpret_cast<uint4 *>(base);               base += c * 48;
         ep.buf[b].Pc = reinterpret_cast<unsigned long long *>(base);    base += c * 8;
-        ep.buf[b].scratch = reinterpret_cast<uint32_t *>(base);         base += n * ENT_SCR_STRIDE * 4;
+        ep.buf[b].scratch = reinterpret_cast<uint32_t *>(base);         base += n * (size_t)stride_t * 4;
         ep.buf[b].L = reinterpret_cast<unsigned int *>(base);           base += n * 4;
         ep.buf[b].ones = reinterpret_cast<unsigned int *>(base);        base += n * 4;
         ep.buf[b].Fc = reinterpret_cast<unsigned int *>(base);          base += c * 4;

@@ -9,10 +9,6 @@
 #include <stddef.h>
 #include <stdint.h>
 
-#ifndef ICB_ENT_TILE
-#define ICB_ENT_TILE 128        // blocks per entropy tile (build knob for A/B runs; a power of two >= 32)
-#endif
-
 namespace icb {
 
 // ---- programmatic dependent launch (sm_90+): the kernels of one fit form a chain on one stream;
@@ -36,10 +32,28 @@ struct Geom {
     int yblk_w, yblk_h;     // real luma block counts
     int crows_real;         // ceil(h/2): downsampled rows that come from pixels
     int nblocks;            // 6 * mcu_cols * mcu_rows
-    int ntiles;             // entropy tiles = ceil(nblocks / ENT_TILE_BLOCKS)
+    int tile_blocks;        // blocks per entropy tile: 64, 128 or 256 (ent_tile_blocks)
+    int ntiles;             // entropy tiles = ceil(nblocks / tile_blocks)
 };
 
-__host__ __device__ inline Geom make_geom(int w, int h, int pitch, int bgr)
+// Blocks per entropy tile (one warp codes one tile per pass).  Every tile costs a fixed overhead per
+// pass (window set-up, final flush, 0xFF fold, tile record), so tiles should be large; but a pass
+// needs a couple of thousand tiles to fill 148 SMs.  Measured on B200 (12 MP = 282 k blocks: 64 ->
+// 10.8 k, 128 -> 12.0 k, 256 -> 11.0 k images/s; 24 MP = 564 k blocks: 7.7 k, 9.1 k, 9.7 k): the
+// largest of 64/128/256 that still leaves about 2000 tiles.  256 is the limit of the per-tile 16-bit
+// 0xFF counters (256 * 208 bytes < 65536).  forced (ICB_ENT_TILE, tests) overrides the rule.
+__host__ __device__ inline int ent_tile_blocks(int nblocks, int forced)
+{
+    if (forced == 32 || forced == 64 || forced == 128 || forced == 256) return forced;
+    if (nblocks >= 256 * 2000) return 256;
+    if (nblocks >= 128 * 2000) return 128;
+    return 64;
+}
+__host__ __device__ inline int ent_cap(int tile_blocks) { return tile_blocks * 64; }                   // survivor entries per tile, worst case
+// worst case per block: DC 9+11 bits, 63 x (16+10) bits = 1658 bits -> 208 B
+__host__ __device__ inline int ent_scr_stride(int tile_blocks) { return tile_blocks * 52 + 4; }        // scratch words per tile
+
+__host__ __device__ inline Geom make_geom(int w, int h, int pitch, int bgr, int forced_tile = 0)
 {
     Geom g;
     g.w = w; g.h = h; g.pitch = pitch; g.bgr = bgr;
@@ -49,7 +63,8 @@ __host__ __device__ inline Geom make_geom(int w, int h, int pitch, int bgr)
     g.yblk_h = (h + 7) >> 3;
     g.crows_real = (h + 1) >> 1;
     g.nblocks = 6 * g.mcu_cols * g.mcu_rows;
-    g.ntiles = (g.nblocks + ICB_ENT_TILE - 1) / ICB_ENT_TILE;
+    g.tile_blocks = ent_tile_blocks(g.nblocks, forced_tile);
+    g.ntiles = (g.nblocks + g.tile_blocks - 1) / g.tile_blocks;
     return g;
 }
 
@@ -69,17 +84,11 @@ constexpr int XF_STAGES = ICB_XF_STAGES;            // TMA boxes in flight per C
 constexpr int XF_CTAS = ICB_XF_CTAS;                // resident CTAs per SM the kernel is compiled for (register cap)
 
 // ---- entropy pass tiling ----
-constexpr int ENT_TILE_BLOCKS = ICB_ENT_TILE;       // blocks per warp tile (a multiple of 32)
-constexpr int ENT_TILE_SHIFT = ENT_TILE_BLOCKS == 32 ? 5 : ENT_TILE_BLOCKS == 64 ? 6 : ENT_TILE_BLOCKS == 128 ? 7 : 8;
 constexpr int ENT_WARPS = 8;
 constexpr int ENT_THREADS = ENT_WARPS * 32;
-// worst case per block: DC 9+11 bits, 63 x (16+10) bits = 1658 bits -> 208 B
-constexpr int ENT_SCR_STRIDE = (ENT_TILE_BLOCKS * 208) / 4 + 4;    // scratch words per tile
 constexpr int ENT_WIN = 256;                        // shared-memory bit window per warp (words)
 constexpr int ENT_WSTRIDE = ENT_WIN + 4;
-static_assert(ENT_TILE_BLOCKS == 1 << ENT_TILE_SHIFT && ENT_TILE_BLOCKS * 208 < 65536, "tile: power of two; 0xFF bytes of a tile fit 16 bits");
 constexpr int ENT_RING = 16;                        // CTA rounds whose tile records fit in shared memory at once
-constexpr int ENT_CAP = ENT_TILE_BLOCKS * 64;       // survivor entries per tile, worst case
 
 constexpr int HEADER_BYTES = 623;                   // a2.8, 3-component JFIF
 

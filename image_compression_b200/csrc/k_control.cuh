@@ -218,7 +218,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prune(const EntParams p
     __syncthreads();
     const int tile = blockIdx.x * ENT_WARPS + warp;
     if (tile >= p.ntiles) return;
-    uint32_t *list = p.ent + (size_t)tile * ENT_CAP;
+    uint32_t *list = p.ent + (size_t)tile * p.ent_cap;
     const uint32_t n = p.ent_cnt[tile];
     uint32_t w = 0;
     // four chunks of 32 in flight; a chunk's stores land at or below its own first slot, and every

@@ -49,7 +49,7 @@ __device__ __forceinline__ unsigned long long gtime()
 }
 
 struct PassBufs {
-    uint32_t *scratch;              // [ntiles][ENT_SCR_STRIDE] tile-local bit streams, big-endian words
+    uint32_t *scratch;              // [ntiles][scr_stride] tile-local bit streams, big-endian words
     unsigned int *L;                // [ntiles] bits per tile
     uint4 *ff;                      // [ntiles] 8 x u16: 0xFF bytes inside the tile per absolute start offset mod 8
     unsigned int *ones;             // [ntiles] leading 1-bits | trailing 1-bits << 8 (each capped at 8)
@@ -63,10 +63,11 @@ struct PassBufs {
 struct EntParams {
     const int16_t *coef;
     FitState *st;
-    uint32_t *ent;                  // [ntiles][ENT_CAP] survivor entries
+    uint32_t *ent;                  // [ntiles][ent_cap] survivor entries
     unsigned int *ent_cnt;          // [ntiles]
     PassBufs buf[2];                // ping-pong: the best pass so far is never overwritten
     int nblocks, ntiles, nchunks;
+    int tile_blocks, ent_cap, scr_stride;   // blocks per tile (Geom.tile_blocks), entries and scratch words reserved per tile
 };
 
 // select without dynamic indexing of the kernel parameter block (keeps it out of local memory)
@@ -186,11 +187,11 @@ __global__ void __launch_bounds__(PREP_THREADS, PREP_CTAS_PER_SM) k_entropy_prep
     unsigned char *ts = s_half[warp];
     const unsigned char *rp = ts + lane * PREP_ROW;
     for (int tile = blockIdx.x * PREP_WARPS + warp; tile < p.ntiles; tile += gridDim.x * PREP_WARPS) {
-        uint32_t *out = p.ent + (size_t)tile * ENT_CAP;
+        uint32_t *out = p.ent + (size_t)tile * p.ent_cap;
         uint32_t base = 0;
 #pragma unroll 1
-        for (int half = 0; half < ENT_TILE_BLOCKS / 32; half++) {
-            const int b0 = tile * ENT_TILE_BLOCKS + half * 32;
+        for (int half = 0; half < p.tile_blocks / 32; half++) {
+            const int b0 = tile * p.tile_blocks + half * 32;
             const int nb = p.nblocks - b0;              // rows of this half that exist (may be <= 0)
             if (nb <= 0) break;
             {
@@ -364,19 +365,19 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
       const int tile = chunk * ENT_WARPS + warp;
       const int slot = round & (ENT_RING - 1);
       if (round && slot == 0) __syncthreads();                  // the record ring starts a new lap (rare: > 16 rounds)
-      // count and first 64 entries together: reading past the count stays inside the tile's ENT_CAP
+      // count and first 64 entries together: reading past the count stays inside the tile's ent_cap
       // slots and is masked afterwards.  (Deeper look-ahead -- four rounds, or one tile ahead -- was
       // measured slower, alone and with several fits sharing the GPU: the loop is issue bound.)
       uint32_t n = 0;
       uint2 e_first = make_uint2(0u, 0u);
       if (tile < p.ntiles) {
           n = __ldg(p.ent_cnt + tile);
-          e_first = __ldg(reinterpret_cast<const uint2 *>(p.ent + (size_t)tile * ENT_CAP) + lane);
+          e_first = __ldg(reinterpret_cast<const uint2 *>(p.ent + (size_t)tile * p.ent_cap) + lane);
       }
       ICB_STAMP();                  // 5 / 10: tile start
       if (tile < p.ntiles) {
-        uint32_t *scr = pb.scratch + (size_t)tile * ENT_SCR_STRIDE;
-        const uint32_t *ent = p.ent + (size_t)tile * ENT_CAP;
+        uint32_t *scr = pb.scratch + (size_t)tile * p.scr_stride;
+        const uint32_t *ent = p.ent + (size_t)tile * p.ent_cap;
         uint32_t running = 0;       // bits produced so far (tile-local)
         uint32_t flushed = 0;       // whole words already copied to scratch
         uint32_t acc[4] = {0, 0, 0, 0};     // 0xFF counters, 2 x 16 bits each: local start bit s = 0,1 | 2,3 | 4,5 | 6,7
@@ -718,11 +719,11 @@ struct TileView {
     bool last;
 };
 
-__device__ __forceinline__ TileView tile_view(const PassBufs &pb, int tile, int ntiles, unsigned long long P,
+__device__ __forceinline__ TileView tile_view(const PassBufs &pb, int tile, int ntiles, int scr_stride, unsigned long long P,
                                               uint32_t L, uint32_t Lp)
 {
     TileView v;
-    v.scr = pb.scratch + (size_t)tile * ENT_SCR_STRIDE;
+    v.scr = pb.scratch + (size_t)tile * scr_stride;
     v.r = (uint32_t)(P & 7ull);
     v.nbytes = (uint32_t)(((P + L) >> 3) - (P >> 3));
     v.last = tile == ntiles - 1;
@@ -739,7 +740,7 @@ __device__ __forceinline__ TileView tile_view(const PassBufs &pb, int tile, int 
     }
     v.prev_tail = 0;
     if (v.r && tile > 0) {
-        const uint32_t *sp = pb.scratch + (size_t)(tile - 1) * ENT_SCR_STRIDE;
+        const uint32_t *sp = pb.scratch + (size_t)(tile - 1) * scr_stride;
         const uint32_t o = Lp - v.r, w = o >> 5, sh = o & 31;
         const unsigned long long two = ((unsigned long long)__ldcg(sp + w) << 32) | __ldcg(sp + w + 1);
         v.prev_tail = (uint32_t)(two >> (64 - v.r - sh)) & ((1u << v.r) - 1u);
@@ -823,7 +824,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
     uint32_t Lp = __shfl_sync(0xffffffffu, L_l, (me + 31) & 31);
     if (me == 0 && tile > 0) Lp = __ldcg(pb.L + tile - 1);
 
-    const TileView v = tile_view(pb, tile, p.ntiles, P, L, Lp);
+    const TileView v = tile_view(pb, tile, p.ntiles, p.scr_stride, P, L, Lp);
     const uint32_t nwords = (v.nbytes + 3) >> 2;
     const long long pos0 = (long long)HEADER_BYTES + (long long)(P >> 3) + (long long)ff_before;
     uint32_t ff_run = 0;
@@ -863,10 +864,10 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
 }
 
 // per-slot arenas
-__host__ __device__ inline size_t ent_pass_bytes(int ntiles, int nchunks)
+__host__ __device__ inline size_t ent_pass_bytes(int ntiles, int nchunks, int scr_stride)
 {
     const size_t n = (size_t)ntiles, c = (size_t)nchunks;
-    return n * ENT_SCR_STRIDE * 4 + n * 4 + n * 16 + n * 4 + c * 48 + c * 8 + c * 4 + ENT_THREADS * 4 + 256;
+    return n * (size_t)scr_stride * 4 + n * 4 + n * 16 + n * 4 + c * 48 + c * 8 + c * 4 + ENT_THREADS * 4 + 256;
 }
 
 }  // namespace icb

@@ -94,3 +94,20 @@ def test_both_list_strategies_give_the_same_bytes(forced):
     out = subprocess.run([sys.executable, "-c", _FORCED % root], env=env, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stderr[-2000:]
     assert "BAD 0" in out.stdout, out.stdout[-500:]
+
+
+@pytest.mark.parametrize("tile", ["32", "64", "128", "256"])
+def test_every_entropy_tile_size_gives_the_same_bytes(tile):
+    """The entropy tile (blocks per warp and pass) is picked from the image size (common.cuh
+    ent_tile_blocks); only time may depend on it.  Force each size (ICB_ENT_TILE is read once per
+    process) on images that span several tiles and on ones smaller than a tile, both list strategies."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for prune in ("0", "1"):
+        env = dict(os.environ, ICB_ENT_TILE=tile, ICB_PRUNE=prune)
+        out = subprocess.run([sys.executable, "-c", _FORCED % root], env=env, capture_output=True, text=True,
+                             timeout=600)
+        assert out.returncode == 0, out.stderr[-2000:]
+        assert "BAD 0" in out.stdout, out.stdout[-500:]
