@@ -10,3 +10,4 @@ timeout 300 python bench.py --workload png8k --steps 5 --batch 32 > gpurun_out/b
 timeout 300 python bench.py --workload cfg4 --steps 5 > gpurun_out/bench_final_cfg4.json 2>&1
 timeout 300 python bench.py --workload cfg5 --steps 10 > gpurun_out/bench_final_cfg5.json 2>&1
 nproc
+for f in gpurun_out/bench_final*.json; do echo $f; tail -1 $f | cut -c1-400; done
