@@ -241,6 +241,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prune(const EntParams p
             w += __popc(m);
         }
     }
+    for (uint32_t i = w + lane; i < ((w + 63u) & ~63u); i += 32) list[i] = 0u;     // dead padding to a whole round (k_entropy_pass)
     if (lane == 0) p.ent_cnt[tile] = w;
 }
 
