@@ -613,7 +613,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cfg1", choices=sorted(WORKLOADS) + ["png4k", "png8k", "cfg4", "cfg5"])
-    ap.add_argument("--batch", type=int, default=64, help="images per GPU per step")
+    ap.add_argument("--batch", type=int, default=128, help="images per GPU per step")
     ap.add_argument("--slots", type=int, default=6, help="stream work-queue slots per GPU")
     ap.add_argument("--threads", type=int, default=1, help="caller threads per GPU (each drives slots/threads)")
     ap.add_argument("--no-cpu", action="store_true")

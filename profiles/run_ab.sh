@@ -1,7 +1,7 @@
-# quick A/B pass: parity subset, cfg1 bench without the CPU leg, launch list
-timeout 600 python -m pytest tests/test_gpu_parity.py tests/test_gpu_edges.py -m gpu -x -q 2>&1 | tail -2
-timeout 300 python bench.py --no-cpu > gpurun_out/bench_ab.json 2> gpurun_out/bench_ab.err; python profiles/summ.py gpurun_out/bench_ab.json
+# quick A/B pass: full GPU parity suite, cfg1/cfg2 bench without the CPU leg, launch list
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -2
+timeout 300 python bench.py --no-cpu --no-check --steps 8 --warmup 3 > gpurun_out/bench_ab.json 2> gpurun_out/bench_ab.err; python profiles/summ.py gpurun_out/bench_ab.json
+timeout 300 python bench.py --no-cpu --no-check --workload cfg2 --batch 32 --steps 6 > gpurun_out/bench_ab_cfg2.json 2>/dev/null; python profiles/summ.py gpurun_out/bench_ab_cfg2.json
 CMD="python bench.py --steps 1 --warmup 1 --batch 8 --no-cpu --no-check"
 ncu --metrics gpu__time_duration.sum --clock-control none -s 120 -c 120 --csv --log-file gpurun_out/launches_ab.csv $CMD > gpurun_out/ncu_launches_ab.log 2>&1
 python profiles/launch_summary.py gpurun_out/launches_ab.csv
-[ -x profiles/micro/pipe_rates ] && profiles/micro/pipe_rates | tee gpurun_out/pipe_rates.txt
