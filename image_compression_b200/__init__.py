@@ -25,6 +25,9 @@ from .api import (  # noqa: F401
     FMT_BGR8,
     FMT_RGBA8,
     FMT_ABGR8,
+    FMT_GRAY8,
+    FMT_ARGB32,
+    FMT_XRGB32,
     IcbError,
     create_key,
     library_path,

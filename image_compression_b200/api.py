@@ -15,7 +15,8 @@ import numpy as np
 ICB_OK, ICB_NO_FIT = 0, 1
 ICB_ERR_INVALID, ICB_ERR_OOM, ICB_ERR_CUDA, ICB_ERR_UNSUPPORTED = -1, -2, -3, -4
 ICB_ERR_CAPACITY, ICB_ERR_NO_DEVICE, ICB_ERR_TICKET = -5, -6, -7
-FMT_RGB8, FMT_BGR8, FMT_RGBA8, FMT_ABGR8 = 0, 1, 2, 3
+FMT_RGB8, FMT_BGR8, FMT_RGBA8, FMT_ABGR8, FMT_GRAY8, FMT_ARGB32, FMT_XRGB32 = 0, 1, 2, 3, 4, 5, 6
+_BPP = {FMT_RGB8: 3, FMT_BGR8: 3, FMT_RGBA8: 4, FMT_ABGR8: 4, FMT_GRAY8: 1, FMT_ARGB32: 4, FMT_XRGB32: 4}
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 # IMGCOMP_B200_LIB: load another build of the SAME library (A/B runs of kernel variants); never a fallback
@@ -27,7 +28,11 @@ ABI_SYMBOLS = [
     "icb_alloc_pinned", "icb_free_pinned", "icb_jpg_fit", "icb_jpg_encode", "icb_jpg_sizes",
     "icb_jpg_coefficients", "icb_resize_dims", "icb_resize_bilinear", "icb_png_fit", "icb_png_target_dims",
     "icb_subsample_factor", "icb_subsample",
-    "icb_submit_jpg_fit", "icb_wait", "icb_image_upload", "icb_image_free",
+    "icb_submit_jpg_fit", "icb_wait", "icb_poll", "icb_submit_resize", "icb_submit_png_fit",
+    "icb_png_encode", "icb_submit_png_encode", "icb_png_compress", "icb_submit_png_compress",
+    "icb_profile_resize_series",
+    "icb_run_list",
+    "icb_image_upload", "icb_image_free",
     "icb_submit_jpg_fit_image", "icb_submit_resize_image", "icb_stats", "icb_profile_jpg_fit_image",
     "icb_profile_transform_series",
     "icb_mark", "icb_elapsed_ms",
@@ -49,7 +54,38 @@ class _Stats(C.Structure):
     _fields_ = [("images_done", C.c_uint64), ("kernels_launched", C.c_uint64), ("entropy_passes", C.c_uint64),
                 ("h2d_bytes", C.c_uint64), ("d2h_bytes", C.c_uint64), ("last_transform_ms", C.c_float),
                 ("last_entropy_ms", C.c_float), ("last_total_ms", C.c_float),
-                ("last_transform_launches", C.c_int), ("last_entropy_launches", C.c_int)]
+                ("last_transform_launches", C.c_int), ("last_entropy_launches", C.c_int),
+                ("kernel_clock_ns", C.c_uint64 * 3), ("kernel_clock_launches", C.c_uint64 * 3)]
+
+
+class _Item(C.Structure):
+    """icb_item (include/imgcomp_b200.h)"""
+    _fields_ = [("kind", C.c_int), ("px", C.c_void_p), ("img", C.c_void_p), ("w", C.c_int), ("h", C.c_int),
+                ("pitch", C.c_int), ("fmt", C.c_int), ("init_q", C.c_float), ("target", C.c_int64),
+                ("has_cached", C.c_int), ("cached_q", C.c_float), ("cached_scale", C.c_double), ("min_w", C.c_int),
+                ("min_h", C.c_int), ("out", C.c_void_p), ("out_cap", C.c_size_t), ("dw", C.c_int), ("dh", C.c_int),
+                ("res", _Result)]
+
+
+ITEM_KINDS = {"jpg_fit": 0, "jpg_fit_image": 1, "png_fit": 2, "png_compress": 3, "resize_image": 4}
+
+
+class ItemList:
+    """A prepared array of icb_item for Engine.run_list (built once, run many times: nothing of Python sits
+    between the items of a run).  Keeps the numpy buffers it points into alive."""
+
+    def __init__(self, arr, keep):
+        self.arr, self._keep = arr, keep
+
+    def __len__(self):
+        return len(self.arr)
+
+    def results(self):
+        return [FitResult(int(it.res.status), None, float(it.res.best_q), float(it.res.scale), bool(it.res.used_cache),
+                          int(it.res.n_passes), int(it.res.device), int(it.res.out_len)) for it in self.arr]
+
+    def dims(self):
+        return [(int(it.dw), int(it.dh)) for it in self.arr]
 
 
 def library_path() -> str:
@@ -103,6 +139,20 @@ def load_library(build_if_missing: bool = True):
     L.icb_submit_jpg_fit.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int64, C.c_int,
                                      C.c_float, C.c_double, vp, C.c_size_t, C.POINTER(C.c_int64)]
     L.icb_wait.argtypes = [vp, C.c_int64, C.POINTER(_Result)]
+    L.icb_poll.argtypes = [vp, C.c_int64, C.POINTER(C.c_int)]
+    L.icb_submit_resize.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_int, C.c_int, C.c_int,
+                                    C.POINTER(C.c_int64)]
+    L.icb_submit_png_fit.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_size_t,
+                                     C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int64)]
+    L.icb_png_encode.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_size_t, C.POINTER(C.c_size_t)]
+    L.icb_submit_png_encode.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_size_t,
+                                        C.POINTER(C.c_int64)]
+    L.icb_png_compress.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_size_t,
+                                   C.POINTER(C.c_size_t), C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.icb_submit_png_compress.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp,
+                                          C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int64)]
+    L.icb_profile_resize_series.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float)]
+    L.icb_run_list.argtypes = [vp, C.POINTER(_Item), C.c_size_t, C.c_int, C.c_int]
     L.icb_image_upload.argtypes = [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
     L.icb_image_free.argtypes = [vp, vp]
     L.icb_image_free.restype = None
@@ -113,7 +163,7 @@ def load_library(build_if_missing: bool = True):
     L.icb_profile_jpg_fit_image.argtypes = [vp, vp, C.c_float, C.c_int64, C.c_int, C.POINTER(C.c_float),
                                             C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float),
                                             C.POINTER(C.c_int)]
-    L.icb_profile_transform_series.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int, C.POINTER(C.c_float),
+    L.icb_profile_transform_series.argtypes = [vp, C.POINTER(vp), C.c_int, C.c_int, C.c_float, C.POINTER(C.c_float),
                                                C.POINTER(C.c_int)]
     L.icb_mark.argtypes = [vp, C.c_int, C.c_int]
     L.icb_elapsed_ms.argtypes = [vp, C.c_int, C.POINTER(C.c_float)]
@@ -165,13 +215,17 @@ class FitResult:
 def _image_args(image: np.ndarray, fmt: Optional[int]) -> Tuple[np.ndarray, int, int, int, int]:
     if image is None:
         raise TypeError("image must not be None")         # Java: NullPointerException
-    if image.dtype != np.uint8 or image.ndim != 3 or image.shape[2] not in (3, 4):
-        raise ValueError("image must be uint8 (h, w, 3|4)")
+    if image.dtype == np.uint8 and image.ndim == 2:
+        image = image[:, :, None]                         # TYPE_BYTE_GRAY
+    if image.dtype != np.uint8 or image.ndim != 3 or image.shape[2] not in (1, 3, 4):
+        raise ValueError("image must be uint8 (h, w[, 1|3|4])")
     if not image.flags["C_CONTIGUOUS"]:
         image = np.ascontiguousarray(image)
     h, w, c = image.shape
     if fmt is None:
-        fmt = FMT_RGB8 if c == 3 else FMT_RGBA8
+        fmt = {1: FMT_GRAY8, 3: FMT_RGB8, 4: FMT_RGBA8}[c]
+    if _BPP.get(fmt) != c:
+        raise ValueError("pixel format does not match the channel count")
     return image, w, h, image.strides[0], fmt
 
 
@@ -262,6 +316,11 @@ class Engine:
         arr = np.frombuffer(buf, dtype=dtype).reshape(shape)
         self._pinned[arr.ctypes.data] = p
         return arr
+
+    def free_pinned(self, arr: np.ndarray) -> None:
+        p = self._pinned.pop(arr.ctypes.data, None)
+        if p:
+            self._L.icb_free_pinned(p)
 
     # ---- core/ImageCompressionJpg.java:136-147 ----
     def compress_jpg_to_stream(self, image: np.ndarray, quality: float, fmt: Optional[int] = None) -> bytes:
@@ -407,6 +466,64 @@ class Engine:
             raise self._err(rc)
         return True, dst
 
+    # ---- core/ImageCompressionPng.java:70, and the whole seam :37-75, with the PNG file made on the GPU ----
+    def png_encode(self, image: np.ndarray, fmt: Optional[int] = None) -> bytes:
+        """ImageIO.write(image, "png", ...) on the GPU -> the PNG file bytes (decode to exactly `image`)."""
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        cap = image.size + image.size // 4 + 65536
+        while True:
+            out = np.empty(cap, np.uint8)
+            n = C.c_size_t(0)
+            rc = self._L.icb_png_encode(self._h, image.ctypes.data, w, h, pitch, fmt, out.ctypes.data, cap, C.byref(n))
+            if rc == ICB_ERR_CAPACITY and n.value > cap:
+                cap = n.value
+                continue
+            if rc:
+                raise self._err(rc)
+            return out[: n.value].tobytes()
+
+    def png_compress(self, image: np.ndarray, min_w: int, min_h: int, fmt: Optional[int] = None):
+        """compressPngWithTargetSize as one call: dimension rule, resize, PNG file; the resized pixels never
+        leave the GPU.  -> None when the image is already inside the box, else (png bytes, dw, dh)."""
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        dims = png_target_dims(w, h, min_w, min_h)
+        if dims is None:
+            return None
+        c = image.shape[2]
+        cap = dims[0] * dims[1] * c * 5 // 4 + 65536
+        while True:
+            out = np.empty(cap, np.uint8)
+            n, dw, dh = C.c_size_t(0), C.c_int(0), C.c_int(0)
+            rc = self._L.icb_png_compress(self._h, image.ctypes.data, w, h, pitch, fmt, min_w, min_h, out.ctypes.data,
+                                          cap, C.byref(n), C.byref(dw), C.byref(dh))
+            if rc == ICB_ERR_CAPACITY and n.value > cap:
+                cap = n.value
+                continue
+            if rc:
+                raise self._err(rc)
+            return out[: n.value].tobytes(), dw.value, dh.value
+
+    def submit_png_compress(self, image: np.ndarray, min_w: int, min_h: int, out: np.ndarray, fmt: Optional[int] = None):
+        """Queue form -> (ticket, dw, dh) or None; wait(ticket).out_len = bytes of the PNG file in `out`."""
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        t, dw, dh = C.c_int64(0), C.c_int(0), C.c_int(0)
+        rc = self._L.icb_submit_png_compress(self._h, image.ctypes.data, w, h, pitch, fmt, min_w, min_h,
+                                             out.ctypes.data, out.size, C.byref(dw), C.byref(dh), C.byref(t))
+        if rc == ICB_NO_FIT:
+            return None
+        if rc:
+            raise self._err(rc)
+        self._inflight[t.value] = (image, out)
+        return t.value, dw.value, dh.value
+
+    def profile_resize_series(self, img_handle, dw: int, dh: int, reps: int = 20, with_png: bool = False) -> float:
+        """ms per launch of the resize kernel (or resize + PNG encoder) on a resident image, back to back."""
+        ms = C.c_float(0)
+        rc = self._L.icb_profile_resize_series(self._h, img_handle, dw, dh, reps, 1 if with_png else 0, C.byref(ms))
+        if rc:
+            raise self._err(rc)
+        return float(ms.value)
+
     # ---- asynchronous queue (CompressionBatch.java:77-88 submit / :97-107 await) ----
     def submit_jpg_fit(self, image: np.ndarray, init_q: float, target: int, out: np.ndarray,
                        cached: Optional[LearnedParams] = None, fmt: Optional[int] = None) -> int:
@@ -443,6 +560,77 @@ class Engine:
         self._inflight[t.value] = (None, dst)
         return t.value
 
+    def submit_resize(self, image: np.ndarray, dst: np.ndarray, fmt: Optional[int] = None) -> int:
+        """tools/ImageTools.java:7-26 in the queue: host pixels in, dst (dh, dw, c) filled when wait() returns."""
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        t = C.c_int64(0)
+        rc = self._L.icb_submit_resize(self._h, image.ctypes.data, w, h, pitch, fmt, dst.ctypes.data, dst.shape[1],
+                                       dst.shape[0], dst.strides[0], C.byref(t))
+        if rc:
+            raise self._err(rc)
+        self._inflight[t.value] = (image, dst)
+        return t.value
+
+    def submit_png_fit(self, image: np.ndarray, min_w: int, min_h: int, dst: np.ndarray, fmt: Optional[int] = None):
+        """core/ImageCompressionPng.java:37-66 in the queue -> (ticket, dw, dh), or None when the image is
+        already inside the box (the seam returns false; nothing is queued).  dst: flat uint8 buffer."""
+        image, w, h, pitch, fmt = _image_args(image, fmt)
+        t, dw, dh = C.c_int64(0), C.c_int(0), C.c_int(0)
+        rc = self._L.icb_submit_png_fit(self._h, image.ctypes.data, w, h, pitch, fmt, min_w, min_h, dst.ctypes.data,
+                                        dst.size, C.byref(dw), C.byref(dh), C.byref(t))
+        if rc == ICB_NO_FIT:
+            return None
+        if rc:
+            raise self._err(rc)
+        self._inflight[t.value] = (image, dst)
+        return t.value, dw.value, dh.value
+
+    def poll(self, ticket: int) -> bool:
+        """True once the job has finished (wait() then returns at once); never blocks."""
+        d = C.c_int(0)
+        rc = self._L.icb_poll(self._h, ticket, C.byref(d))
+        if rc:
+            raise self._err(rc)
+        return bool(d.value)
+
+    # ---- the batch executor in native code (CompressionBatch.java:64-108) ----
+    def make_items(self, specs) -> ItemList:
+        """specs: dicts with kind ("jpg_fit" | "jpg_fit_image" | "png_fit" | "png_compress" | "resize_image"),
+        image (host ndarray, or a resident handle for the *_image kinds), out (uint8 ndarray or None) and, by kind,
+        init_q / target / cached (LearnedParams) or min_w / min_h or dw / dh."""
+        arr = (_Item * len(specs))()
+        keep = []
+        for it, sp in zip(arr, specs):
+            kind = sp["kind"]
+            it.kind = ITEM_KINDS[kind]
+            if kind in ("jpg_fit_image", "resize_image"):
+                h = sp["image"]
+                it.img = getattr(h, "value", h)
+            else:
+                image, w, hh, pitch, fmt = _image_args(sp["image"], sp.get("fmt"))
+                it.px, it.w, it.h, it.pitch, it.fmt = image.ctypes.data, w, hh, pitch, fmt
+                keep.append(image)
+            it.init_q = sp.get("init_q", 0.0)
+            it.target = int(sp.get("target", 0))
+            c = sp.get("cached")
+            it.has_cached = 1 if c else 0
+            it.cached_q = c.quality if c else 0.0
+            it.cached_scale = c.scale if c else 1.0
+            it.min_w, it.min_h = sp.get("min_w", 0), sp.get("min_h", 0)
+            it.dw, it.dh = sp.get("dw", 0), sp.get("dh", 0)
+            out = sp.get("out")
+            if out is not None:
+                it.out, it.out_cap = out.ctypes.data, out.size
+                keep.append(out)
+        return ItemList(arr, keep)
+
+    def run_list(self, items: ItemList, threads: int = 2, inflight: int = 3) -> None:
+        """Runs every item through the library's own worker threads (one atomic cursor, `inflight` jobs per thread
+        in the GPU work queues); results are in items.results() afterwards."""
+        rc = self._L.icb_run_list(self._h, items.arr, len(items.arr), threads, inflight)
+        if rc:
+            raise self._err(rc)
+
     def wait(self, ticket: int) -> FitResult:
         r = _Result()
         rc = self._L.icb_wait(self._h, ticket, C.byref(r))
@@ -474,11 +662,13 @@ class Engine:
         return dict(transform_ms=float(a.value), search_ms=float(b.value), total_ms=float(c.value),
                     entropy_kernel_ms=float(d.value), entropy_kernel_launches=int(n.value))
 
-    def profile_transform_series(self, img_handles, reps: int = 4):
-        """-> (ms per transform launch, launches timed): the images' transforms back to back on one stream"""
+    def profile_transform_series(self, img_handles, reps: int = 4, list_q: float = 0.0):
+        """-> (ms per transform launch, launches timed): the images' transforms back to back on one stream;
+        list_q > 0: with the survivor lists for that quality, as inside a fit"""
         arr = (C.c_void_p * len(img_handles))(*[getattr(x, "value", x) for x in img_handles])
         ms, n = C.c_float(0), C.c_int(0)
-        rc = self._L.icb_profile_transform_series(self._h, arr, len(img_handles), reps, C.byref(ms), C.byref(n))
+        rc = self._L.icb_profile_transform_series(self._h, arr, len(img_handles), reps, C.c_float(list_q),
+                                                  C.byref(ms), C.byref(n))
         if rc:
             raise self._err(rc)
         return float(ms.value), int(n.value)
@@ -500,4 +690,7 @@ class Engine:
         rc = self._L.icb_stats(self._h, C.byref(s))
         if rc:
             raise self._err(rc)
-        return {k: getattr(s, k) for k, _ in _Stats._fields_}
+        d = {k: getattr(s, k) for k, _ in _Stats._fields_}
+        d["kernel_clock_ns"] = list(s.kernel_clock_ns)              # [transform, entropy passes, emit]
+        d["kernel_clock_launches"] = list(s.kernel_clock_launches)
+        return d

@@ -10,8 +10,12 @@ counters for the report -- a host-side all-reduce of seven integers.
 """
 from __future__ import annotations
 
-from dataclasses import dataclass, field, asdict
-from typing import Callable, Dict, Iterable, List, Optional, Sequence, Tuple
+import threading
+from collections import deque
+from dataclasses import dataclass, field
+from typing import Callable, Dict, Iterable, List, Optional, Sequence
+
+import numpy as np
 
 # core/CompressionResult.java:3-16
 COMPRESSED_SUCCESS = "COMPRESSED_SUCCESS"
@@ -102,14 +106,28 @@ class WorkItem:
     original_size: int
 
 
-def run_shard(engine, items: Iterable[WorkItem], params, cache, rank: int = 0, world: int = 1,
-              on_output: Optional[Callable[[WorkItem, object], None]] = None) -> BatchCounters:
-    """Process this rank's share of `items` through the seams (image_compression_b200.api.Engine
-    or anything with the same two methods) and count results like CompressionBatch does."""
-    counters = BatchCounters()
-    items = list(items)
-    for i in shard_indices(len(items), rank, world):
-        it = items[i]
+class _Cursor:
+    """The one shared cursor the workers pull lines from (dynamic, granularity one image --
+    the reference's pool threads take the next queued task the same way, CompressionBatch.java:72-90)."""
+
+    def __init__(self, n: int):
+        self._n, self._i, self._lock = n, 0, threading.Lock()
+
+    def next(self) -> int:
+        with self._lock:
+            i = self._i
+            self._i += 1
+        return i if i < self._n else -1
+
+
+def _run_sync(engine, lines, cursor, params, cache, on_output) -> BatchCounters:
+    """One worker over the synchronous seams (anything with the Engine's two seam methods)."""
+    c = BatchCounters()
+    while True:
+        k = cursor.next()
+        if k < 0:
+            return c
+        it = lines[k]
         try:
             if it.kind == "jpg":
                 ok = engine.compress_jpg_with_target_size(it.pixels, it.original_size, None, params, cache)
@@ -119,16 +137,136 @@ def run_shard(engine, items: Iterable[WorkItem], params, cache, rank: int = 0, w
                 ok, out = engine.compress_png_with_target_size(it.pixels, "-", params)
                 size = int(out.size) if ok else 0           # resized pixels; the PNG writer stays with the host
             else:
-                counters.add(FAILED_UNSUPPORTED_FORMAT, it.original_size, it.original_size)
+                c.add(FAILED_UNSUPPORTED_FORMAT, it.original_size, it.original_size)
                 continue
             if ok:
-                counters.add(COMPRESSED_SUCCESS, it.original_size, size)
+                c.add(COMPRESSED_SUCCESS, it.original_size, size)
                 if on_output is not None:
                     on_output(it, out)
             else:
-                counters.add(FAILED_COMPRESSION, it.original_size, 0)
+                c.add(FAILED_COMPRESSION, it.original_size, 0)
         except MemoryError:
-            counters.add(FAILED_OUT_OF_MEMORY, it.original_size, 0)
+            c.add(FAILED_OUT_OF_MEMORY, it.original_size, 0)
         except Exception:
-            counters.add(FAILED_UNKNOWN, it.original_size, 0)
-    return counters
+            c.add(FAILED_UNKNOWN, it.original_size, 0)
+
+
+def _run_queued(engine, lines, cursor, params, cache, on_output, inflight: int) -> BatchCounters:
+    """One worker over the queue form of the seams: up to `inflight` jobs of this thread sit in the GPU
+    work queues while it stages the next line (icb_submit_* / icb_wait); cache.get before the submit and
+    cache.put after the wait, as core/ImageCompressionJpg.java:79-80, :111 do around the encode."""
+    from .api import IcbError, LearnedParams, create_key, png_target_dims
+    c = BatchCounters()
+    pending = deque()
+    target = int(params.target_max_size_bytes)
+    # one output buffer per job in flight, page-locked so the stream lands in it without a bounce
+    jpg_outs = [engine.alloc_pinned((max(target, 0) + 16,)) for _ in range(inflight)]
+    free_outs = list(range(inflight))
+
+    def finish():
+        it, kind, ticket, out, extra = pending.popleft()
+        try:
+            r = engine.wait(ticket)
+            if kind == "jpg":
+                key, slot = extra
+                if r.status == 0:
+                    data = out[: r.out_len].tobytes()
+                    if not r.used_cache:
+                        cache[key] = LearnedParams(r.best_q, r.scale)
+                    c.add(COMPRESSED_SUCCESS, it.original_size, len(data))
+                    if on_output is not None:
+                        on_output(it, data)
+                else:
+                    c.add(status_to_result(r.status), it.original_size, 0)
+            else:
+                dw, dh, ch = extra
+                px = out[: dw * dh * ch].reshape(dh, dw, ch)
+                c.add(COMPRESSED_SUCCESS, it.original_size, int(px.size))
+                if on_output is not None:
+                    on_output(it, px)
+        except IcbError as e:
+            c.add(status_to_result(e.code), it.original_size, 0)
+        finally:
+            if kind == "jpg":
+                free_outs.append(extra[1])
+
+    while True:
+        k = cursor.next()
+        if k < 0:
+            break
+        it = lines[k]
+        if it.kind not in ("jpg", "png"):
+            c.add(FAILED_UNSUPPORTED_FORMAT, it.original_size, it.original_size)
+            continue
+        if len(pending) == inflight:
+            finish()
+        try:
+            h, w = it.pixels.shape[:2]
+            if it.kind == "jpg":
+                key = create_key(w, h, it.original_size)
+                slot = free_outs.pop()
+                try:
+                    t = engine.submit_jpg_fit(it.pixels, params.quality, target, jpg_outs[slot], cached=cache.get(key))
+                except Exception:
+                    free_outs.append(slot)
+                    raise
+                pending.append((it, "jpg", t, jpg_outs[slot], (key, slot)))
+            else:
+                dims = png_target_dims(w, h, params.min_width, params.min_height)
+                if dims is None:
+                    c.add(FAILED_COMPRESSION, it.original_size, 0)          # the seam returns false (:49-53)
+                    continue
+                ch = it.pixels.shape[2] if it.pixels.ndim == 3 else 1
+                dst = np.empty(dims[0] * dims[1] * ch, np.uint8)
+                t, dw, dh = engine.submit_png_fit(it.pixels, params.min_width, params.min_height, dst)
+                pending.append((it, "png", t, dst, (dw, dh, ch)))
+        except MemoryError:
+            c.add(FAILED_OUT_OF_MEMORY, it.original_size, 0)
+        except IcbError as e:
+            c.add(status_to_result(e.code), it.original_size, 0)
+        except Exception:
+            c.add(FAILED_UNKNOWN, it.original_size, 0)
+    while pending:
+        finish()
+    for o in jpg_outs:
+        engine.free_pinned(o)
+    return c
+
+
+def run_shard(engine, items: Iterable[WorkItem], params, cache, rank: int = 0, world: int = 1,
+              on_output: Optional[Callable[[WorkItem, object], None]] = None, threads: int = 1,
+              inflight_per_thread: int = 2) -> BatchCounters:
+    """Process this rank's share of `items` and count results like CompressionBatch does.
+
+    Ranks (one process per GPU) take interleaved lines of the list; inside a rank `threads` workers pull
+    from ONE shared cursor and, when the engine has the queue form of the seams (icb_submit_* / icb_wait),
+    each keeps `inflight_per_thread` jobs in the GPU work queues, so uploads, kernels and downloads of
+    different lines overlap.  An engine that only has the two synchronous seam methods is driven through
+    those.  An Engine opened on several GPUs spreads the jobs over all of them (one process, the Java
+    host's shape)."""
+    items = list(items)
+    lines = [items[i] for i in shard_indices(len(items), rank, world)]
+    cursor = _Cursor(len(lines))
+    queued = hasattr(engine, "submit_jpg_fit") and hasattr(engine, "submit_png_fit")
+    threads = max(1, int(threads))
+    results: List[Optional[BatchCounters]] = [None] * threads
+
+    def work(t: int) -> None:
+        if queued:
+            results[t] = _run_queued(engine, lines, cursor, params, cache, on_output, max(1, int(inflight_per_thread)))
+        else:
+            results[t] = _run_sync(engine, lines, cursor, params, cache, on_output)
+
+    if threads == 1:
+        work(0)
+    else:
+        ts = [threading.Thread(target=work, args=(t,)) for t in range(threads)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join()
+    total = BatchCounters()
+    for r in results:
+        if r is not None:
+            total = total.merged(r)
+    return total

@@ -13,6 +13,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <utility>
@@ -22,6 +23,7 @@
 #include "common.cuh"
 #include "k_control.cuh"
 #include "k_entropy.cuh"
+#include "k_png.cuh"
 #include "k_resize.cuh"
 #include "k_transform.cuh"
 
@@ -42,7 +44,7 @@ struct DeviceCtx {
     cudaEvent_t join = nullptr;
 };
 
-enum Phase { PH_IDLE = 0, PH_CACHED, PH_SEARCH, PH_RESIZE };
+enum Phase { PH_IDLE = 0, PH_CACHED, PH_SEARCH, PH_RESIZE, PH_PNG, PH_DONE };
 
 struct Job {
     Phase phase = PH_IDLE;
@@ -53,12 +55,17 @@ struct Job {
     int has_cached = 0;
     float cached_q = 0;
     double cached_scale = 1.0;
-    unsigned char *out = nullptr;
+    unsigned char *out = nullptr;           // caller's output buffer
     size_t out_cap = 0;
+    bool out_pinned = false;                // the device can copy straight into it
+    bool stage_stream = false;              // the JFIF stream of this job lands in the slot's h_out first
+    size_t staged_out = 0;                  // bytes waiting in the slot's pinned h_out for the caller's pageable buffer
+    int out_rows = 0, out_row_bytes = 0, out_pitch = 0;   // PH_RESIZE: shape of the staged rows
     double scale = 1.0;                     // scale of the phase in flight
     bool coef_is_scale1 = false;            // coefficients in HBM belong to the unscaled image
     long long dev_cap = 0;                  // capacity handed to the kernels
     int passes = 0;
+    bool xf_this_phase = false;             // the phase in flight ran the transform (its kernel clock is fresh)
     icb_result res{};
 };
 
@@ -74,6 +81,14 @@ struct Slot {
     unsigned char *d_out = nullptr;   size_t out_cap = 0;       // final JFIF stream
     FitState *d_state = nullptr;
     FitState *h_state = nullptr;            // pinned
+    // page-locked staging for callers that bring pageable memory (a Java heap array copied by FFM,
+    // a numpy array): pixels are copied in here slice by slice with the H2D of each slice queued behind
+    // it, results land here and are copied out when the job is collected
+    unsigned char *h_in = nullptr;    size_t h_in_cap = 0;
+    unsigned char *h_out = nullptr;   size_t h_out_cap = 0;
+    unsigned char *d_png = nullptr;   size_t png_cap = 0;       // PNG encoder work arena (k_png.cuh)
+    unsigned char *d_file = nullptr;  size_t file_cap = 0;      // the PNG file as it is assembled
+    unsigned long long *h_len = nullptr;                        // pinned: length of the PNG file of the job in flight
     Geom geom{};
     bool busy = false;
     uint64_t gen = 0;
@@ -93,25 +108,33 @@ struct icb_handle {
     std::vector<Slot> slots;
     std::mutex mu;
     std::condition_variable cv;
+    std::unique_ptr<std::mutex[]> slot_mu;   // one per slot: serialises icb_poll / icb_wait on the same ticket
     int rr = 0;
     int table_mode = 0, jfif_minor = 2;
     PFN_encodeTiled encode_tiled = nullptr;
     std::string last_error;
     std::atomic<uint64_t> images_done{0}, kernels{0}, passes{0}, h2d{0}, d2h{0};
+    // kernel clocks summed over finished jobs (FitState.kt): [0] transform, [1] entropy passes, [2] emit
+    std::atomic<uint64_t> kclk_ns[3], kclk_n[3];
     float last_xf_ms = 0, last_ent_ms = 0, last_total_ms = 0;
     int last_xf_launches = 0, last_ent_launches = 0;
     // what the first midpoint of earlier searches of the same (w, h, q, target) did: key << 1 | failed
     std::atomic<uint64_t> first_pass_seen[256];
-    icb_handle() { for (auto &e : first_pass_seen) e.store(0); }
+    icb_handle() { for (auto &e : first_pass_seen) e.store(0); for (int i = 0; i < 3; i++) { kclk_ns[i].store(0); kclk_n[i].store(0); } }
 };
 
 namespace {
 
+// icb_last_error hands out the calling thread's own copy: another thread's failure cannot reassign the
+// string while the caller reads it
+thread_local std::string tl_last_error;
+
 int fail(icb_handle *h, int code, const char *what, cudaError_t e = cudaSuccess)
 {
+    tl_last_error = std::string(what) + (e != cudaSuccess ? std::string(": ") + cudaGetErrorString(e) : "");
     if (h) {
         std::lock_guard<std::mutex> lk(h->mu);
-        h->last_error = std::string(what) + (e != cudaSuccess ? std::string(": ") + cudaGetErrorString(e) : "");
+        h->last_error = tl_last_error;
     }
     if (e == cudaErrorMemoryAllocation) return ICB_ERR_OOM;
     return code;
@@ -147,7 +170,15 @@ cudaError_t launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, c
     return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
 }
 
-inline int bpp_of(int fmt) { return (fmt == ICB_FMT_RGBA8 || fmt == ICB_FMT_ABGR8) ? 4 : 3; }
+inline int bpp_of(int fmt)
+{
+    switch (fmt) {
+    case ICB_FMT_RGBA8: case ICB_FMT_ABGR8: case ICB_FMT_ARGB32: case ICB_FMT_XRGB32: return 4;
+    case ICB_FMT_GRAY8: return 1;
+    default: return 3;
+    }
+}
+inline bool fmt_valid(int fmt) { return fmt >= ICB_FMT_RGB8 && fmt <= ICB_FMT_XRGB32; }
 inline size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 // device pitch: 16-byte multiple (TMA global stride) and at least one TMA box wide
 inline int dev_pitch(int w, int bpp) { return (int)std::max<size_t>(round_up((size_t)w * bpp, 16), TILE_ROW_BYTES); }
@@ -261,12 +292,75 @@ void release_slot(icb_handle *h, Slot *s)
 
 // ---- enqueue helpers (all asynchronous on the slot's stream) ----
 
-int enqueue_transform(icb_handle *h, Slot *s, const unsigned char *d_px, int w, int hgt, int pitch, int fmt)
+// What a fit job asks of the entropy kernels: the mode, the quality it starts from, how many passes to
+// queue, and the quality the first survivor lists are built for.
+struct FitPlan {
+    int mode;               // FitMode
+    float q;                // initial quality (search) or the one quality to encode at
+    long long target;
+    int npasses;
+    bool prune;             // search expected to overshoot at its first midpoint: lists for that midpoint, pruned as hi drops
+    float list_q;
+};
+
+FitPlan make_plan(int mode, float q, long long target, int npasses, bool expect_fail)
+{
+    FitPlan pl;
+    pl.mode = mode; pl.q = q; pl.target = target; pl.npasses = npasses;
+    pl.prune = mode == MODE_SEARCH && expect_fail && npasses > 1;
+    pl.list_q = pl.prune ? (0.0f + q) / 2.0f : q;               // = the first midpoint (:168)
+    return pl;
+}
+
+// per-slot entropy arenas for geometry g: survivor lists, unit links, two pass arenas
+int ensure_entropy_arenas(icb_handle *h, Slot *s, const Geom &g)
+{
+    const int nchunks = (g.ntiles + ENT_WARPS - 1) / ENT_WARPS;
+    const size_t per = round_up(ent_pass_bytes(g.ntiles, nchunks, ent_scr_stride(g.unit_group)), 256);
+    int rc = ensure(h, s->d_pass, s->pass_cap, 2 * per + 256);
+    if (rc) return rc;
+    return ensure(h, s->d_ent, s->ent_cap, ent_list_bytes(g.nunits));
+}
+
+void fill_ent_params(const Slot *s, EntParams &ep)
+{
+    const Geom &g = s->geom;
+    const int nchunks = (g.ntiles + ENT_WARPS - 1) / ENT_WARPS;      // chunk = the 8 tiles one CTA takes per round
+    const int stride_t = ent_scr_stride(g.unit_group);
+    const size_t per = round_up(ent_pass_bytes(g.ntiles, nchunks, stride_t), 256);
+    ep.coef = s->d_coef;
+    ep.st = s->d_state;
+    ep.ent = s->d_ent;
+    ep.ent_cnt = s->d_ent + (size_t)g.nunits * UNIT_CAP;
+    ep.unit_info = reinterpret_cast<unsigned short *>(ep.ent_cnt + round_up((size_t)g.nunits, 4));
+    ep.unit_group = g.unit_group; ep.scr_stride = stride_t;
+    ep.units_per_row = g.units_per_row; ep.mcu_cols = g.mcu_cols;
+    ep.nblocks = g.nblocks;
+    ep.nunits = g.nunits;
+    ep.ntiles = g.ntiles;
+    ep.nchunks = nchunks;
+    for (int b = 0; b < 2; b++) {
+        unsigned char *base = s->d_pass + (size_t)b * per;
+        const size_t n = (size_t)g.ntiles, c = (size_t)nchunks;
+        ep.buf[b].ff = reinterpret_cast<uint4 *>(base);                 base += n * 16;
+        ep.buf[b].crec = reinterpret_cast<uint4 *>(base);               base += c * 48;
+        ep.buf[b].Pc = reinterpret_cast<unsigned long long *>(base);    base += c * 8;
+        ep.buf[b].scratch = reinterpret_cast<uint32_t *>(base);         base += n * (size_t)stride_t * 4;
+        ep.buf[b].L = reinterpret_cast<unsigned int *>(base);           base += n * 4;
+        ep.buf[b].ones = reinterpret_cast<unsigned int *>(base);        base += n * 4;
+        ep.buf[b].Fc = reinterpret_cast<unsigned int *>(base);          base += c * 4;
+        ep.buf[b].Fb = reinterpret_cast<unsigned int *>(base);
+    }
+}
+
+// The forward transform of one image; with a plan it also writes the survivor lists the plan's passes
+// start from (the stand-alone list kernel k_entropy_prepare is then not needed).
+int enqueue_transform(icb_handle *h, Slot *s, const unsigned char *d_px, int w, int hgt, int pitch, int fmt,
+                      const FitPlan *plan)
 {
     static const int forced_tile = [] { const char *e = getenv("ICB_ENT_TILE"); return e ? atoi(e) : 0; }();   // tests / A-B runs
-    // a fit that has the GPU to itself (no other slot of this device in use) is a latency case: smaller
-    // tiles give its passes more warps (25 MP alone: 1.22 ms with 128-block tiles, 1.36 ms with 256);
-    // the tile size never changes a byte of the result
+    // a fit that has the GPU to itself (no other slot of this device in use) is a latency case: one unit
+    // per tile gives its passes more warps; the tile size never changes a byte of the result
     int tile_pick = forced_tile;
     if (!tile_pick) {
         int busy = 0;
@@ -274,12 +368,22 @@ int enqueue_transform(icb_handle *h, Slot *s, const unsigned char *d_px, int w, 
             std::lock_guard<std::mutex> lk(h->mu);
             for (const Slot &o : h->slots) busy += (o.busy && o.devi == s->devi) ? 1 : 0;
         }
-        if (busy <= 1) tile_pick = std::min(128, ent_tile_blocks(6 * ((w + 15) >> 4) * ((hgt + 15) >> 4), 0));
+        if (busy <= 1) tile_pick = 128;
     }
     const Geom g = make_geom(w, hgt, pitch, fmt == ICB_FMT_BGR8, tile_pick);
     s->geom = g;
     int rc = ensure(h, s->d_coef, s->coef_cap, (size_t)g.nblocks * 128);
     if (rc) return rc;
+    XfLists xl = {};
+    if (plan) {
+        rc = ensure_entropy_arenas(h, s, g);
+        if (rc) return rc;
+        EntParams ep;
+        fill_ent_params(s, ep);
+        xl.ent = ep.ent; xl.ent_cnt = ep.ent_cnt; xl.unit_info = ep.unit_info;
+        xl.list_q = plan->list_q; xl.table_mode = h->table_mode;
+        xl.st = s->d_state;
+    }
     CUtensorMap tmap;
     const cuuint64_t gdim[2] = {(cuuint64_t)(pitch / 4), (cuuint64_t)hgt};
     const cuuint64_t gstr[1] = {(cuuint64_t)pitch};
@@ -289,14 +393,14 @@ int enqueue_transform(icb_handle *h, Slot *s, const unsigned char *d_px, int w, 
                                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
                                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (cr != CUDA_SUCCESS) return fail(h, ICB_ERR_CUDA, "cuTensorMapEncodeTiled failed");
-    const int tiles_per_row = (g.mcu_cols + TILE_MCUS - 1) / TILE_MCUS;
-    const int ntiles = tiles_per_row * g.mcu_rows;
+    const int tiles_per_row = g.units_per_row;
+    const int ntiles = g.nunits;
     static const int xf_cps = [] { const char *e = getenv("ICB_XF_CPS"); return e ? atoi(e) : XF_CTAS; }();   // tuning knob
     const int grid = std::min(ntiles, h->devs[s->devi].sms * std::max(1, std::min(XF_CTAS, xf_cps)));
     if (g.bgr)
-        k_transform<true><<<grid, XF_THREADS, XF_SMEM_BYTES, s->stream>>>(tmap, g, s->d_coef, tiles_per_row, ntiles);
+        k_transform<true><<<grid, XF_THREADS, XF_SMEM_BYTES, s->stream>>>(tmap, g, s->d_coef, tiles_per_row, ntiles, xl);
     else
-        k_transform<false><<<grid, XF_THREADS, XF_SMEM_BYTES, s->stream>>>(tmap, g, s->d_coef, tiles_per_row, ntiles);
+        k_transform<false><<<grid, XF_THREADS, XF_SMEM_BYTES, s->stream>>>(tmap, g, s->d_coef, tiles_per_row, ntiles, xl);
     CK(cudaGetLastError());
     h->kernels++;
     return ICB_OK;
@@ -370,66 +474,46 @@ void note_first_pass(icb_handle *h, int w, int hgt, float q, long long target, b
     h->first_pass_seen[k & 255].store(k << 1 | (failed ? 1u : 0u), std::memory_order_relaxed);
 }
 
-int enqueue_passes(icb_handle *h, Slot *s, int mode, float q, long long target, int npasses, bool emit,
-                   long long dev_cap, cudaEvent_t *pass_ev = nullptr, bool expect_fail = false)
+// The entropy side of a job: job start (with lists_ready the transform wrote the survivor lists and only
+// the unit links are missing; otherwise the stand-alone list kernel builds them from the coefficients),
+// the plan's passes, and optionally the emission of the best stream.
+int enqueue_passes(icb_handle *h, Slot *s, const FitPlan &pl, bool lists_ready, bool emit, long long dev_cap,
+                   cudaEvent_t *pass_ev = nullptr)
 {
     const Geom &g = s->geom;
-    const int nctas = (g.ntiles + ENT_WARPS - 1) / ENT_WARPS;
-    const int nchunks = nctas;                       // chunk = the 8 tiles one CTA takes per round
-    const int cap_t = ent_cap(g.tile_blocks), stride_t = ent_scr_stride(g.tile_blocks);
-    const size_t per = round_up(ent_pass_bytes(g.ntiles, nchunks, stride_t), 256);
-    int rc = ensure(h, s->d_pass, s->pass_cap, 2 * per + 256);
-    if (rc) return rc;
-    rc = ensure(h, s->d_ent, s->ent_cap, ((size_t)g.ntiles * cap_t + (size_t)g.ntiles) * 4 + 256);
+    int rc = ensure_entropy_arenas(h, s, g);
     if (rc) return rc;
     EntParams ep;
-    ep.coef = s->d_coef;
-    ep.st = s->d_state;
-    ep.ent = s->d_ent;
-    ep.ent_cnt = s->d_ent + (size_t)g.ntiles * cap_t;
-    ep.tile_blocks = g.tile_blocks; ep.ent_cap = cap_t; ep.scr_stride = stride_t;
-    ep.nblocks = g.nblocks;
-    ep.ntiles = g.ntiles;
-    ep.nchunks = nchunks;
-    for (int b = 0; b < 2; b++) {
-        unsigned char *base = s->d_pass + (size_t)b * per;
-        const size_t n = (size_t)g.ntiles, c = (size_t)nchunks;
-        ep.buf[b].ff = reinterpret_cast<uint4 *>(base);                 base += n * 16;
-        ep.buf[b].crec = reinterpret_cast<uint4 *>(base);               base += c * 48;
-        ep.buf[b].Pc = reinterpret_cast<unsigned long long *>(base);    base += c * 8;
-        ep.buf[b].scratch = reinterpret_cast<uint32_t *>(base);         base += n * (size_t)stride_t * 4;
-        ep.buf[b].L = reinterpret_cast<unsigned int *>(base);           base += n * 4;
-        ep.buf[b].ones = reinterpret_cast<unsigned int *>(base);        base += n * 4;
-        ep.buf[b].Fc = reinterpret_cast<unsigned int *>(base);          base += c * 4;
-        ep.buf[b].Fb = reinterpret_cast<unsigned int *>(base);
-    }
-    // searches expected to overshoot at their first midpoint walk hi down from there: the first
-    // lists are built for that midpoint only (rebuilt for hi if the pass fits after all) and pruned
-    // between passes as hi drops
-    const bool prune = mode == MODE_SEARCH && expect_fail && npasses > 1;
+    fill_ent_params(s, ep);
+    const int nctas = ep.nchunks;
     BeginArgs ba;
-    ba.mode = mode; ba.q = q; ba.target = target; ba.table_mode = h->table_mode; ba.jfif_minor = h->jfif_minor;
-    ba.list_q = prune ? (0.0f + q) / 2.0f : q;                   // = the first midpoint (:168)
+    ba.mode = pl.mode; ba.q = pl.q; ba.target = pl.target; ba.table_mode = h->table_mode; ba.jfif_minor = h->jfif_minor;
+    ba.list_q = pl.list_q;
     ba.pad = 0;
-    const int pneed = (g.ntiles + PREP_WARPS - 1) / PREP_WARPS;
+    const int pneed = (g.nunits + PREP_WARPS - 1) / PREP_WARPS;
     const int pwave = h->devs[s->devi].sms * PREP_CTAS_PER_SM;
-    const int prounds = (pneed + pwave - 1) / pwave;             // tiles a warp takes
+    const int prounds = (pneed + pwave - 1) / pwave;             // units a warp takes
     const dim3 prep_grid((pneed + prounds - 1) / prounds);
-    CK(launch(k_entropy_prepare<false>, prep_grid, dim3(PREP_THREADS), 0, s->stream, true, ep, ba));
+    if (lists_ready)
+        CK(launch(k_job_begin, dim3((g.nunits + BEGIN_THREADS - 1) / BEGIN_THREADS), dim3(BEGIN_THREADS), 0, s->stream,
+                  true, ep, ba));
+    else
+        CK(launch(k_entropy_prepare<false>, prep_grid, dim3(PREP_THREADS), 0, s->stream, true, ep, ba));
     h->kernels += 1;
     const int pgrid = pass_grid(g.ntiles, h->devs[s->devi].sms);
     const bool pdl = pass_ev == nullptr;
-    for (int i = 0; i < npasses; i++) {
+    for (int i = 0; i < pl.npasses; i++) {
         if (pass_ev) cudaEventRecord(pass_ev[2 * i], s->stream);
         CK(launch(k_entropy_pass, dim3(pgrid), dim3(ENT_THREADS), 0, s->stream, pdl, ep));
         if (pass_ev) cudaEventRecord(pass_ev[2 * i + 1], s->stream);
         h->kernels += 1;
-        if (prune && i + 1 < npasses) {
+        if (pl.prune && i + 1 < pl.npasses) {
             if (i == 0) {
                 CK(launch(k_entropy_prepare<true>, prep_grid, dim3(PREP_THREADS), 0, s->stream, pdl, ep, ba));
                 h->kernels += 1;
             }
-            CK(launch(k_entropy_prune, dim3(nctas), dim3(ENT_THREADS), 0, s->stream, pdl, ep, i + 1));
+            CK(launch(k_entropy_prune, dim3((g.nunits + ENT_WARPS - 1) / ENT_WARPS), dim3(ENT_THREADS), 0, s->stream, pdl,
+                      ep, i + 1));
             h->kernels += 1;
         }
     }
@@ -462,24 +546,125 @@ int enqueue_resize(icb_handle *h, Slot *s, const unsigned char *d_src, int w, in
     rp.w = w; rp.h = hgt; rp.pitch = pitch;
     rp.dw = dw; rp.dh = dh; rp.dpitch = dpitch;
     resize_consts(w, hgt, dw, dh, rp);
-    dim3 grid((dw + 31) / 32, (dh + 7) / 8);
-    if (fmt == ICB_FMT_RGBA8) k_resize<4, 3><<<grid, 256, 0, s->stream>>>(rp);
-    else if (fmt == ICB_FMT_ABGR8) k_resize<4, 0><<<grid, 256, 0, s->stream>>>(rp);
-    else k_resize<3, -1><<<grid, 256, 0, s->stream>>>(rp);
+    // destination tile of the CTA: the widest power of two (<= 128 pixels) whose source row segment --
+    // (tw - 1) source steps plus the two outer taps, rounded out to 16-byte vectors -- fits the staging rows
+    const int bpp = bpp_of(fmt);
+    const double step = (double)w / dw;
+    int tl = 7;
+    size_t seg = 0;
+    for (; tl >= 2; tl--) {
+        seg = round_up((size_t)(((1 << tl) - 1) * step + 3.0) * bpp + 32, 16);
+        if (seg <= (size_t)RS_MAX_SEG) break;
+    }
+    if (tl < 2) {
+        // more than ~200 source pixels per destination pixel (a 1 x 1 thumbnail of a large image): the taps of
+        // neighbouring pixels share nothing, so there is nothing to stage -- plain gather, one thread per pixel
+        rp.tw_log2 = 0; rp.seg_bytes = 0;
+        const dim3 ggrid((dw + 31) / 32, (dh + 7) / 8);
+        switch (fmt) {
+        case ICB_FMT_RGBA8: case ICB_FMT_ARGB32: k_resize_gather<4, 3><<<ggrid, 256, 0, s->stream>>>(rp); break;
+        case ICB_FMT_ABGR8: k_resize_gather<4, 0><<<ggrid, 256, 0, s->stream>>>(rp); break;
+        case ICB_FMT_XRGB32: k_resize_gather<4, -1><<<ggrid, 256, 0, s->stream>>>(rp); break;
+        case ICB_FMT_GRAY8: k_resize_gather<1, -1><<<ggrid, 256, 0, s->stream>>>(rp); break;
+        default: k_resize_gather<3, -1><<<ggrid, 256, 0, s->stream>>>(rp); break;
+        }
+        CK(cudaGetLastError());
+        h->kernels++;
+        return ICB_OK;
+    }
+    rp.tw_log2 = tl;
+    rp.seg_bytes = (int)seg;
+    const int tw = 1 << tl;
+    const dim3 grid((dw + tw - 1) / tw, (dh + RS_ROWS - 1) / RS_ROWS);
+    const size_t smem = (size_t)resize_smem_bytes(rp.seg_bytes, tw, bpp);
+    switch (fmt) {
+    case ICB_FMT_RGBA8: case ICB_FMT_ARGB32: k_resize<4, 3><<<grid, RS_THREADS, smem, s->stream>>>(rp); break;
+    case ICB_FMT_ABGR8: k_resize<4, 0><<<grid, RS_THREADS, smem, s->stream>>>(rp); break;
+    case ICB_FMT_XRGB32: k_resize<4, -1><<<grid, RS_THREADS, smem, s->stream>>>(rp); break;
+    case ICB_FMT_GRAY8: k_resize<1, -1><<<grid, RS_THREADS, smem, s->stream>>>(rp); break;
+    default: k_resize<3, -1><<<grid, RS_THREADS, smem, s->stream>>>(rp); break;
+    }
     CK(cudaGetLastError());
     h->kernels++;
     return ICB_OK;
 }
 
-int upload(icb_handle *h, cudaStream_t st, unsigned char *d, int dpitch, const unsigned char *px, int w, int hgt,
+// Is p page-locked (or device-accessible) memory the copy engines can reach without a bounce buffer?
+bool is_pinned(const void *p)
+{
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    return at.type == cudaMemoryTypeHost || at.type == cudaMemoryTypeManaged || at.type == cudaMemoryTypeDevice;
+}
+
+int ensure_pinned(icb_handle *h, unsigned char *&p, size_t &cap, size_t need)
+{
+    if (need <= cap) return ICB_OK;
+    if (p) cudaFreeHost(p);
+    p = nullptr; cap = 0;
+    void *q = nullptr;
+    cudaError_t e = cudaHostAlloc(&q, need, cudaHostAllocPortable | cudaHostAllocMapped);
+    if (e != cudaSuccess) return fail(h, ICB_ERR_OOM, "cudaHostAlloc", e);
+    p = (unsigned char *)q; cap = need;
+    return ICB_OK;
+}
+
+// Host pixels -> the slot's device buffer.  Pinned sources copy asynchronously as they are; pageable
+// ones go through the slot's pinned staging in slices of a few MB, the calling thread copying slice k + 1
+// while the DMA engine moves slice k (several caller threads -- the reference's pool threads,
+// CompressionBatch.java:64-88 -- stage their images side by side).
+int upload(icb_handle *h, Slot *s, unsigned char *d, int dpitch, const unsigned char *px, int w, int hgt,
            int pitch, int bpp)
 {
-    if (pitch == dpitch)
-        CK(cudaMemcpyAsync(d, px, (size_t)(hgt - 1) * pitch + (size_t)w * bpp, cudaMemcpyHostToDevice, st));
-    else
-        CK(cudaMemcpy2DAsync(d, dpitch, px, pitch, (size_t)w * bpp, hgt, cudaMemcpyHostToDevice, st));
-    h->h2d += (uint64_t)w * bpp * hgt;
+    cudaStream_t st = s->stream;
+    const size_t row = (size_t)w * bpp;
+    h->h2d += (uint64_t)row * hgt;
+    if (is_pinned(px)) {
+        if (pitch == dpitch)
+            CK(cudaMemcpyAsync(d, px, (size_t)(hgt - 1) * pitch + row, cudaMemcpyHostToDevice, st));
+        else
+            CK(cudaMemcpy2DAsync(d, dpitch, px, pitch, row, hgt, cudaMemcpyHostToDevice, st));
+        return ICB_OK;
+    }
+    int rc = ensure_pinned(h, s->h_in, s->h_in_cap, row * hgt + 16);
+    if (rc) return rc;
+    const int rows_per = (int)std::max<size_t>(1, ((size_t)4 << 20) / row);
+    for (int y = 0; y < hgt; y += rows_per) {
+        const int n = std::min(rows_per, hgt - y);
+        unsigned char *stage = s->h_in + (size_t)y * row;
+        if ((size_t)pitch == row) memcpy(stage, px + (size_t)y * pitch, row * n);
+        else for (int r = 0; r < n; r++) memcpy(stage + (size_t)r * row, px + (size_t)(y + r) * pitch, row);
+        CK(cudaMemcpy2DAsync(d + (size_t)y * dpitch, dpitch, stage, row, row, n, cudaMemcpyHostToDevice, st));
+    }
     return ICB_OK;
+}
+
+// Queue the copy of the job's result rows (n_rows x row_bytes at device pitch spitch) to the caller:
+// straight into a pinned destination, else into the slot's pinned h_out (collect_output finishes it).
+int fetch_rows(icb_handle *h, Slot *s, const unsigned char *d_src, size_t spitch, size_t row_bytes, int n_rows,
+               size_t out_pitch)
+{
+    Job &j = s->job;
+    h->d2h += (uint64_t)row_bytes * n_rows;
+    if (j.out_pinned) {
+        CK(cudaMemcpy2DAsync(j.out, out_pitch, d_src, spitch, row_bytes, n_rows, cudaMemcpyDeviceToHost, s->stream));
+        return ICB_OK;
+    }
+    int rc = ensure_pinned(h, s->h_out, s->h_out_cap, row_bytes * n_rows + 16);
+    if (rc) return rc;
+    CK(cudaMemcpy2DAsync(s->h_out, row_bytes, d_src, spitch, row_bytes, n_rows, cudaMemcpyDeviceToHost, s->stream));
+    j.staged_out = row_bytes * n_rows;
+    j.out_rows = n_rows; j.out_row_bytes = (int)row_bytes; j.out_pitch = (int)out_pitch;
+    return ICB_OK;
+}
+
+void collect_output(Slot *s)                                // after the stream drained
+{
+    Job &j = s->job;
+    if (!j.staged_out || !j.out) return;
+    for (int r = 0; r < j.out_rows; r++)
+        memcpy(j.out + (size_t)r * j.out_pitch, s->h_out + (size_t)r * j.out_row_bytes, (size_t)j.out_row_bytes);
+    j.staged_out = 0;
 }
 
 }  // namespace
@@ -501,6 +686,10 @@ int fit_enqueue_phase(icb_handle *h, Slot *s)
     const unsigned char *src = j.d_src;
     int w = j.w, hgt = j.h, pitch = j.pitch;
     const double scale = j.phase == PH_CACHED ? j.cached_scale : j.scale;
+    const FitPlan pl = j.phase == PH_CACHED
+        ? make_plan(MODE_SINGLE, j.cached_q, j.target, 1, false)
+        : make_plan(MODE_SEARCH, j.init_q, j.target, max_search_iters(j.init_q),
+                    scale < 1.0 || expect_first_pass_fails(h, j.w, j.h, j.init_q, j.target));
     bool need_xf = true;
     if (scale < 1.0) {                                   // :97-102 / :221-224, always from the original
         int nw, nh;
@@ -515,8 +704,13 @@ int fit_enqueue_phase(icb_handle *h, Slot *s)
     } else if (j.coef_is_scale1) {
         need_xf = false;                                 // cached miss at scale 1: coefficients still valid
     }
+    j.xf_this_phase = need_xf;
+    // A/B knob: ICB_FUSED_LISTS=0 makes the transform write coefficients only and the stand-alone list kernel
+    // build the survivor lists from them (the round-1 structure); results are identical either way
+    static const bool fused = [] { const char *e = getenv("ICB_FUSED_LISTS"); return !(e && e[0] == '0'); }();
+    bool lists_ready = need_xf && fused;
     if (need_xf) {
-        int rc = enqueue_transform(h, s, src, w, hgt, pitch, j.fmt);
+        int rc = enqueue_transform(h, s, src, w, hgt, pitch, j.fmt, fused ? &pl : nullptr);
         if (rc) return rc;
         if (!(scale < 1.0)) j.coef_is_scale1 = true;
     }
@@ -527,19 +721,26 @@ int fit_enqueue_phase(icb_handle *h, Slot *s)
         int rc = ensure(h, s->d_out, s->out_cap, round_up((size_t)cap, 16) + 32);
         if (rc) return rc;
     }
-    int rc;
-    if (j.phase == PH_CACHED)
-        rc = enqueue_passes(h, s, MODE_SINGLE, j.cached_q, j.target, 1, true, cap);
-    else
-        rc = enqueue_passes(h, s, MODE_SEARCH, j.init_q, j.target, max_search_iters(j.init_q), true, cap, nullptr,
-                            scale < 1.0 || expect_first_pass_fails(h, j.w, j.h, j.init_q, j.target));
+    int rc = enqueue_passes(h, s, pl, lists_ready, true, cap);
     if (rc) return rc;
-    CK(cudaMemcpyAsync(s->h_state, s->d_state, sizeof(FitState), cudaMemcpyDeviceToHost, s->stream));
-    const size_t ncopy = (size_t)std::min<long long>((long long)j.out_cap, cap);
-    if (ncopy && j.out) {
-        CK(cudaMemcpyAsync(j.out, s->d_out, ncopy, cudaMemcpyDeviceToHost, s->stream));
-        h->d2h += ncopy;
+    // the stream goes back by a kernel that knows best_size (exactly that many bytes, nothing on a phase
+    // that failed): into the caller's buffer when it is page-locked and 16-byte aligned, else into the slot's
+    // page-locked staging (copied out when the job is collected)
+    if (j.out && j.out_cap) {
+        unsigned char *dst = j.out;
+        long long dcap = (long long)j.out_cap;
+        if (!j.out_pinned || ((uintptr_t)j.out & 15)) {
+            rc = ensure_pinned(h, s->h_out, s->h_out_cap, round_up((size_t)cap, 16) + 32);
+            if (rc) return rc;
+            dst = s->h_out;
+            dcap = std::min<long long>((long long)j.out_cap, cap);
+            j.stage_stream = true;
+        }
+        CK(launch(k_fetch_stream, dim3(8), dim3(FETCH_THREADS), 0, s->stream, true, (const FitState *)s->d_state,
+                  (const unsigned char *)s->d_out, cap, dst, dcap));
+        h->kernels += 1;
     }
+    CK(cudaMemcpyAsync(s->h_state, s->d_state, sizeof(FitState), cudaMemcpyDeviceToHost, s->stream));
     h->d2h += sizeof(FitState);
     return ICB_OK;
 }
@@ -551,6 +752,14 @@ int fit_advance(icb_handle *h, Slot *s)
     const FitState &st = *s->h_state;
     j.passes += st.passes;
     h->passes += (uint64_t)st.passes;
+    {   // kernel clocks of the phase that just drained
+        auto add = [&](int k, const unsigned long long (&t)[2]) {
+            if (t[1] > t[0] && t[0]) { h->kclk_ns[k] += t[1] - t[0]; h->kclk_n[k] += 1; }
+        };
+        if (j.xf_this_phase) add(0, st.kt[0]);
+        for (int i = 0; i < st.passes && i < 8; i++) add(1, st.kt[2 + i]);
+        if (st.best_size > 0) add(2, st.kt[10]);
+    }
     j.res.n_passes = j.passes;
     j.res.device = h->devs[s->devi].dev;
     bool ok = false;
@@ -585,6 +794,10 @@ int fit_advance(icb_handle *h, Slot *s)
     if (ok) {
         j.res.out_len = (size_t)st.best_size;
         j.res.status = (size_t)st.best_size <= j.out_cap ? ICB_OK : ICB_ERR_CAPACITY;
+        if (j.res.status == ICB_OK && j.out && st.best_size > 0) {
+            h->d2h += (uint64_t)st.best_size;            // k_fetch_stream moved exactly these bytes
+            if (j.stage_stream) memcpy(j.out, s->h_out, (size_t)st.best_size);
+        }
         return 0;
     }
     int rc = fit_enqueue_phase(h, s);
@@ -600,6 +813,7 @@ int start_fit(icb_handle *h, Slot *s, const unsigned char *d_src, int w, int hgt
     j.init_q = init_q; j.target = target;
     j.has_cached = has_cached; j.cached_q = cached_q; j.cached_scale = cached_scale;
     j.out = out; j.out_cap = out ? out_cap : 0;
+    j.out_pinned = out && is_pinned(out);
     j.phase = has_cached ? PH_CACHED : PH_SEARCH;
     j.scale = 1.0;
     return fit_enqueue_phase(h, s);
@@ -612,6 +826,17 @@ int check_jpg_args(icb_handle *h, const void *px, int w, int hgt, int pitch, int
     if (fmt != ICB_FMT_RGB8 && fmt != ICB_FMT_BGR8)
         return fail(h, ICB_ERR_UNSUPPORTED, "JPG path takes RGB8/BGR8 (gray, CMYK, alpha: use the stock writer)");
     if (pitch < w * 3) return fail(h, ICB_ERR_INVALID, "pitch smaller than a row");
+    return ICB_OK;
+}
+
+// ImageWriteParam.setCompressionQuality throws IllegalArgumentException outside [0, 1]; the reference would
+// hit that as soon as a midpoint (or the cached quality) left the range.  NaN is refused as well.
+bool bad_quality(float q) { return !(q >= 0.0f && q <= 1.0f); }
+
+int check_fit_qualities(icb_handle *h, float init_q, int has_cached, float cached_q)
+{
+    if (init_q != init_q || init_q > 1.0f) return fail(h, ICB_ERR_INVALID, "initial quality outside [0, 1]");
+    if (has_cached && bad_quality(cached_q)) return fail(h, ICB_ERR_INVALID, "cached quality outside [0, 1]");
     return ICB_OK;
 }
 
@@ -656,6 +881,7 @@ int icb_init(const int *devices, int n_devices, int slots_per_gpu, int max_w, in
         h->devs.push_back(dc);
     }
     h->slots.resize(devs.size() * (size_t)slots_per_gpu);
+    h->slot_mu.reset(new std::mutex[h->slots.size()]);
     // interleave devices so round-robin acquisition spreads images over GPUs
     for (size_t i = 0; i < h->slots.size(); i++) {
         Slot &s = h->slots[i];
@@ -664,14 +890,18 @@ int icb_init(const int *devices, int n_devices, int slots_per_gpu, int max_w, in
         if (cudaSetDevice(h->devs[s.devi].dev) != cudaSuccess ||
             cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking) != cudaSuccess ||
             cudaMalloc((void **)&s.d_state, sizeof(FitState)) != cudaSuccess ||
-            cudaMallocHost((void **)&s.h_state, sizeof(FitState)) != cudaSuccess) {
+            cudaMallocHost((void **)&s.h_state, sizeof(FitState)) != cudaSuccess ||
+            cudaMallocHost((void **)&s.h_len, 64) != cudaSuccess) {
             icb_shutdown(h);
             return ICB_ERR_OOM;
         }
         if (max_w > 0 && max_h > 0) {
             const Geom g = make_geom(max_w, max_h, dev_pitch(max_w, 3), 0);
+            // every arena a job of that size needs, so that no cudaMalloc / cudaFree (a device-wide
+            // synchronisation) happens while other slots are working
             if (ensure(h, s.d_rgb, s.rgb_cap, (size_t)g.pitch * max_h + 16) ||
-                ensure(h, s.d_coef, s.coef_cap, (size_t)g.nblocks * 128)) {
+                ensure(h, s.d_coef, s.coef_cap, (size_t)g.nblocks * 128) ||
+                ensure_entropy_arenas(h, &s, g) || ensure(h, s.d_out, s.out_cap, ((size_t)4 << 20) + 32)) {
                 icb_shutdown(h);
                 return ICB_ERR_OOM;
             }
@@ -704,13 +934,17 @@ void icb_shutdown(icb_handle *h)
         cudaFree(s.d_rgb); cudaFree(s.d_rgb2); cudaFree(s.d_coef); cudaFree(s.d_pass);
         cudaFree(s.d_out); cudaFree(s.d_state); cudaFree(s.d_ent);
         if (s.h_state) cudaFreeHost(s.h_state);
+        cudaFree(s.d_png); cudaFree(s.d_file);
+        if (s.h_len) cudaFreeHost(s.h_len);
+        if (s.h_in) cudaFreeHost(s.h_in);
+        if (s.h_out) cudaFreeHost(s.h_out);
     }
     delete h;
 }
 
 int icb_device_count(const icb_handle *h) { return h ? (int)h->devs.size() : 0; }
 
-const char *icb_last_error(const icb_handle *h) { return h ? h->last_error.c_str() : "no handle"; }
+const char *icb_last_error(const icb_handle *h) { return h ? tl_last_error.c_str() : "no handle"; }
 
 int icb_set_profile(icb_handle *h, int table_mode, int jfif_minor)
 {
@@ -723,7 +957,8 @@ int icb_set_profile(icb_handle *h, int table_mode, int jfif_minor)
 void *icb_alloc_pinned(size_t bytes)
 {
     void *p = nullptr;
-    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
+    // portable + mapped: every GPU of the handle can DMA from it and write results straight into it
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable | cudaHostAllocMapped) != cudaSuccess) return nullptr;
     return p;
 }
 
@@ -741,13 +976,14 @@ int icb_submit_jpg_fit(icb_handle *h, const uint8_t *px, int w, int hgt, int pit
                        size_t out_cap, int64_t *ticket)
 {
     int rc = check_jpg_args(h, px, w, hgt, pitch, fmt);
+    if (!rc) rc = check_fit_qualities(h, init_q, has_cached, cached_q);
     if (rc) return rc;
     if (!ticket) return ICB_ERR_INVALID;
     Slot *s = acquire_slot(h);
-    CK(cudaSetDevice(h->devs[s->devi].dev));
     const int dp = dev_pitch(w, 3);
-    rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)dp * hgt + 16);
-    if (!rc) rc = upload(h, s->stream, s->d_rgb, dp, px, w, hgt, pitch, 3);
+    if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "cudaSetDevice");
+    if (!rc) rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)dp * hgt + 16);
+    if (!rc) rc = upload(h, s, s->d_rgb, dp, px, w, hgt, pitch, 3);
     if (!rc) rc = start_fit(h, s, s->d_rgb, w, hgt, dp, fmt, init_q, target, has_cached, cached_q, cached_scale, out,
                             out_cap);
     if (rc) { cudaStreamSynchronize(s->stream); release_slot(h, s); return rc; }
@@ -760,13 +996,169 @@ int icb_submit_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q, 
 {
     if (!h || !img || !ticket) return ICB_ERR_INVALID;
     if (img->fmt != ICB_FMT_RGB8 && img->fmt != ICB_FMT_BGR8) return fail(h, ICB_ERR_UNSUPPORTED, "format");
+    int rc = check_fit_qualities(h, init_q, has_cached, cached_q);
+    if (rc) return rc;
     Slot *s = acquire_slot(h, img->devi);
-    int rc = start_fit(h, s, img->d_px, img->w, img->h, img->pitch, img->fmt, init_q, target, has_cached, cached_q,
-                       cached_scale, out, out_cap);
+    rc = start_fit(h, s, img->d_px, img->w, img->h, img->pitch, img->fmt, init_q, target, has_cached, cached_q,
+                   cached_scale, out, out_cap);
     if (rc) { cudaStreamSynchronize(s->stream); release_slot(h, s); return rc; }
     *ticket = make_ticket(s);
     return ICB_OK;
 }
+
+}  // extern "C"
+
+namespace {
+
+// resize of pixels already in HBM into the slot's d_rgb2, result rows queued for dst (NULL: they stay in HBM)
+int start_resize(icb_handle *h, Slot *s, const unsigned char *d_src, int w, int hgt, int pitch, int fmt, int dw, int dh,
+                 uint8_t *dst, int dpitch)
+{
+    const int bpp = bpp_of(fmt);
+    const int np = (int)round_up((size_t)dw * bpp, 16);
+    int rc = ensure(h, s->d_rgb2, s->rgb2_cap, (size_t)np * dh + 16);
+    if (!rc) rc = enqueue_resize(h, s, d_src, w, hgt, pitch, fmt, s->d_rgb2, dw, dh, np);
+    s->job = Job();
+    s->job.phase = PH_RESIZE;
+    s->job.out = dst;
+    s->job.out_pinned = dst && is_pinned(dst);
+    if (!rc && dst) rc = fetch_rows(h, s, s->d_rgb2, (size_t)np, (size_t)dw * bpp, dh, (size_t)dpitch);
+    return rc;
+}
+
+// PNG channel layout of a raster format: bytes per PNG pixel and, per PNG channel (R G B A), its source byte
+void png_layout(int fmt, int &pbpp, int &perm)
+{
+    switch (fmt) {
+    case ICB_FMT_BGR8:   pbpp = 3; perm = 0x012; break;
+    case ICB_FMT_RGBA8:  pbpp = 4; perm = 0x3210; break;
+    case ICB_FMT_ABGR8:  pbpp = 4; perm = 0x0123; break;
+    case ICB_FMT_ARGB32: pbpp = 4; perm = 0x3012; break;     // bytes B G R A
+    case ICB_FMT_XRGB32: pbpp = 3; perm = 0x012; break;      // bytes B G R x
+    case ICB_FMT_GRAY8:  pbpp = 1; perm = 0x0; break;
+    default:             pbpp = 3; perm = 0x210; break;      // RGB8
+    }
+}
+
+// core/ImageCompressionPng.java:70 on the device: pixels in HBM -> a PNG file in the slot's d_file, its length in
+// h_len, the file bytes on their way to the caller (exactly as many as the file has).
+int enqueue_png(icb_handle *h, Slot *s, const unsigned char *d_src, int w, int hgt, int pitch, int fmt)
+{
+    Job &j = s->job;
+    PngParams pp = {};
+    pp.src = d_src; pp.w = w; pp.h = hgt; pp.pitch = pitch; pp.sbpp = bpp_of(fmt);
+    png_layout(fmt, pp.pbpp, pp.perm);
+    pp.nfilt = (long long)hgt * (1 + (long long)w * pp.pbpp);
+    pp.npieces = (int)std::max<long long>(1, pp.nfilt / PNG_PIECE);
+    const size_t np = (size_t)pp.npieces;
+    const size_t o_filt = 0, o_seg = round_up((size_t)pp.nfilt + 64, 256);
+    const size_t o_len = o_seg + (np + 1) * PNG_PIECE_WORDS * 4, o_pos = round_up(o_len + (np + 1) * 4, 8);
+    const size_t o_adl = o_pos + (np + 2) * 8, o_hist = o_adl + np * 8, o_codes = o_hist + 320 * 4;
+    const size_t o_misc = o_codes + 320 * 4, total = o_misc + 64;
+    int rc = ensure(h, s->d_png, s->png_cap, total);
+    const size_t fcap = (size_t)pp.nfilt * 2 + (size_t)pp.nfilt / 512 + 65536;     // 15 bits per byte at the very worst
+    if (!rc) rc = ensure(h, s->d_file, s->file_cap, fcap);
+    if (rc) return rc;
+    pp.filt = s->d_png + o_filt;
+    pp.seg_bits = reinterpret_cast<uint32_t *>(s->d_png + o_seg);
+    pp.seg_len = reinterpret_cast<unsigned int *>(s->d_png + o_len);
+    pp.seg_pos = reinterpret_cast<unsigned long long *>(s->d_png + o_pos);
+    pp.adler = reinterpret_cast<uint2 *>(s->d_png + o_adl);
+    pp.hist = reinterpret_cast<unsigned int *>(s->d_png + o_hist);
+    pp.codes = reinterpret_cast<uint32_t *>(s->d_png + o_codes);
+    pp.out_len = reinterpret_cast<unsigned long long *>(s->d_png + o_misc);
+    pp.adler_out = reinterpret_cast<unsigned int *>(s->d_png + o_misc + 8);
+    pp.out = s->d_file;
+    pp.out_cap = (long long)fcap;
+    cudaStream_t st = s->stream;
+    CK(cudaMemsetAsync(pp.hist, 0, 320 * 4, st));
+    k_png_filter<<<(hgt + 7) / 8, 256, 0, st>>>(pp);
+    k_png_hist<<<(pp.npieces + 7) / 8, 256, 0, st>>>(pp);
+    k_png_tree<<<1, 32, 0, st>>>(pp);
+    k_png_encode<<<(pp.npieces + 7) / 8, 256, 0, st>>>(pp);
+    k_png_scan<<<1, 1024, 0, st>>>(pp);
+    k_png_merge<<<(pp.npieces + 1 + 7) / 8, 256, 0, st>>>(pp);
+    const long long max_idat = ((long long)fcap + PNG_IDAT - 1) / PNG_IDAT;
+    k_png_finish<<<(unsigned)((std::min<long long>(max_idat, ((long long)pp.nfilt * 2) / PNG_IDAT + 2) + 127) / 128), 128, 0, st>>>(pp);
+    CK(cudaGetLastError());
+    h->kernels += 7;
+    // file bytes to the caller: the length is known on the device only
+    if (j.out && j.out_cap) {
+        unsigned char *dst = j.out;
+        long long dcap = (long long)j.out_cap;
+        if (!j.out_pinned || ((uintptr_t)j.out & 15)) {
+            rc = ensure_pinned(h, s->h_out, s->h_out_cap, std::min(fcap, round_up(j.out_cap, 16) + 32));
+            if (rc) return rc;
+            dst = s->h_out;
+            dcap = (long long)std::min(s->h_out_cap, j.out_cap);
+            j.stage_stream = true;
+        }
+        k_fetch_len<<<16, FETCH_THREADS, 0, st>>>(pp.out_len, s->d_file, (long long)fcap, dst, dcap);
+        CK(cudaGetLastError());
+        h->kernels += 1;
+    }
+    CK(cudaMemcpyAsync(s->h_len, pp.out_len, 8, cudaMemcpyDeviceToHost, st));
+    j.phase = PH_PNG;
+    return ICB_OK;
+}
+
+int check_resize_args(icb_handle *h, const void *src, int w, int hgt, int pitch, int fmt, const void *dst, int dw, int dh,
+                      int dpitch)
+{
+    if (!h) return ICB_ERR_INVALID;
+    if (!src || !dst || w < 1 || hgt < 1 || dw < 1 || dh < 1) return fail(h, ICB_ERR_INVALID, "bad resize arguments");
+    if (!fmt_valid(fmt)) return fail(h, ICB_ERR_UNSUPPORTED, "format");
+    const int bpp = bpp_of(fmt);
+    if (pitch < w * bpp || dpitch < dw * bpp) return fail(h, ICB_ERR_INVALID, "pitch smaller than a row");
+    return ICB_OK;
+}
+
+// Drives the job that holds slot s: wait = false returns false as soon as the stream still has work.
+// On true the job is finished and s->job.res is final.
+bool drive_job(icb_handle *h, Slot *s, bool wait)
+{
+    std::lock_guard<std::mutex> lk(h->slot_mu[s->index]);
+    if (s->job.phase == PH_DONE) return true;
+    int status = ICB_OK;
+    cudaSetDevice(h->devs[s->devi].dev);
+    while (true) {
+        cudaError_t e = wait ? cudaStreamSynchronize(s->stream) : cudaStreamQuery(s->stream);
+        if (!wait && e == cudaErrorNotReady) return false;
+        if (e != cudaSuccess) { status = fail(h, ICB_ERR_CUDA, "stream", e); break; }
+        if (s->job.phase == PH_RESIZE) { collect_output(s); s->job.res.status = ICB_OK; break; }
+        if (s->job.phase == PH_PNG) {
+            Job &j = s->job;
+            j.res.out_len = (size_t)*s->h_len;
+            j.res.device = h->devs[s->devi].dev;
+            status = j.res.out_len <= j.out_cap ? ICB_OK : ICB_ERR_CAPACITY;
+            if (status == ICB_OK) {
+                h->d2h += j.res.out_len;
+                if (j.stage_stream) memcpy(j.out, s->h_out, j.res.out_len);
+            }
+            break;
+        }
+        int rc = fit_advance(h, s);
+        if (rc == 0) { status = s->job.res.status; break; }
+        if (rc < 0) { status = rc; cudaStreamSynchronize(s->stream); break; }
+    }
+    s->job.res.status = status;
+    s->job.phase = PH_DONE;
+    return true;
+}
+
+Slot *slot_of_ticket(icb_handle *h, int64_t ticket)
+{
+    const size_t idx = (size_t)(ticket & 0xffff);
+    if (idx >= h->slots.size()) return nullptr;
+    Slot *s = &h->slots[idx];
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!s->busy || make_ticket(s) != ticket) return nullptr;
+    return s;
+}
+
+}  // namespace
+
+extern "C" {
 
 int icb_submit_resize_image(icb_handle *h, const icb_image *img, int dw, int dh, uint8_t *dst, int dpitch,
                             int64_t *ticket)
@@ -775,44 +1167,134 @@ int icb_submit_resize_image(icb_handle *h, const icb_image *img, int dw, int dh,
     const int bpp = bpp_of(img->fmt);
     if (dst && dpitch < dw * bpp) return fail(h, ICB_ERR_INVALID, "dpitch smaller than a row");
     Slot *s = acquire_slot(h, img->devi);
-    CK(cudaSetDevice(h->devs[s->devi].dev));
-    const int np = (int)round_up((size_t)dw * bpp, 16);
-    int rc = ensure(h, s->d_rgb2, s->rgb2_cap, (size_t)np * dh + 16);
-    if (!rc) rc = enqueue_resize(h, s, img->d_px, img->w, img->h, img->pitch, img->fmt, s->d_rgb2, dw, dh, np);
-    if (!rc && dst) {                            // dst == NULL: the resized pixels stay in HBM (kernel-only timing)
-        cudaError_t e = cudaMemcpy2DAsync(dst, dpitch, s->d_rgb2, np, (size_t)dw * bpp, dh, cudaMemcpyDeviceToHost,
-                                          s->stream);
-        if (e != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "D2H", e);
-        h->d2h += (uint64_t)dw * bpp * dh;
+    int rc = cudaSetDevice(h->devs[s->devi].dev) == cudaSuccess ? ICB_OK : fail(h, ICB_ERR_CUDA, "cudaSetDevice");
+    if (!rc) rc = start_resize(h, s, img->d_px, img->w, img->h, img->pitch, img->fmt, dw, dh, dst, dpitch);
+    if (rc) { cudaStreamSynchronize(s->stream); release_slot(h, s); return rc; }
+    *ticket = make_ticket(s);
+    return ICB_OK;
+}
+
+int icb_submit_resize(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt, uint8_t *dst, int dw, int dh,
+                      int dpitch, int64_t *ticket)
+{
+    int rc = check_resize_args(h, src, w, hgt, pitch, fmt, dst, dw, dh, dpitch);
+    if (rc) return rc;
+    if (!ticket) return ICB_ERR_INVALID;
+    const int bpp = bpp_of(fmt);
+    Slot *s = acquire_slot(h);
+    const int sp = (int)round_up((size_t)w * bpp, 16);
+    if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "cudaSetDevice");
+    if (!rc) rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)sp * hgt + 16);
+    if (!rc) rc = upload(h, s, s->d_rgb, sp, src, w, hgt, pitch, bpp);
+    if (!rc) rc = start_resize(h, s, s->d_rgb, w, hgt, sp, fmt, dw, dh, dst, dpitch);
+    if (rc) { cudaStreamSynchronize(s->stream); release_slot(h, s); return rc; }
+    *ticket = make_ticket(s);
+    return ICB_OK;
+}
+
+int icb_submit_png_fit(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt, int min_w, int min_h,
+                       uint8_t *dst, size_t dst_cap, int *dw, int *dh, int64_t *ticket)
+{
+    if (!h) return ICB_ERR_INVALID;
+    if (!src || !dst || !dw || !dh || !ticket || w < 1 || hgt < 1) return fail(h, ICB_ERR_INVALID, "null argument");   // :39-41 NPE
+    if (!fmt_valid(fmt)) return fail(h, ICB_ERR_UNSUPPORTED, "format");
+    const int rc0 = icb_png_target_dims(w, hgt, min_w, min_h, dw, dh, nullptr);
+    if (rc0) return rc0;                                            // ICB_NO_FIT: nothing queued, no ticket
+    const int bpp = bpp_of(fmt);
+    if (dst_cap < (size_t)*dw * *dh * bpp) return fail(h, ICB_ERR_CAPACITY, "dst too small");
+    return icb_submit_resize(h, src, w, hgt, pitch, fmt, dst, *dw, *dh, *dw * bpp, ticket);
+}
+
+int icb_submit_png_encode(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, int fmt, uint8_t *out,
+                          size_t out_cap, int64_t *ticket)
+{
+    if (!h) return ICB_ERR_INVALID;
+    if (!px || !out || !ticket || w < 1 || hgt < 1) return fail(h, ICB_ERR_INVALID, "null argument");
+    if (!fmt_valid(fmt)) return fail(h, ICB_ERR_UNSUPPORTED, "format");
+    const int bpp = bpp_of(fmt);
+    if (pitch < w * bpp) return fail(h, ICB_ERR_INVALID, "pitch smaller than a row");
+    Slot *s = acquire_slot(h);
+    const int sp = (int)round_up((size_t)w * bpp, 16);
+    int rc = cudaSetDevice(h->devs[s->devi].dev) == cudaSuccess ? ICB_OK : fail(h, ICB_ERR_CUDA, "cudaSetDevice");
+    if (!rc) rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)sp * hgt + 16);
+    if (!rc) rc = upload(h, s, s->d_rgb, sp, px, w, hgt, pitch, bpp);
+    if (!rc) {
+        s->job = Job();
+        s->job.out = out; s->job.out_cap = out_cap; s->job.out_pinned = is_pinned(out);
+        rc = enqueue_png(h, s, s->d_rgb, w, hgt, sp, fmt);
     }
     if (rc) { cudaStreamSynchronize(s->stream); release_slot(h, s); return rc; }
-    s->job = Job();
-    s->job.phase = PH_RESIZE;
     *ticket = make_ticket(s);
+    return ICB_OK;
+}
+
+int icb_png_encode(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, int fmt, uint8_t *out, size_t out_cap,
+                   size_t *out_len)
+{
+    int64_t t = 0;
+    int rc = icb_submit_png_encode(h, px, w, hgt, pitch, fmt, out, out_cap, &t);
+    if (rc) return rc;
+    icb_result r;
+    rc = icb_wait(h, t, &r);
+    if (out_len) *out_len = r.out_len;
+    return rc;
+}
+
+int icb_submit_png_compress(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt, int min_w, int min_h,
+                            uint8_t *out, size_t out_cap, int *dw, int *dh, int64_t *ticket)
+{
+    if (!h) return ICB_ERR_INVALID;
+    if (!src || !out || !dw || !dh || !ticket || w < 1 || hgt < 1) return fail(h, ICB_ERR_INVALID, "null argument");   // :39-41 NPE
+    if (!fmt_valid(fmt)) return fail(h, ICB_ERR_UNSUPPORTED, "format");
+    const int bpp = bpp_of(fmt);
+    if (pitch < w * bpp) return fail(h, ICB_ERR_INVALID, "pitch smaller than a row");
+    const int rc0 = icb_png_target_dims(w, hgt, min_w, min_h, dw, dh, nullptr);
+    if (rc0) return rc0;                                            // ICB_NO_FIT: the seam returns false, nothing queued
+    Slot *s = acquire_slot(h);
+    const int sp = (int)round_up((size_t)w * bpp, 16), np = (int)round_up((size_t)*dw * bpp, 16);
+    int rc = cudaSetDevice(h->devs[s->devi].dev) == cudaSuccess ? ICB_OK : fail(h, ICB_ERR_CUDA, "cudaSetDevice");
+    if (!rc) rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)sp * hgt + 16);
+    if (!rc) rc = ensure(h, s->d_rgb2, s->rgb2_cap, (size_t)np * *dh + 16);
+    if (!rc) rc = upload(h, s, s->d_rgb, sp, src, w, hgt, pitch, bpp);
+    if (!rc) rc = enqueue_resize(h, s, s->d_rgb, w, hgt, sp, fmt, s->d_rgb2, *dw, *dh, np);      // :66, pixels stay in HBM
+    if (!rc) {
+        s->job = Job();
+        s->job.out = out; s->job.out_cap = out_cap; s->job.out_pinned = is_pinned(out);
+        rc = enqueue_png(h, s, s->d_rgb2, *dw, *dh, np, fmt);                                    // :70
+    }
+    if (rc) { cudaStreamSynchronize(s->stream); release_slot(h, s); return rc; }
+    *ticket = make_ticket(s);
+    return ICB_OK;
+}
+
+int icb_png_compress(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt, int min_w, int min_h,
+                     uint8_t *out, size_t out_cap, size_t *out_len, int *dw, int *dh)
+{
+    int64_t t = 0;
+    int rc = icb_submit_png_compress(h, src, w, hgt, pitch, fmt, min_w, min_h, out, out_cap, dw, dh, &t);
+    if (rc) return rc;
+    icb_result r;
+    rc = icb_wait(h, t, &r);
+    if (out_len) *out_len = r.out_len;
+    return rc;
+}
+
+int icb_poll(icb_handle *h, int64_t ticket, int *done)
+{
+    if (!h || !done) return ICB_ERR_INVALID;
+    Slot *s = slot_of_ticket(h, ticket);
+    if (!s) return ICB_ERR_TICKET;
+    *done = drive_job(h, s, false) ? 1 : 0;
     return ICB_OK;
 }
 
 int icb_wait(icb_handle *h, int64_t ticket, icb_result *res)
 {
     if (!h) return ICB_ERR_INVALID;
-    const size_t idx = (size_t)(ticket & 0xffff);
-    if (idx >= h->slots.size()) return ICB_ERR_TICKET;
-    Slot *s = &h->slots[idx];
-    {
-        std::lock_guard<std::mutex> lk(h->mu);
-        if (!s->busy || (int64_t)((s->gen << 16) | (uint64_t)s->index) != ticket) return ICB_ERR_TICKET;
-    }
-    int status = ICB_OK;
-    cudaSetDevice(h->devs[s->devi].dev);
-    while (true) {
-        cudaError_t e = cudaStreamSynchronize(s->stream);
-        if (e != cudaSuccess) { status = fail(h, ICB_ERR_CUDA, "stream", e); break; }
-        if (s->job.phase == PH_RESIZE) { s->job.res.status = ICB_OK; break; }
-        int rc = fit_advance(h, s);
-        if (rc == 0) { status = s->job.res.status; break; }
-        if (rc < 0) { status = rc; cudaStreamSynchronize(s->stream); break; }
-    }
-    s->job.res.status = status;
+    Slot *s = slot_of_ticket(h, ticket);
+    if (!s) return ICB_ERR_TICKET;
+    drive_job(h, s, true);
+    const int status = s->job.res.status;
     if (res) *res = s->job.res;
     h->images_done++;
     release_slot(h, s);
@@ -844,13 +1326,14 @@ int icb_jpg_fit(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, int
 namespace {
 
 // upload + transform on a freshly acquired slot (synchronous helpers below use it)
-int stage_and_transform(icb_handle *h, Slot *s, const uint8_t *px, int w, int hgt, int pitch, int fmt)
+int stage_and_transform(icb_handle *h, Slot *s, const uint8_t *px, int w, int hgt, int pitch, int fmt,
+                        const FitPlan *plan)
 {
     CK(cudaSetDevice(h->devs[s->devi].dev));
     const int dp = dev_pitch(w, 3);
     int rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)dp * hgt + 16);
-    if (!rc) rc = upload(h, s->stream, s->d_rgb, dp, px, w, hgt, pitch, 3);
-    if (!rc) rc = enqueue_transform(h, s, s->d_rgb, w, hgt, dp, fmt);
+    if (!rc) rc = upload(h, s, s->d_rgb, dp, px, w, hgt, pitch, 3);
+    if (!rc) rc = enqueue_transform(h, s, s->d_rgb, w, hgt, dp, fmt, plan);
     return rc;
 }
 
@@ -869,14 +1352,16 @@ int icb_jpg_encode(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, 
     int rc = check_jpg_args(h, px, w, hgt, pitch, fmt);
     if (rc) return rc;
     if (!out_len) return ICB_ERR_INVALID;
+    if (bad_quality(q)) return fail(h, ICB_ERR_INVALID, "quality outside [0, 1]");     // ImageWriteParam.setCompressionQuality
+    const FitPlan pl = make_plan(MODE_SINGLE, q, 0, 1, false);
     Slot *s = acquire_slot(h);
-    rc = stage_and_transform(h, s, px, w, hgt, pitch, fmt);
+    rc = stage_and_transform(h, s, px, w, hgt, pitch, fmt, &pl);
     long long cap = 0;
     if (!rc) {
         cap = std::min<long long>(out ? (long long)out_cap : 0, worst_stream_bytes(s->geom));
         rc = ensure_out(h, s, cap);
     }
-    if (!rc) rc = enqueue_passes(h, s, MODE_SINGLE, q, 0, 1, true, cap);
+    if (!rc) rc = enqueue_passes(h, s, pl, true, true, cap);
     if (!rc) {
         cudaError_t e = cudaMemcpyAsync(s->h_state, s->d_state, sizeof(FitState), cudaMemcpyDeviceToHost, s->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
@@ -908,10 +1393,11 @@ int icb_jpg_sizes(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, i
     int rc = check_jpg_args(h, px, w, hgt, pitch, fmt);
     if (rc) return rc;
     if (!qs || !sizes || n < 0) return ICB_ERR_INVALID;
+    for (int i = 0; i < n; i++) if (bad_quality(qs[i])) return fail(h, ICB_ERR_INVALID, "quality outside [0, 1]");
     Slot *s = acquire_slot(h);
-    rc = stage_and_transform(h, s, px, w, hgt, pitch, fmt);
-    for (int i = 0; i < n && !rc; i++) {
-        rc = enqueue_passes(h, s, MODE_SINGLE, qs[i], 0, 1, false, 0);
+    rc = stage_and_transform(h, s, px, w, hgt, pitch, fmt, nullptr);
+    for (int i = 0; i < n && !rc; i++) {        // one transform; every size from the coefficients in HBM
+        rc = enqueue_passes(h, s, make_plan(MODE_SINGLE, qs[i], 0, 1, false), false, false, 0);
         if (rc) break;
         cudaError_t e = cudaMemcpyAsync(s->h_state, s->d_state, sizeof(FitState), cudaMemcpyDeviceToHost, s->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
@@ -931,7 +1417,7 @@ int icb_jpg_coefficients(icb_handle *h, const uint8_t *px, int w, int hgt, int p
     if (rc) return rc;
     if (!out) return ICB_ERR_INVALID;
     Slot *s = acquire_slot(h);
-    rc = stage_and_transform(h, s, px, w, hgt, pitch, fmt);
+    rc = stage_and_transform(h, s, px, w, hgt, pitch, fmt, nullptr);
     if (!rc) {
         const size_t need = (size_t)s->geom.nblocks * 64;
         if (out_elems < need) {
@@ -950,34 +1436,10 @@ int icb_jpg_coefficients(icb_handle *h, const uint8_t *px, int w, int hgt, int p
 int icb_resize_bilinear(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt, uint8_t *dst, int dw,
                         int dh, int dpitch)
 {
-    if (!h) return ICB_ERR_INVALID;
-    if (!src || !dst || w < 1 || hgt < 1 || dw < 1 || dh < 1) return fail(h, ICB_ERR_INVALID, "bad resize arguments");
-    if (fmt < ICB_FMT_RGB8 || fmt > ICB_FMT_ABGR8) return fail(h, ICB_ERR_UNSUPPORTED, "format");
-    const int bpp = bpp_of(fmt);
-    if (pitch < w * bpp || dpitch < dw * bpp) return fail(h, ICB_ERR_INVALID, "pitch smaller than a row");
-    Slot *s = acquire_slot(h);
-    int rc = ICB_OK;
-    do {
-        if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess) { rc = ICB_ERR_CUDA; break; }
-        const int sp = (int)round_up((size_t)w * bpp, 16), np = (int)round_up((size_t)dw * bpp, 16);
-        rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)sp * hgt + 16);
-        if (rc) break;
-        rc = ensure(h, s->d_rgb2, s->rgb2_cap, (size_t)np * dh + 16);
-        if (rc) break;
-        rc = upload(h, s->stream, s->d_rgb, sp, src, w, hgt, pitch, bpp);
-        if (rc) break;
-        rc = enqueue_resize(h, s, s->d_rgb, w, hgt, sp, fmt, s->d_rgb2, dw, dh, np);
-        if (rc) break;
-        cudaError_t e = cudaMemcpy2DAsync(dst, dpitch, s->d_rgb2, np, (size_t)dw * bpp, dh, cudaMemcpyDeviceToHost,
-                                          s->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
-        if (e != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "resize", e);
-        h->d2h += (uint64_t)dw * bpp * dh;
-    } while (0);
-    if (rc) cudaStreamSynchronize(s->stream);
-    h->images_done++;
-    release_slot(h, s);
-    return rc;
+    int64_t t = 0;
+    int rc = icb_submit_resize(h, src, w, hgt, pitch, fmt, dst, dw, dh, dpitch, &t);
+    if (rc) return rc;
+    return icb_wait(h, t, nullptr);
 }
 
 int icb_subsample_factor(int w, int hgt)
@@ -995,7 +1457,7 @@ int icb_subsample(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, 
 {
     if (!h) return ICB_ERR_INVALID;
     if (!src || !dst || w < 1 || hgt < 1 || sfac < 1) return fail(h, ICB_ERR_INVALID, "bad subsample arguments");
-    if (fmt < ICB_FMT_RGB8 || fmt > ICB_FMT_ABGR8) return fail(h, ICB_ERR_UNSUPPORTED, "format");
+    if (!fmt_valid(fmt)) return fail(h, ICB_ERR_UNSUPPORTED, "format");
     const int bpp = bpp_of(fmt);
     const int dw = (w + sfac - 1) / sfac, dh = (hgt + sfac - 1) / sfac;
     if (pitch < w * bpp || dpitch < dw * bpp) return fail(h, ICB_ERR_INVALID, "pitch smaller than a row");
@@ -1008,10 +1470,11 @@ int icb_subsample(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, 
         if (rc) break;
         rc = ensure(h, s->d_rgb2, s->rgb2_cap, (size_t)np * dh + 16);
         if (rc) break;
-        rc = upload(h, s->stream, s->d_rgb, sp, src, w, hgt, pitch, bpp);
+        rc = upload(h, s, s->d_rgb, sp, src, w, hgt, pitch, bpp);
         if (rc) break;
-        dim3 grid((dw + 31) / 32, (dh + 7) / 8);
+        dim3 grid((dw + 127) / 128, (dh + 7) / 8);
         if (bpp == 4) k_subsample<4><<<grid, 256, 0, s->stream>>>(s->d_rgb, sp, sfac, s->d_rgb2, dw, dh, np);
+        else if (bpp == 1) k_subsample<1><<<grid, 256, 0, s->stream>>>(s->d_rgb, sp, sfac, s->d_rgb2, dw, dh, np);
         else k_subsample<3><<<grid, 256, 0, s->stream>>>(s->d_rgb, sp, sfac, s->d_rgb2, dw, dh, np);
         h->kernels++;
         cudaError_t e = cudaGetLastError();
@@ -1056,7 +1519,7 @@ int icb_image_upload(icb_handle *h, int device_index, const uint8_t *px, int w, 
 {
     if (!h || !px || !img || w < 1 || hgt < 1) return ICB_ERR_INVALID;
     if (device_index < 0 || device_index >= (int)h->devs.size()) return fail(h, ICB_ERR_INVALID, "device index");
-    if (fmt < ICB_FMT_RGB8 || fmt > ICB_FMT_ABGR8) return fail(h, ICB_ERR_UNSUPPORTED, "format");
+    if (!fmt_valid(fmt)) return fail(h, ICB_ERR_UNSUPPORTED, "format");
     const int bpp = bpp_of(fmt);
     if (pitch < w * bpp) return fail(h, ICB_ERR_INVALID, "pitch smaller than a row");
     CK(cudaSetDevice(h->devs[device_index].dev));
@@ -1096,12 +1559,15 @@ int icb_stats(icb_handle *h, icb_stats_t *out)
     out->last_total_ms = h->last_total_ms;
     out->last_transform_launches = h->last_xf_launches;
     out->last_entropy_launches = h->last_ent_launches;
+    for (int i = 0; i < 3; i++) { out->kernel_clock_ns[i] = h->kclk_ns[i].load(); out->kernel_clock_launches[i] = h->kclk_n[i].load(); }
     return ICB_OK;
 }
 
-int icb_profile_transform_series(icb_handle *h, const icb_image *const *imgs, int n, int reps, float *ms_per_launch,
-                                 int *launches)
+int icb_profile_transform_series(icb_handle *h, const icb_image *const *imgs, int n, int reps, float list_q,
+                                 float *ms_per_launch, int *launches)
 {
+    const FitPlan pl = make_plan(MODE_SEARCH, list_q, 0, 1, false);
+    const FitPlan *plan = list_q > 0.0f ? &pl : nullptr;
     if (!h || !imgs || n < 1 || reps < 1) return ICB_ERR_INVALID;
     for (int i = 0; i < n; i++) {
         if (!imgs[i] || imgs[i]->devi != imgs[0]->devi) return ICB_ERR_INVALID;
@@ -1116,7 +1582,7 @@ int icb_profile_transform_series(icb_handle *h, const icb_image *const *imgs, in
         for (int r = -1; r < reps && !rc; r++) {            // round -1 is the untimed warm-up
             if (r == 0) cudaEventRecord(e0, s->stream);
             for (int i = 0; i < n && !rc; i++)
-                rc = enqueue_transform(h, s, imgs[i]->d_px, imgs[i]->w, imgs[i]->h, imgs[i]->pitch, imgs[i]->fmt);
+                rc = enqueue_transform(h, s, imgs[i]->d_px, imgs[i]->w, imgs[i]->h, imgs[i]->pitch, imgs[i]->fmt, plan);
         }
         if (rc) break;
         cudaEventRecord(e1, s->stream);
@@ -1126,6 +1592,40 @@ int icb_profile_transform_series(icb_handle *h, const icb_image *const *imgs, in
         cudaEventElapsedTime(&ms, e0, e1);
         if (ms_per_launch) *ms_per_launch = ms / (float)(n * reps);
         if (launches) *launches = n * reps;
+    } while (0);
+    if (rc) cudaStreamSynchronize(s->stream);
+    if (e0) cudaEventDestroy(e0);
+    if (e1) cudaEventDestroy(e1);
+    release_slot(h, s);
+    return rc;
+}
+
+int icb_profile_resize_series(icb_handle *h, const icb_image *img, int dw, int dh, int reps, int with_png,
+                              float *ms_per_launch)
+{
+    if (!h || !img || dw < 1 || dh < 1 || reps < 1 || !ms_per_launch) return ICB_ERR_INVALID;
+    Slot *s = acquire_slot(h, img->devi);
+    int rc = ICB_OK;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    do {
+        if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess || cudaEventCreate(&e0) != cudaSuccess ||
+            cudaEventCreate(&e1) != cudaSuccess) { rc = ICB_ERR_CUDA; break; }
+        const int bpp = bpp_of(img->fmt);
+        const int np = (int)round_up((size_t)dw * bpp, 16);
+        rc = ensure(h, s->d_rgb2, s->rgb2_cap, (size_t)np * dh + 16);
+        s->job = Job();
+        for (int r = -2; r < reps && !rc; r++) {            // two untimed warm-up rounds
+            if (r == 0) cudaEventRecord(e0, s->stream);
+            rc = enqueue_resize(h, s, img->d_px, img->w, img->h, img->pitch, img->fmt, s->d_rgb2, dw, dh, np);
+            if (!rc && with_png) rc = enqueue_png(h, s, s->d_rgb2, dw, dh, np, img->fmt);
+        }
+        if (rc) break;
+        cudaEventRecord(e1, s->stream);
+        cudaError_t e = cudaStreamSynchronize(s->stream);
+        if (e != cudaSuccess) { rc = fail(h, ICB_ERR_CUDA, "profile", e); break; }
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        *ms_per_launch = ms / (float)reps;
     } while (0);
     if (rc) cudaStreamSynchronize(s->stream);
     if (e0) cudaEventDestroy(e0);
@@ -1152,17 +1652,18 @@ int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q,
         if (!ok) { rc = ICB_ERR_CUDA; break; }
         for (int r = 0; r < reps && !rc; r++) {
             const uint64_t k0 = h->kernels.load();
+            const int npairs = max_search_iters(init_q);
+            const FitPlan pl = make_plan(MODE_SEARCH, init_q, target, npairs,
+                                         expect_first_pass_fails(h, img->w, img->h, init_q, target));
             cudaEventRecord(e0, s->stream);
-            rc = enqueue_transform(h, s, img->d_px, img->w, img->h, img->pitch, img->fmt);
+            rc = enqueue_transform(h, s, img->d_px, img->w, img->h, img->pitch, img->fmt, &pl);
             if (rc) break;
             const uint64_t k1 = h->kernels.load();
             cudaEventRecord(e1, s->stream);
             const long long cap = std::min<long long>(target, worst_stream_bytes(s->geom));
             rc = ensure_out(h, s, cap);
             if (rc) break;
-            const int npairs = max_search_iters(init_q);
-            rc = enqueue_passes(h, s, MODE_SEARCH, init_q, target, npairs, true, cap, pe,
-                                expect_first_pass_fails(h, img->w, img->h, init_q, target));
+            rc = enqueue_passes(h, s, pl, true, true, cap, pe);
             if (rc) break;
             cudaEventRecord(e2, s->stream);
             cudaError_t e = cudaMemcpyAsync(s->h_state, s->d_state, sizeof(FitState), cudaMemcpyDeviceToHost,
@@ -1253,3 +1754,83 @@ int icb_elapsed_ms(icb_handle *h, int device_index, float *ms)
 }
 
 }  // extern "C"
+
+// ======================================================================
+//  C ABI, part 3: the batch executor (CompressionBatch.java:64-108) in native code
+// ======================================================================
+// Executors.newFixedThreadPool(n) + one task per file-list line becomes: `threads` worker threads of this
+// library pulling items from ONE atomic cursor (work granularity = one image, so 12 MP / 24 MP / PNG
+// mixes balance over the GPUs of the handle), each keeping `inflight` jobs in the per-GPU stream work
+// queues -- upload of item k+1 overlaps the kernels of item k and the download of item k-1 on other slots.
+#include <deque>
+#include <thread>
+
+namespace {
+
+int submit_item(icb_handle *h, icb_item *it, int64_t *ticket)
+{
+    switch (it->kind) {
+    case ICB_ITEM_JPG_FIT:
+        return icb_submit_jpg_fit(h, it->px, it->w, it->h, it->pitch, it->fmt, it->init_q, it->target, it->has_cached,
+                                  it->cached_q, it->cached_scale, it->out, it->out_cap, ticket);
+    case ICB_ITEM_JPG_FIT_IMAGE:
+        return icb_submit_jpg_fit_image(h, it->img, it->init_q, it->target, it->has_cached, it->cached_q,
+                                        it->cached_scale, it->out, it->out_cap, ticket);
+    case ICB_ITEM_PNG_FIT:
+        return icb_submit_png_fit(h, it->px, it->w, it->h, it->pitch, it->fmt, it->min_w, it->min_h, it->out, it->out_cap,
+                                  &it->dw, &it->dh, ticket);
+    case ICB_ITEM_PNG_COMPRESS:
+        return icb_submit_png_compress(h, it->px, it->w, it->h, it->pitch, it->fmt, it->min_w, it->min_h, it->out,
+                                       it->out_cap, &it->dw, &it->dh, ticket);
+    case ICB_ITEM_RESIZE_IMAGE:
+        if (!it->img) return ICB_ERR_INVALID;
+        return icb_submit_resize_image(h, it->img, it->dw, it->dh, it->out, it->out ? it->dw * bpp_of(it->img->fmt) : 0,
+                                       ticket);
+    default:
+        return ICB_ERR_INVALID;
+    }
+}
+
+}  // namespace
+
+extern "C" int icb_run_list(icb_handle *h, icb_item *items, size_t n, int threads, int inflight)
+{
+    if (!h || (!items && n)) return ICB_ERR_INVALID;
+    threads = std::max(1, std::min(threads, 256));
+    // a thread that holds every slot while it asks for one more would wait for itself: cap what is in flight
+    const int slots = (int)h->slots.size();
+    inflight = std::max(1, std::min(inflight, std::max(1, slots / threads)));
+    std::atomic<size_t> cursor{0};
+    auto work = [&]() {
+        std::deque<std::pair<icb_item *, int64_t>> pending;
+        auto finish = [&]() {
+            icb_item *it = pending.front().first;
+            const int64_t t = pending.front().second;
+            pending.pop_front();
+            icb_wait(h, t, &it->res);
+        };
+        while (true) {
+            const size_t k = cursor.fetch_add(1, std::memory_order_relaxed);
+            if (k >= n) break;
+            icb_item *it = &items[k];
+            if ((int)pending.size() == inflight) finish();
+            int64_t t = 0;
+            const int rc = submit_item(h, it, &t);
+            if (rc != ICB_OK) {                     // ICB_NO_FIT from the PNG rule, or an error: nothing was queued
+                it->res = icb_result{};
+                it->res.status = rc;
+                continue;
+            }
+            pending.emplace_back(it, t);
+        }
+        while (!pending.empty()) finish();
+    };
+    if (threads == 1) {
+        work();
+    } else {
+        std::vector<std::thread> pool;
+        for (int t = 0; t < threads; t++) pool.emplace_back(work);
+        for (auto &t : pool) t.join();
+    }
+    return ICB_OK;
+}

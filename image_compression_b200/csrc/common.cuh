@@ -11,6 +11,13 @@
 
 namespace icb {
 
+__device__ __forceinline__ unsigned long long gtime()
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
 // ---- programmatic dependent launch (sm_90+): the kernels of one fit form a chain on one stream;
 // each lets its successor start early (launch latency and the successor's table set-up overlap
 // the predecessor's tail) and waits for its predecessor's results only where it first needs them
@@ -23,6 +30,49 @@ __device__ __forceinline__ void pdl_wait()
     asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
+// ---- transform kernel tiling ----
+#ifndef ICB_TILE_MCUS
+#define ICB_TILE_MCUS 21
+#endif
+// MCUs per tile (one MCU row); 48 * TILE_MCUS <= 1024 (TMA box of <= 256 words).  21 MCUs = 126 blocks: the DCT stage
+// (one thread per block) keeps 126 of 128 threads busy, and a tile's blocks make a survivor-list unit of the size the
+// entropy pass likes (measured r02: transform 23.4 -> 22.7 us at 12 MP against 16-MCU tiles)
+constexpr int TILE_MCUS = ICB_TILE_MCUS;
+constexpr int TILE_ROW_BYTES = TILE_MCUS * 48;      // bytes of RGB per pixel row of a tile
+constexpr int TILE_IN_BYTES = TILE_ROW_BYTES * 16;  // one TMA box
+constexpr int TILE_BLOCKS = TILE_MCUS * 6;          // blocks per tile
+constexpr int XF_THREADS = 128;
+#ifndef ICB_XF_STAGES
+#define ICB_XF_STAGES 2
+#endif
+#ifndef ICB_XF_CTAS
+#define ICB_XF_CTAS 5
+#endif
+constexpr int XF_STAGES = ICB_XF_STAGES;            // TMA boxes in flight per CTA
+constexpr int XF_CTAS = ICB_XF_CTAS;                // resident CTAs per SM the kernel is compiled for (register cap)
+
+// ---- survivor-list units and entropy tiles ----
+// A UNIT is the run of blocks one transform tile produces (TILE_MCUS MCUs of one MCU row, fewer at the
+// right edge): consecutive in scan order, and the transform kernel writes its survivor list while the
+// coefficients are still on chip.  An entropy TILE (what one warp codes per pass) is unit_group
+// consecutive units.  Every tile costs a fixed overhead per pass (window set-up, final flush, 0xFF
+// fold, tile record), so tiles should be large; but a pass needs a couple of thousand tiles to fill
+// 148 SMs: two units per tile once that still leaves about 2000 tiles.  The per-tile 0xFF counters
+// are 16 bits wide: 2 * TILE_BLOCKS * 208 bytes must stay below 65536.
+constexpr int UNIT_BLOCKS = TILE_BLOCKS;
+constexpr int UNIT_CAP = UNIT_BLOCKS * 64;          // survivor entries per unit, worst case (a multiple of 64)
+constexpr int MAX_UNIT_GROUP = 2;
+static_assert(MAX_UNIT_GROUP * UNIT_BLOCKS * 208 < 65536, "16-bit 0xFF counters per tile");
+
+// forced (ICB_ENT_TILE, tests): <= 128 -> one unit per tile, larger -> two
+__host__ __device__ inline int ent_unit_group(int nunits, int forced)
+{
+    if (forced > 0) return forced <= 128 ? 1 : 2;
+    return nunits >= 2 * 2000 ? 2 : 1;
+}
+// worst case per block: DC 9+11 bits, 63 x (16+10) bits = 1658 bits -> 208 B
+__host__ __device__ inline int ent_scr_stride(int unit_group) { return unit_group * UNIT_BLOCKS * 52 + 4; }   // scratch words per tile
+
 // ---- geometry (IJG jcmaster.c initial_setup, 3 components 2x2,1x1,1x1) ----
 struct Geom {
     int w, h;
@@ -32,26 +82,11 @@ struct Geom {
     int yblk_w, yblk_h;     // real luma block counts
     int crows_real;         // ceil(h/2): downsampled rows that come from pixels
     int nblocks;            // 6 * mcu_cols * mcu_rows
-    int tile_blocks;        // blocks per entropy tile: 64, 128 or 256 (ent_tile_blocks)
-    int ntiles;             // entropy tiles = ceil(nblocks / tile_blocks)
+    int units_per_row;      // transform tiles per MCU row
+    int nunits;             // survivor-list units = transform tiles
+    int unit_group;         // units per entropy tile (1 or 2)
+    int ntiles;             // entropy tiles = ceil(nunits / unit_group)
 };
-
-// Blocks per entropy tile (one warp codes one tile per pass).  Every tile costs a fixed overhead per
-// pass (window set-up, final flush, 0xFF fold, tile record), so tiles should be large; but a pass
-// needs a couple of thousand tiles to fill 148 SMs.  Measured on B200 (12 MP = 282 k blocks: 64 ->
-// 10.8 k, 128 -> 12.0 k, 256 -> 11.0 k images/s; 24 MP = 564 k blocks: 7.7 k, 9.1 k, 9.7 k): the
-// largest of 64/128/256 that still leaves about 2000 tiles.  256 is the limit of the per-tile 16-bit
-// 0xFF counters (256 * 208 bytes < 65536).  forced (ICB_ENT_TILE, tests) overrides the rule.
-__host__ __device__ inline int ent_tile_blocks(int nblocks, int forced)
-{
-    if (forced == 32 || forced == 64 || forced == 128 || forced == 256) return forced;
-    if (nblocks >= 256 * 2000) return 256;
-    if (nblocks >= 128 * 2000) return 128;
-    return 64;
-}
-__host__ __device__ inline int ent_cap(int tile_blocks) { return tile_blocks * 64; }                   // survivor entries per tile, worst case
-// worst case per block: DC 9+11 bits, 63 x (16+10) bits = 1658 bits -> 208 B
-__host__ __device__ inline int ent_scr_stride(int tile_blocks) { return tile_blocks * 52 + 4; }        // scratch words per tile
 
 __host__ __device__ inline Geom make_geom(int w, int h, int pitch, int bgr, int forced_tile = 0)
 {
@@ -63,25 +98,21 @@ __host__ __device__ inline Geom make_geom(int w, int h, int pitch, int bgr, int 
     g.yblk_h = (h + 7) >> 3;
     g.crows_real = (h + 1) >> 1;
     g.nblocks = 6 * g.mcu_cols * g.mcu_rows;
-    g.tile_blocks = ent_tile_blocks(g.nblocks, forced_tile);
-    g.ntiles = (g.nblocks + g.tile_blocks - 1) / g.tile_blocks;
+    g.units_per_row = (g.mcu_cols + TILE_MCUS - 1) / TILE_MCUS;
+    g.nunits = g.units_per_row * g.mcu_rows;
+    g.unit_group = ent_unit_group(g.nunits, forced_tile);
+    g.ntiles = (g.nunits + g.unit_group - 1) / g.unit_group;
     return g;
 }
 
-// ---- transform kernel tiling ----
-constexpr int TILE_MCUS = 16;                       // MCUs per tile (one MCU row)
-constexpr int TILE_ROW_BYTES = TILE_MCUS * 48;      // 768 B of RGB per pixel row
-constexpr int TILE_IN_BYTES = TILE_ROW_BYTES * 16;  // 12 KB per TMA box
-constexpr int TILE_BLOCKS = TILE_MCUS * 6;          // 96 blocks
-constexpr int XF_THREADS = 128;
-#ifndef ICB_XF_STAGES
-#define ICB_XF_STAGES 2
-#endif
-#ifndef ICB_XF_CTAS
-#define ICB_XF_CTAS 6
-#endif
-constexpr int XF_STAGES = ICB_XF_STAGES;            // TMA boxes in flight per CTA
-constexpr int XF_CTAS = ICB_XF_CTAS;                // resident CTAs per SM the kernel is compiled for (register cap)
+// first block (scan order) and block count of unit u
+__host__ __device__ inline void unit_span(int u, int units_per_row, int mcu_cols, int &b0, int &nb)
+{
+    const int my = u / units_per_row, tx = u - my * units_per_row;
+    const int m0 = tx * TILE_MCUS;
+    b0 = (my * mcu_cols + m0) * 6;
+    nb = 6 * (mcu_cols - m0 < TILE_MCUS ? mcu_cols - m0 : TILE_MCUS);
+}
 
 // ---- entropy pass tiling ----
 constexpr int ENT_WARPS = 8;
@@ -128,6 +159,12 @@ struct FitState {
     // pass scratch
     unsigned int done_a;            // finished CTAs of k_entropy_pass
     int pad1, pad2, pad3;
+    // kernel clock (always on): GPU global timer when block 0 of a kernel of this job started its work and
+    // when the kernel's LAST CTA finished -- the duration a kernel really has inside a busy step, with
+    // other jobs' kernels sharing the GPU (bench.py's in-step roofline).  [0] transform, [1] job start /
+    // list kernel, [2..9] entropy passes by iteration, [10] emit
+    unsigned long long kt[11][2];
+    unsigned int xf_done, emit_done; // finished CTAs of k_transform / k_entropy_emit (the last one stamps kt[.][1])
     unsigned long long dbg_k[4];    // ICB_TIMING: globaltimer at survivor-kernel start / emit start / emit end (block 0)
     unsigned long long dbg_w[24];   // ICB_TIMING: clock64 timeline of one warp of the last pass
     unsigned long long dbg_t[8][4]; // per pass: globaltimer at kernel start / tail start / step start / tail end

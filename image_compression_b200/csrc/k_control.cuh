@@ -185,10 +185,29 @@ __device__ void begin_job(FitState *st, const BeginArgs &b)
         for (int t = lane; t < 128; t += 32) table_entry(&st->tab[0], t, q0, b.table_mode);
 }
 
+// Job start after a transform that wrote the survivor lists itself (k_transform.cuh): the search state and
+// first tables, and the three DC predictors per unit that look into the previous unit (the first MCU's
+// Y00, Cb and Cr follow the previous unit's last Y11, Cb and Cr in scan order).
+constexpr int BEGIN_THREADS = 256;
+__global__ void __launch_bounds__(BEGIN_THREADS) k_job_begin(const EntParams p, const BeginArgs ba)
+{
+    pdl_launch_dependents();
+    if (blockIdx.x == 0 && threadIdx.x < 32) begin_job(p.st, ba);       // touches nothing the transform writes
+    pdl_wait();                                                         // lists and unit_info are complete
+    const int u = blockIdx.x * BEGIN_THREADS + threadIdx.x;
+    if (u < 1 || u >= p.nunits) return;
+    const uint4 prev = __ldcg(reinterpret_cast<const uint4 *>(p.unit_info) + (u - 1));   // .y = Y11 | Cb << 16, .z = Cr
+    const uint32_t pos = __ldcg(reinterpret_cast<const uint32_t *>(p.unit_info) + 4 * u);      // Cb | Cr << 16
+    uint32_t *list = p.ent + (size_t)u * UNIT_CAP;
+    list[0] |= (prev.y & 0x3fffu) << 18;
+    list[pos & 0xffffu] |= ((prev.y >> 16) & 0x3fffu) << 18;
+    list[pos >> 16] |= (prev.z & 0x3fffu) << 18;
+}
+
 // Between two passes of a long search: when the upper end of the bracket has dropped well below
 // the quality the survivor lists were built for, every midpoint still to come quantises with
 // tables at least as coarse as those of hi, so entries below the thresholds of hi are dead for the
-// rest of the job.  One warp per tile compacts its list in place (DC entries always stay: they
+// rest of the job.  One warp per unit compacts its list in place (DC entries always stay: they
 // carry the block boundaries).  A no-op otherwise; only enqueued for searches the host expects to
 // overshoot at their first midpoint (api.cu expect_first_pass_fails).
 constexpr float PRUNE_RATIO = 0.8f;
@@ -216,10 +235,10 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prune(const EntParams p
         s_thr[tb][z] = (unsigned short)(scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], hi, st->table_mode) << 2);
     }
     __syncthreads();
-    const int tile = blockIdx.x * ENT_WARPS + warp;
-    if (tile >= p.ntiles) return;
-    uint32_t *list = p.ent + (size_t)tile * p.ent_cap;
-    const uint32_t n = p.ent_cnt[tile];
+    const int unit = blockIdx.x * ENT_WARPS + warp;
+    if (unit >= p.nunits) return;
+    uint32_t *list = p.ent + (size_t)unit * UNIT_CAP;
+    const uint32_t n = p.ent_cnt[unit];
     uint32_t w = 0;
     // four chunks of 32 in flight; a chunk's stores land at or below its own first slot, and every
     // lane holds its entry of that chunk (it went into the ballot) before any of them
@@ -242,7 +261,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_prune(const EntParams p
         }
     }
     for (uint32_t i = w + lane; i < ((w + 63u) & ~63u); i += 32) list[i] = 0u;     // dead padding to a whole round (k_entropy_pass)
-    if (lane == 0) p.ent_cnt[tile] = w;
+    if (lane == 0) p.ent_cnt[unit] = w;
 }
 
 }  // namespace icb

@@ -41,13 +41,6 @@
 
 namespace icb {
 
-__device__ __forceinline__ unsigned long long gtime()
-{
-    unsigned long long t;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-    return t;
-}
-
 struct PassBufs {
     uint32_t *scratch;              // [ntiles][scr_stride] tile-local bit streams, big-endian words
     unsigned int *L;                // [ntiles] bits per tile
@@ -63,11 +56,13 @@ struct PassBufs {
 struct EntParams {
     const int16_t *coef;
     FitState *st;
-    uint32_t *ent;                  // [ntiles][ent_cap] survivor entries
-    unsigned int *ent_cnt;          // [ntiles]
+    uint32_t *ent;                  // [nunits][UNIT_CAP] survivor entries, one list per unit (common.cuh)
+    unsigned int *ent_cnt;          // [nunits]
+    unsigned short *unit_info;      // [nunits][8] links between the units' DC predictors (k_transform.cuh XfLists)
     PassBufs buf[2];                // ping-pong: the best pass so far is never overwritten
-    int nblocks, ntiles, nchunks;
-    int tile_blocks, ent_cap, scr_stride;   // blocks per tile (Geom.tile_blocks), entries and scratch words reserved per tile
+    int nblocks, nunits, ntiles, nchunks;
+    int unit_group, scr_stride;     // units per entropy tile (Geom.unit_group), scratch words reserved per tile
+    int units_per_row, mcu_cols;    // unit geometry (unit_span)
 };
 
 // select without dynamic indexing of the kernel parameter block (keeps it out of local memory)
@@ -127,7 +122,10 @@ __device__ __forceinline__ uint32_t span_ff(uint32_t ones_prev, uint32_t ones_cu
     return (r != 0u && (ones_prev >> 8) >= r && (ones_cur & 0xffu) >= 8u - r) ? 1u : 0u;
 }
 
-// Survivor extraction.  One warp per tile of 64 blocks, taken as two halves of 32: a half (4 KB of
+// Survivor extraction from the dense coefficients in HBM/L2 -- the stand-alone form (the transform kernel
+// writes the same lists itself while a tile's coefficients are on chip, k_transform.cuh; this kernel
+// serves callers that reuse coefficients: icb_jpg_sizes, the search after a missed cached try, and the
+// rebuild below).  One warp per unit, taken 32 blocks at a time: a slice (4 KB of
 // zigzag int16) is staged in shared memory with coalesced 16-byte loads, rows padded to 144 bytes
 // so that the 16-byte reads of 32 lanes standing on 32 different rows touch every bank once.  Each
 // lane then owns one whole block: 64 threshold compares into a 64-bit mask, one warp scan for the
@@ -181,26 +179,28 @@ __global__ void __launch_bounds__(PREP_THREADS, PREP_CTAS_PER_SM) k_entropy_prep
 #ifdef ICB_TIMING
     if (blockIdx.x == 0 && tid == 0) p.st->dbg_k[0] = gtime();
 #endif
+    if (!REBUILD && blockIdx.x == 0 && tid == 0) { p.st->kt[1][0] = gtime(); p.st->kt[1][1] = 0; }
     if (!REBUILD && blockIdx.x == 0 && warp == PREP_WARPS - 1) begin_job(p.st, ba);
     __syncthreads();
     if (!REBUILD) pdl_wait();       // the coefficients are complete and visible from here on
     unsigned char *ts = s_half[warp];
     const unsigned char *rp = ts + lane * PREP_ROW;
-    for (int tile = blockIdx.x * PREP_WARPS + warp; tile < p.ntiles; tile += gridDim.x * PREP_WARPS) {
-        uint32_t *out = p.ent + (size_t)tile * p.ent_cap;
+    for (int unit = blockIdx.x * PREP_WARPS + warp; unit < p.nunits; unit += gridDim.x * PREP_WARPS) {
+        uint32_t *out = p.ent + (size_t)unit * UNIT_CAP;
         uint32_t base = 0;
+        int ub0, unb;
+        unit_span(unit, p.units_per_row, p.mcu_cols, ub0, unb);
 #pragma unroll 1
-        for (int half = 0; half < p.tile_blocks / 32; half++) {
-            const int b0 = tile * p.tile_blocks + half * 32;
-            const int nb = p.nblocks - b0;              // rows of this half that exist (may be <= 0)
-            if (nb <= 0) break;
+        for (int half = 0; half * 32 < unb; half++) {
+            const int b0 = ub0 + half * 32;
+            const int nb = unb - half * 32;             // blocks of the unit from this slice on
             {
                 const uint4 *src = reinterpret_cast<const uint4 *>(p.coef) + (size_t)b0 * 8;
                 uint4 v[8];
 #pragma unroll
                 for (int r = 0; r < 8; r++) {
                     const int idx = r * 32 + lane;
-                    v[r] = (idx >> 3) < nb ? __ldg(src + idx) : make_uint4(0, 0, 0, 0);
+                    v[r] = (idx >> 3) < nb ? __ldcg(src + idx) : make_uint4(0, 0, 0, 0);
                 }
 #pragma unroll
                 for (int r = 0; r < 8; r++) {
@@ -250,7 +250,7 @@ __global__ void __launch_bounds__(PREP_THREADS, PREP_CTAS_PER_SM) k_entropy_prep
                 int xp = 0;
                 if (has_prev)
                     xp = prev >= b0 ? (int)*reinterpret_cast<const short *>(ts + (prev - b0) * PREP_ROW)
-                                    : (int)__ldg(p.coef + (size_t)prev * 64);
+                                    : (int)__ldcg(p.coef + (size_t)prev * 64);
                 out[rank++] = ENTRY_DC | tag | ((uint32_t)xp << 18) |
                               (uint32_t)*reinterpret_cast<const unsigned short *>(rp);
                 uint32_t m = lo & ~1u;
@@ -269,9 +269,9 @@ __global__ void __launch_bounds__(PREP_THREADS, PREP_CTAS_PER_SM) k_entropy_prep
             __syncwarp();                                   // the rows are free for the next half
         }
         // the list is padded with dead (zero) entries to a whole number of 64-entry rounds: the pass
-        // reads rounds without masking their tails (ent_cap is a multiple of 64)
+        // reads rounds without masking their tails (UNIT_CAP is a multiple of 64)
         for (uint32_t i = base + lane; i < ((base + 63u) & ~63u); i += 32) out[i] = 0u;
-        if (lane == 0) p.ent_cnt[tile] = base;
+        if (lane == 0) p.ent_cnt[unit] = base;
     }
 }
 
@@ -346,6 +346,8 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
     if (dbg_me) { st->dbg_w[0] = dbg_early[0]; st->dbg_w[1] = dbg_early[1]; st->dbg_w[2] = dbg_early[2]; }
 #endif
     const PassBufs pb = pick_buf(p, c2.x);
+    const int kt_slot = 2 + ((c1.x - 1) & 7);       // kernel clock of this pass (FitState.kt)
+    if (blockIdx.x == 0 && tid == 0) st->kt[kt_slot][0] = gtime();
 #ifdef ICB_TIMING
     const int dbg_pass = (c1.x - 1) & 7;
     if (blockIdx.x == 0 && threadIdx.x == 0) st->dbg_t[dbg_pass][0] = gtime();
@@ -369,19 +371,24 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
       const int tile = chunk * ENT_WARPS + warp;
       const int slot = round & (ENT_RING - 1);
       if (round && slot == 0) __syncthreads();                  // the record ring starts a new lap (rare: > 16 rounds)
-      // count and first 64 entries together: reading past the count stays inside the tile's ent_cap
-      // slots and is masked afterwards.  (Deeper look-ahead -- four rounds, or one tile ahead -- was
+      // The tile's units (one or two lists, each zero-padded to whole 64-entry rounds) are coded as one
+      // run of rounds.  Counts and the first round are requested together: every unit has at least one
+      // DC entry, so its first round exists.  (Deeper look-ahead -- four rounds, or one tile ahead -- was
       // measured slower, alone and with several fits sharing the GPU: the loop is issue bound.)
-      uint32_t n = 0;
+      // Plain (.cg) loads, not the non-coherent path: the lists are rewritten by kernels of this same
+      // stream chain that may still be running when this grid becomes resident.
+      const int u0 = tile * p.unit_group;
+      uint32_t rounds0 = 0, rounds = 0;
       uint2 e_first = make_uint2(0u, 0u);
       if (tile < p.ntiles) {
-          n = __ldg(p.ent_cnt + tile);
-          e_first = __ldg(reinterpret_cast<const uint2 *>(p.ent + (size_t)tile * p.ent_cap) + lane);
+          rounds0 = (__ldcg(p.ent_cnt + u0) + 63u) >> 6;
+          rounds = rounds0;
+          if (p.unit_group > 1 && u0 + 1 < p.nunits) rounds += (__ldcg(p.ent_cnt + u0 + 1) + 63u) >> 6;
+          e_first = __ldcg(reinterpret_cast<const uint2 *>(p.ent + (size_t)u0 * UNIT_CAP) + lane);
       }
       ICB_STAMP();                  // 5 / 10: tile start
       if (tile < p.ntiles) {
         uint32_t *scr = pb.scratch + (size_t)tile * p.scr_stride;
-        const uint32_t *ent = p.ent + (size_t)tile * p.ent_cap;
         uint32_t running = 0;       // bits produced so far (tile-local)
         uint32_t flushed = 0;       // whole words already copied to scratch
         uint32_t acc[4] = {0, 0, 0, 0};     // 0xFF counters, 2 x 16 bits each: local start bit s = 0,1 | 2,3 | 4,5 | 6,7
@@ -539,13 +546,13 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             if ((running >> 5) - flushed > (uint32_t)(ENT_WIN - 128)) flush_some();   // a round adds <= 118 words
         };
 
-        const uint2 *ent2 = reinterpret_cast<const uint2 *>(ent);
-        uint2 e_next = 2u * lane < n ? e_first : make_uint2(0u, 0u);         // (an empty list has no padding to read)
-        for (uint32_t i0 = 0; i0 < n; i0 += 64) {
+        const uint2 *ent2 = reinterpret_cast<const uint2 *>(p.ent + (size_t)u0 * UNIT_CAP) + lane;
+        uint2 e_next = e_first;
+        for (uint32_t r = 0; r < rounds; r++) {
             const uint2 e = e_next;
-            const uint32_t ni = i0 + 64u + 2u * lane;                   // next round's entries fly while this one is coded
-            e_next = ni < n ? __ldg(ent2 + (ni >> 1)) : make_uint2(0u, 0u);  // tails are zero-padded by the list writers
-            code_round(e);
+            const uint32_t rn = r + 1;                                  // next round's entries fly while this one is coded
+            if (rn < rounds) e_next = __ldcg(rn < rounds0 ? ent2 + 32u * rn : ent2 + UNIT_CAP / 2 + 32u * (rn - rounds0));
+            code_round(e);                                              // (tails are zero-padded by the list writers)
         }
         ICB_STAMP();                // 7 / 12: rounds done
         if (carry < 126u) {                                     // EOB of the tile's last block
@@ -716,6 +723,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
     if (tid == 0) st->dbg_t[dbg_pass][2] = gtime();
 #endif
     if (warp == 0) device_step(st, reinterpret_cast<const FitState *>(s_ctl), 0, s_total[0], s_total[1]);      // :176-189 on the exact size, then the next table slot
+    if (tid == 0) st->kt[kt_slot][1] = gtime();
 #ifdef ICB_TIMING
     if (tid == 0) st->dbg_t[dbg_pass][3] = gtime();
 #endif
@@ -775,35 +783,10 @@ __device__ __forceinline__ uint32_t tile_word(const TileView &v, uint32_t w, uin
 __constant__ unsigned char c_hdr[HEADER_BYTES];
 constexpr int HDR_OFF_MINOR = 12, HDR_OFF_DQT0 = 25, HDR_OFF_DQT1 = 94, HDR_OFF_H = 163, HDR_OFF_W = 165;
 
-// once per image: header (a2.8), a2.7 emit_bits byte stuffing of the chosen pass, EOI
-__global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p, unsigned char *out, long long cap,
-                                                              int img_w, int img_h)
+// one tile of the chosen pass: its bits at their absolute alignment, stuffed, at their final offsets (one warp)
+__device__ __forceinline__ void emit_tile(const EntParams &p, const PassBufs &pb, const FitState *st, unsigned char *out,
+                                          long long cap, int tile, int lane)
 {
-    const FitState *st = p.st;
-    pdl_wait();
-    if (st->best_size <= 0 || out == nullptr) return;
-#ifdef ICB_TIMING
-    if (blockIdx.x == 0 && threadIdx.x == 0) const_cast<FitState *>(st)->dbg_k[1] = gtime();
-#endif
-    const int best_buf = st->best_buf;
-    const PassBufs pb = pick_buf(p, best_buf);
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (blockIdx.x == 0) {
-        for (int i = tid; i < HEADER_BYTES; i += ENT_THREADS) {
-            unsigned char b = c_hdr[i];
-            if (i == HDR_OFF_MINOR) b = (unsigned char)st->jfif_minor;
-            else if (i >= HDR_OFF_DQT0 && i < HDR_OFF_DQT0 + 64) b = st->cand_qtab[best_buf][0][i - HDR_OFF_DQT0];
-            else if (i >= HDR_OFF_DQT1 && i < HDR_OFF_DQT1 + 64) b = st->cand_qtab[best_buf][1][i - HDR_OFF_DQT1];
-            else if (i == HDR_OFF_H) b = (unsigned char)(img_h >> 8);
-            else if (i == HDR_OFF_H + 1) b = (unsigned char)img_h;
-            else if (i == HDR_OFF_W) b = (unsigned char)(img_w >> 8);
-            else if (i == HDR_OFF_W + 1) b = (unsigned char)img_w;
-            if (i < cap) out[i] = b;
-        }
-    }
-    const int tile = blockIdx.x * ENT_WARPS + warp;
-    if (tile >= p.ntiles) return;
-
     // this tile's bit prefix and the 0xFF bytes completed before it: the chunk prefixes of the pass
     // plus the tiles in front of it inside its chunk of 8 (lane = tile of the chunk)
     const int chunk = tile / ENT_WARPS, t_first = chunk * ENT_WARPS, me = tile - t_first;
@@ -875,11 +858,87 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
     }
 }
 
+// once per image: header (a2.8), a2.7 emit_bits byte stuffing of the chosen pass, EOI
+__global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p, unsigned char *out, long long cap,
+                                                              int img_w, int img_h)
+{
+    const FitState *st = p.st;
+    pdl_wait();
+    if (st->best_size <= 0 || out == nullptr) return;
+    if (blockIdx.x == 0 && threadIdx.x == 0) const_cast<FitState *>(st)->kt[10][0] = gtime();
+#ifdef ICB_TIMING
+    if (blockIdx.x == 0 && threadIdx.x == 0) const_cast<FitState *>(st)->dbg_k[1] = gtime();
+#endif
+    const int best_buf = st->best_buf;
+    const PassBufs pb = pick_buf(p, best_buf);
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (blockIdx.x == 0) {
+        for (int i = tid; i < HEADER_BYTES; i += ENT_THREADS) {
+            unsigned char b = c_hdr[i];
+            if (i == HDR_OFF_MINOR) b = (unsigned char)st->jfif_minor;
+            else if (i >= HDR_OFF_DQT0 && i < HDR_OFF_DQT0 + 64) b = st->cand_qtab[best_buf][0][i - HDR_OFF_DQT0];
+            else if (i >= HDR_OFF_DQT1 && i < HDR_OFF_DQT1 + 64) b = st->cand_qtab[best_buf][1][i - HDR_OFF_DQT1];
+            else if (i == HDR_OFF_H) b = (unsigned char)(img_h >> 8);
+            else if (i == HDR_OFF_H + 1) b = (unsigned char)img_h;
+            else if (i == HDR_OFF_W) b = (unsigned char)(img_w >> 8);
+            else if (i == HDR_OFF_W + 1) b = (unsigned char)img_w;
+            if (i < cap) out[i] = b;
+        }
+    }
+    const int tile = blockIdx.x * ENT_WARPS + warp;
+    if (tile < p.ntiles) emit_tile(p, pb, st, out, cap, tile, lane);
+    __syncthreads();
+    if (tid == 0) {                                 // kernel clock: the last CTA to finish stamps the end
+        FitState *w = const_cast<FitState *>(st);
+        if (atomicAdd(&w->emit_done, 1u) == gridDim.x - 1u) { w->emit_done = 0; w->kt[10][1] = gtime(); }
+    }
+}
+
+// After the emit kernel: the chosen stream goes to the caller -- exactly best_size bytes of it, and only if the
+// phase succeeded (a missed cached try or a scale that did not fit sends nothing).  The size is known on the
+// device only, so the copy is a kernel: 16-byte loads from HBM, 16-byte stores into page-locked host memory
+// (zero-copy over PCIe); a cudaMemcpyAsync would have to be sized by the host after a round trip.
+constexpr int FETCH_THREADS = 256;
+__global__ void __launch_bounds__(FETCH_THREADS) k_fetch_stream(const FitState *st, const unsigned char *d_out, long long d_cap,
+                                                                unsigned char *h_out, long long h_cap)
+{
+    pdl_wait();
+    const long long n = st->best_size;
+    if (n <= 0 || n > st->target || n > d_cap || n > h_cap) return;
+    const long long nvec = n >> 4;
+    const uint4 *src = reinterpret_cast<const uint4 *>(d_out);
+    uint4 *dst = reinterpret_cast<uint4 *>(h_out);
+    for (long long i = (long long)blockIdx.x * FETCH_THREADS + threadIdx.x; i < nvec; i += (long long)gridDim.x * FETCH_THREADS)
+        dst[i] = __ldcg(src + i);
+    if (blockIdx.x == 0 && threadIdx.x < (n & 15)) h_out[(nvec << 4) + threadIdx.x] = d_out[(nvec << 4) + threadIdx.x];
+}
+
+// the same for a byte string whose length sits in device memory (the PNG file, k_png.cuh)
+__global__ void __launch_bounds__(FETCH_THREADS) k_fetch_len(const unsigned long long *len, const unsigned char *d_src,
+                                                             long long d_cap, unsigned char *h_out, long long h_cap)
+{
+    const long long n = (long long)*len;
+    if (n <= 0 || n > d_cap || n > h_cap) return;
+    const long long nvec = n >> 4;
+    const uint4 *src = reinterpret_cast<const uint4 *>(d_src);
+    uint4 *dst = reinterpret_cast<uint4 *>(h_out);
+    for (long long i = (long long)blockIdx.x * FETCH_THREADS + threadIdx.x; i < nvec; i += (long long)gridDim.x * FETCH_THREADS)
+        dst[i] = __ldcg(src + i);
+    if (blockIdx.x == 0 && threadIdx.x < (n & 15)) h_out[(nvec << 4) + threadIdx.x] = d_src[(nvec << 4) + threadIdx.x];
+}
+
 // per-slot arenas
 __host__ __device__ inline size_t ent_pass_bytes(int ntiles, int nchunks, int scr_stride)
 {
     const size_t n = (size_t)ntiles, c = (size_t)nchunks;
     return n * (size_t)scr_stride * 4 + n * 4 + n * 16 + n * 4 + c * 48 + c * 8 + c * 4 + ENT_THREADS * 4 + 256;
+}
+
+// survivor lists + counts + unit links of one image
+__host__ __device__ inline size_t ent_list_bytes(int nunits)
+{
+    const size_t n = (size_t)nunits;
+    return n * (size_t)UNIT_CAP * 4 + ((n + 3) / 4 * 4) * 4 + n * 16 + 256;
 }
 
 }  // namespace icb

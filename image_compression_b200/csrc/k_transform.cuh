@@ -32,6 +32,7 @@
 
 #include <cuda.h>
 #include "common.cuh"
+#include "k_control.cuh"
 #include "xf_arith.cuh"
 
 namespace icb {
@@ -98,21 +99,101 @@ __device__ __forceinline__ int samp_chunk(int blk, int chunk)     // in 16-byte 
     return blk * 4 + (chunk ^ ((blk >> 1) & 3));
 }
 
+// natural index -> zigzag position
+__device__ constexpr unsigned char kZZinv[64] = {
+    0, 1, 5, 6, 14, 15, 27, 28, 2, 4, 7, 13, 16, 26, 29, 42,
+    3, 8, 12, 17, 25, 30, 41, 43, 9, 11, 18, 24, 31, 40, 44, 53,
+    10, 19, 23, 32, 39, 45, 52, 54, 20, 22, 33, 38, 46, 51, 55, 60,
+    21, 34, 37, 47, 50, 56, 59, 61, 35, 36, 48, 49, 57, 58, 62, 63};
+
+// Survivor lists written by the transform kernel (k_entropy.cuh has the consumer side): the unit of
+// tile t gets its entries while the tile's coefficients are still in shared memory.  ent == nullptr
+// switches the lists off (coefficient-only callers).
+struct XfLists {
+    uint32_t *ent;                  // [nunits][UNIT_CAP]
+    unsigned int *ent_cnt;          // [nunits]
+    unsigned short *unit_info;      // [nunits][8]: entry index of the first MCU's Cb / Cr DC entry, raw DC of the
+                                    //              last MCU's Y11 / Cb / Cr (k_job_begin links the units with them)
+    float list_q;                   // quality whose tables bound the lists (k_entropy_prepare has the rule)
+    int table_mode;
+    FitState *st;                   // kernel clock of the job (FitState.kt[0]); nullptr: not a fit job
+};
+
+// survivor test on a column-pass result d = x * 65536 + junk (0 <= junk < 65536): |x| >= t  <=>  d lies
+// outside [(1 - t) << 16, t << 16)  <=>  (unsigned)(d - A) >= B with A = (1 - t) << 16, B = (2 t - 1) << 16
+template <int NAT>
+__device__ __forceinline__ void xf_test(int d, uint32_t A, uint32_t B, uint32_t &mlo, uint32_t &mhi)
+{
+    constexpr int z = kZZinv[NAT];
+    constexpr uint32_t blo = z < 32 ? 1u << (z & 31) : 0u, bhi = z < 32 ? 0u : 1u << (z & 31);
+    if ((uint32_t)d - A >= B) {
+        if (z < 32) mlo |= blo; else mhi |= bhi;
+    }
+}
+
+// fdct_block_col (xf_arith.cuh) plus the survivor mask of column K: thr = this block's table,
+// [4 K + j] = (A, B) of rows 2 j and 2 j + 1
+template <int K>
+__device__ __forceinline__ void fdct_block_col_m(const uint32_t (&sw)[16], uint32_t (&P)[32], const uint4 *thr,
+                                                 uint32_t &mlo, uint32_t &mhi)
+{
+    int v0 = fdct_row_k<K>(sw[0], sw[1]), v1 = fdct_row_k<K>(sw[2], sw[3]);
+    int v2 = fdct_row_k<K>(sw[4], sw[5]), v3 = fdct_row_k<K>(sw[6], sw[7]);
+    int v4 = fdct_row_k<K>(sw[8], sw[9]), v5 = fdct_row_k<K>(sw[10], sw[11]);
+    int v6 = fdct_row_k<K>(sw[12], sw[13]), v7 = fdct_row_k<K>(sw[14], sw[15]);
+    fdct_col_hi16(v0, v1, v2, v3, v4, v5, v6, v7);
+    uint4 t = thr[4 * K];
+    xf_test<K>(v0, t.x, t.y, mlo, mhi); xf_test<8 + K>(v1, t.z, t.w, mlo, mhi);
+    t = thr[4 * K + 1];
+    xf_test<16 + K>(v2, t.x, t.y, mlo, mhi); xf_test<24 + K>(v3, t.z, t.w, mlo, mhi);
+    t = thr[4 * K + 2];
+    xf_test<32 + K>(v4, t.x, t.y, mlo, mhi); xf_test<40 + K>(v5, t.z, t.w, mlo, mhi);
+    t = thr[4 * K + 3];
+    xf_test<48 + K>(v6, t.x, t.y, mlo, mhi); xf_test<56 + K>(v7, t.z, t.w, mlo, mhi);
+    P[4 * K + 0] = prmt((uint32_t)v0, (uint32_t)v1, 0x7632);
+    P[4 * K + 1] = prmt((uint32_t)v2, (uint32_t)v3, 0x7632);
+    P[4 * K + 2] = prmt((uint32_t)v4, (uint32_t)v5, 0x7632);
+    P[4 * K + 3] = prmt((uint32_t)v6, (uint32_t)v7, 0x7632);
+}
+
+constexpr int XF_OFF_SAMP = XF_STAGES * TILE_IN_BYTES;
+constexpr int XF_OFF_BAR = XF_OFF_SAMP + TILE_BLOCKS * 64;
+constexpr int XF_OFF_THR = XF_OFF_BAR + 64;             // 2 tables x 64 x (A, B)
+constexpr int XF_OFF_WTOT = XF_OFF_THR + 1024;
+constexpr int XF_SMEM_BYTES = XF_OFF_WTOT + 64;
+static_assert(XF_OFF_BAR % 16 == 0, "shared-memory carve-up");
+
 template <bool BGR>
 __global__ void __launch_bounds__(XF_THREADS, XF_CTAS)
 k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__restrict__ coef,
-            int tiles_per_row, int ntiles)
+            int tiles_per_row, int ntiles, const XfLists xl)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    unsigned char *in_buf = smem_raw;                                             // XF_STAGES x 12 KB
-    uint4 *samp = reinterpret_cast<uint4 *>(smem_raw + XF_STAGES * TILE_IN_BYTES);    // 96 blocks x 64 sample bytes
-    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + XF_STAGES * TILE_IN_BYTES + TILE_BLOCKS * 64);
+    unsigned char *in_buf = smem_raw;                                             // XF_STAGES TMA boxes
+    uint4 *samp = reinterpret_cast<uint4 *>(smem_raw + XF_OFF_SAMP);              // TILE_BLOCKS x 64 sample bytes
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + XF_OFF_BAR);
+    uint4 *s_thr = reinterpret_cast<uint4 *>(smem_raw + XF_OFF_THR);              // [table][4 K + j]
+    uint32_t *s_wtot = reinterpret_cast<uint32_t *>(smem_raw + XF_OFF_WTOT);      // survivor entries per warp of blocks
 
-    const int tid = threadIdx.x;
-    pdl_launch_dependents();        // k_entropy_prepare may set up while this grid drains
+    const int tid = threadIdx.x, lane = tid & 31;
+    const bool lists = xl.ent != nullptr;
+    pdl_launch_dependents();        // the job-start kernel may set up while this grid drains
     if (tid == 0) {
+        if (blockIdx.x == 0 && xl.st) xl.st->kt[0][0] = gtime();
         for (int s = 0; s < XF_STAGES; s++) mbar_init(&full[s], 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // survivor thresholds of the quality the lists are built for (a coefficient is non-zero at quality q
+    // iff |x| >= 4 * table(q), and table(q) never grows with q); without lists nothing survives the test
+    {
+        const int tb = tid >> 6, nat = tid & 63, r = nat >> 3, K = nat & 7;
+        uint32_t A = 0x80000000u, B = 0xffffffffu;
+        if (lists) {
+            const int t = scaled_qval(tb ? c_base_chr[nat] : c_base_lum[nat], xl.list_q, xl.table_mode) << 2;
+            A = (uint32_t)((1 - t) * 65536);
+            B = (uint32_t)((2 * t - 1) * 65536);
+        }
+        reinterpret_cast<uint2 *>(s_thr)[tb * 64 + K * 8 + r] = make_uint2(A, B);
     }
     __syncthreads();
 
@@ -138,15 +219,13 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
         unsigned char *tile = in_buf + s * TILE_IN_BYTES;
         mbar_wait(&full[s], parity);
 
-#ifndef ICB_XF_DBG
-#define ICB_XF_DBG 0        // experiments only: 1 = no arithmetic (TMA in, barriers, copy-out), 2 = no global stores
-#endif
         // ---- stage A: colour conversion + 4:2:0 downsample, 8x2-pixel strips ----
 #pragma unroll
-        for (int round = 0; round < ((ICB_XF_DBG & 1) ? 0 : 2); round++) {
+        for (int round = 0; round < (TILE_MCUS * 16 + XF_THREADS - 1) / XF_THREADS; round++) {
             const int sid = tid + round * XF_THREADS;
-            const int sc = sid & 31, sr = sid >> 5;
+            const int sr = sid / (2 * TILE_MCUS), sc = sid - sr * (2 * TILE_MCUS);
             const int m = sc >> 1, xi = sc & 1;
+            if ((TILE_MCUS * 16) % XF_THREADS != 0 && sid >= TILE_MCUS * 16) continue;
             if (mcu0 + m >= g.mcu_cols) continue;
             const int x0 = mcu0 * 16 + sc * 8, y0 = my * 16 + 2 * sr;
             const int yblk = m * 6 + (sr >> 2) * 2 + xi;
@@ -202,86 +281,120 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
         __syncthreads();            // samples complete; the RGB tile is dead
 
         // ---- stage B: one thread = one 8x8 block, both DCT passes in registers ----
-        // 96 blocks on 4 warps: one warp sits a tile out.  Which one rotates with the tile count
-        // and with the CTA's position among the CTAs sharing the SM, so that every SM
-        // sub-partition (warp w of each CTA lands on sub-partition w) carries 3/4 of the DCT work
-        // instead of three of them carrying all of it.
-        const int vt = (tid + 32 * ((k + cta_slot) & 3)) & (XF_THREADS - 1);
-        if (!(ICB_XF_DBG & 1) && vt < TILE_BLOCKS) {
-            const int blk = vt;
-            const int m = blk / 6, c = blk - m * 6;
-            const int gx = mcu0 + m;
-            if (gx < g.mcu_cols) {
-                int src = blk;
-                bool dummy = false;
-                if (c < 4) {        // jccoefct.c dummy blocks (a2.6): luma only
-                    const int yi = c >> 1, xi = c & 1;
-                    const bool row_real = (2 * my + yi) < g.yblk_h;
-                    const bool col_real = (2 * gx + xi) < g.yblk_w;
-                    if (!(row_real && col_real)) {
-                        dummy = true;
-                        if (row_real) src = m * 6 + yi * 2;                       // block to its left
-                        else src = m * 6 + ((2 * gx + 1) < g.yblk_w ? 1 : 0);   // MCU_buffer[blkn-1]
-                    }
+        // With fewer blocks than threads one warp sits a tile out.  Which one rotates with the tile
+        // count and with the CTA's position among the CTAs sharing the SM, so that every SM
+        // sub-partition (warp w of each CTA lands on sub-partition w) carries its share of the DCT work.
+        const int vt = TILE_BLOCKS <= XF_THREADS - 32 ? (tid + 32 * ((k + cta_slot) & 3)) & (XF_THREADS - 1) : tid;
+        const int nm = min(TILE_MCUS, g.mcu_cols - mcu0);       // MCUs of this tile
+        uint32_t mlo = 0, mhi = 0;                              // survivor mask of this thread's block, zigzag positions
+        const int blk = vt;
+        const int bm = blk / 6, bc = blk - bm * 6;
+        const bool have = blk < TILE_BLOCKS && bm < nm;
+        if (have) {
+            const int gx = mcu0 + bm;
+            int src = blk;
+            bool dummy = false;
+            if (bc < 4) {        // jccoefct.c dummy blocks (a2.6): luma only
+                const int yi = bc >> 1, xi = bc & 1;
+                const bool row_real = (2 * my + yi) < g.yblk_h;
+                const bool col_real = (2 * gx + xi) < g.yblk_w;
+                if (!(row_real && col_real)) {
+                    dummy = true;
+                    if (row_real) src = bm * 6 + yi * 2;                       // block to its left
+                    else src = bm * 6 + ((2 * gx + 1) < g.yblk_w ? 1 : 0);    // MCU_buffer[blkn-1]
                 }
-                uint32_t sw[16];
-#pragma unroll
-                for (int ch = 0; ch < 4; ch++) {
-                    const uint4 v = samp[samp_chunk(src, ch)];
-                    sw[4 * ch] = v.x; sw[4 * ch + 1] = v.y; sw[4 * ch + 2] = v.z; sw[4 * ch + 3] = v.w;
-                }
-#ifdef ICB_XF_ROWMAJOR      // kept for A/B: all 64 intermediates alive between the passes (122 registers)
-                int d[64];
-#pragma unroll
-                for (int r = 0; r < 8; r++) fdct_row_bytes(sw[2 * r], sw[2 * r + 1], &d[8 * r]);
-#pragma unroll
-                for (int cc = 0; cc < 8; cc++)
-                    fdct_col_hi16(d[cc], d[8 + cc], d[16 + cc], d[24 + cc], d[32 + cc], d[40 + cc], d[48 + cc],
-                                  d[56 + cc]);
-                if (dummy) {
-#pragma unroll
-                    for (int i = 1; i < 64; i++) d[i] = 0;
-                }
-                // zigzag + int16 pack (upper half-words, see fdct_col_hi16) into the (now free) RGB stage buffer, swizzled chunks
-                uint4 *outp = reinterpret_cast<uint4 *>(tile + blk * 128);
-#pragma unroll
-                for (int kk = 0; kk < 8; kk++) {
-                    uint4 o;
-                    o.x = __byte_perm(d[kZZ[8 * kk + 0]], d[kZZ[8 * kk + 1]], 0x7632);
-                    o.y = __byte_perm(d[kZZ[8 * kk + 2]], d[kZZ[8 * kk + 3]], 0x7632);
-                    o.z = __byte_perm(d[kZZ[8 * kk + 4]], d[kZZ[8 * kk + 5]], 0x7632);
-                    o.w = __byte_perm(d[kZZ[8 * kk + 6]], d[kZZ[8 * kk + 7]], 0x7632);
-                    outp[kk ^ (blk & 7)] = o;
-                }
-#else
-                uint32_t P[32];
-                fdct_block_bytes(sw, P);
-                if (dummy) {
-                    P[0] &= 0xffffu;
-#pragma unroll
-                    for (int i = 1; i < 32; i++) P[i] = 0;
-                }
-                // zigzag + int16 pack into the (now free) RGB stage buffer, swizzled chunks
-                uint4 *outp = reinterpret_cast<uint4 *>(tile + blk * 128);
-                uint4 o;
-#define ICB_CHUNK(KK) fdct_zz_chunk<KK>(P, o.x, o.y, o.z, o.w); outp[KK ^ (blk & 7)] = o;
-                ICB_CHUNK(0) ICB_CHUNK(1) ICB_CHUNK(2) ICB_CHUNK(3) ICB_CHUNK(4) ICB_CHUNK(5) ICB_CHUNK(6) ICB_CHUNK(7)
-#undef ICB_CHUNK
-#endif
             }
+            uint32_t sw[16];
+#pragma unroll
+            for (int ch = 0; ch < 4; ch++) {
+                const uint4 v = samp[samp_chunk(src, ch)];
+                sw[4 * ch] = v.x; sw[4 * ch + 1] = v.y; sw[4 * ch + 2] = v.z; sw[4 * ch + 3] = v.w;
+            }
+            uint32_t P[32];
+            const uint4 *thr = s_thr + (bc >= 4 ? 32 : 0);
+            fdct_block_col_m<0>(sw, P, thr, mlo, mhi); fdct_block_col_m<1>(sw, P, thr, mlo, mhi);
+            fdct_block_col_m<2>(sw, P, thr, mlo, mhi); fdct_block_col_m<3>(sw, P, thr, mlo, mhi);
+            fdct_block_col_m<4>(sw, P, thr, mlo, mhi); fdct_block_col_m<5>(sw, P, thr, mlo, mhi);
+            fdct_block_col_m<6>(sw, P, thr, mlo, mhi); fdct_block_col_m<7>(sw, P, thr, mlo, mhi);
+            if (dummy) {
+                P[0] &= 0xffffu;
+#pragma unroll
+                for (int i = 1; i < 32; i++) P[i] = 0;
+                mlo = 0; mhi = 0;
+            }
+            mlo |= 1u;                                          // DC always codes a symbol
+            // zigzag + int16 pack into the (now free) RGB stage buffer, swizzled chunks
+            uint4 *outp = reinterpret_cast<uint4 *>(tile + blk * 128);
+            uint4 o;
+#define ICB_CHUNK(KK) fdct_zz_chunk<KK>(P, o.x, o.y, o.z, o.w); outp[KK ^ (blk & 7)] = o;
+            ICB_CHUNK(0) ICB_CHUNK(1) ICB_CHUNK(2) ICB_CHUNK(3) ICB_CHUNK(4) ICB_CHUNK(5) ICB_CHUNK(6) ICB_CHUNK(7)
+#undef ICB_CHUNK
+        }
+        // entries in front of this block inside the unit: warp scan now, the warps' totals across the barrier
+        uint32_t cnt = 0, incl = 0;
+        if (lists) {
+            cnt = __popc(mlo) + __popc(mhi);
+            incl = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t u = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += u;
+            }
+            if (lane == 31) s_wtot[vt >> 5] = incl;
         }
         __syncthreads();            // coefficients staged
 
-        // ---- copy-out: 96 blocks x 128 B, consecutive lanes -> consecutive 16 B ----
+        // ---- survivor list of the unit (k_entropy.cuh entry format), from the staged coefficients ----
+        if (lists) {
+            uint32_t *out = xl.ent + (size_t)t * UNIT_CAP;
+            const uint32_t w0 = s_wtot[0], w1 = s_wtot[1], w2 = s_wtot[2], w3 = s_wtot[3];
+            const int vw = vt >> 5;
+            uint32_t rank = incl - cnt + (vw > 0 ? w0 : 0u) + (vw > 1 ? w1 : 0u) + (vw > 2 ? w2 : 0u);
+            const uint32_t total = w0 + w1 + w2 + w3;
+            if (have) {
+                const unsigned char *mine = tile + blk * 128;
+                const int sw7 = blk & 7;
+                const uint32_t tag = bc >= 4 ? 1u << 17 : 0u;
+                // DC predictor = previous block of the same component in scan order; the first MCU's Y00, Cb
+                // and Cr look into the previous unit: k_job_begin fills those three in
+                int pb = blk - 1;
+                if (bc == 0) pb = blk - 3; else if (bc >= 4) pb = blk - 6;
+                int xp = 0;
+                if (pb >= 0) xp = *reinterpret_cast<const short *>(tile + pb * 128 + (pb & 7) * 16);
+                const uint32_t dc = *reinterpret_cast<const unsigned short *>(mine + sw7 * 16);
+                if (bm == 0 && bc >= 4) xl.unit_info[8 * (size_t)t + (bc - 4)] = (unsigned short)rank;
+                if (bm == nm - 1 && bc >= 3) xl.unit_info[8 * (size_t)t + 2 + (bc - 3)] = (unsigned short)dc;
+                out[rank++] = ENTRY_DC | tag | ((uint32_t)xp << 18) | dc;
+                uint32_t m = mlo & ~1u;
+                while (m) {
+                    const uint32_t z = __ffs(m) - 1;
+                    m &= m - 1;
+                    out[rank++] = (uint32_t)*reinterpret_cast<const unsigned short *>(mine + (((z >> 3) ^ sw7) << 4) + ((z & 7) << 1)) |
+                                  tag | (z << 18);
+                }
+                m = mhi;
+                while (m) {
+                    const uint32_t z = __ffs(m) + 31;
+                    m &= m - 1;
+                    out[rank++] = (uint32_t)*reinterpret_cast<const unsigned short *>(mine + (((z >> 3) ^ sw7) << 4) + ((z & 7) << 1)) |
+                                  tag | (z << 18);
+                }
+            }
+            // dead (zero) entries up to a whole 64-entry round: the pass reads rounds without masking tails
+            for (uint32_t i = total + tid; i < ((total + 63u) & ~63u); i += XF_THREADS) out[i] = 0u;
+            if (tid == 0) xl.ent_cnt[t] = total;
+        }
+
+        // ---- copy-out: TILE_BLOCKS x 128 B, consecutive lanes -> consecutive 16 B ----
         {
             const size_t base = ((size_t)my * g.mcu_cols + mcu0) * 6;
             uint4 *gout = reinterpret_cast<uint4 *>(coef) + base * 8;
 #pragma unroll
-            for (int i = 0; i < (TILE_BLOCKS * 8) / XF_THREADS; i++) {
+            for (int i = 0; i < (TILE_BLOCKS * 8 + XF_THREADS - 1) / XF_THREADS; i++) {
                 const int idx = tid + i * XF_THREADS;
-                const int blk = idx >> 3, kk = idx & 7;
-                if (!(ICB_XF_DBG & 2) && mcu0 + blk / 6 < g.mcu_cols) {
-                    uint4 v = reinterpret_cast<const uint4 *>(tile + blk * 128)[kk ^ (blk & 7)];
+                const int b = idx >> 3, kk = idx & 7;
+                if (((TILE_BLOCKS * 8) % XF_THREADS == 0 || idx < TILE_BLOCKS * 8) && b < nm * 6) {
+                    uint4 v = reinterpret_cast<const uint4 *>(tile + b * 128)[kk ^ (b & 7)];
                     gout[idx] = v;
                 }
             }
@@ -298,8 +411,9 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
             }
         }
     }
+    if (tid == 0 && xl.st) {        // kernel clock: the last CTA to finish stamps the end
+        if (atomicAdd(&xl.st->xf_done, 1u) == gridDim.x - 1u) { xl.st->xf_done = 0; xl.st->kt[0][1] = gtime(); }
+    }
 }
-
-constexpr int XF_SMEM_BYTES = XF_STAGES * TILE_IN_BYTES + TILE_BLOCKS * 64 + 64;
 
 }  // namespace icb

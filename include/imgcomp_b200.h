@@ -45,7 +45,12 @@ typedef enum {
     ICB_FMT_RGB8 = 0,    /* what JPEGImageWriter hands libjpeg                       */
     ICB_FMT_BGR8 = 1,    /* BufferedImage.TYPE_3BYTE_BGR (ImageIO JPEG reader)       */
     ICB_FMT_RGBA8 = 2,   /* resize only                                              */
-    ICB_FMT_ABGR8 = 3    /* BufferedImage.TYPE_4BYTE_ABGR (ImageIO PNG reader); resize only */
+    ICB_FMT_ABGR8 = 3,   /* BufferedImage.TYPE_4BYTE_ABGR (ImageIO PNG reader); resize only */
+    ICB_FMT_GRAY8 = 4,   /* BufferedImage.TYPE_BYTE_GRAY; resize / subsample only (1-component JPG: stock writer) */
+    ICB_FMT_ARGB32 = 5,  /* BufferedImage.TYPE_INT_ARGB raster as bytes (little-endian ints: B G R A) --
+                            tools/ImageTools.java:12-15 falls back to it for type-0 / custom images; resize only */
+    ICB_FMT_XRGB32 = 6   /* BufferedImage.TYPE_INT_RGB raster as bytes (B G R x; x is interpolated like a
+                            colour byte, Java leaves it 0); resize only */
 } icb_fmt;
 
 typedef struct icb_handle icb_handle;
@@ -77,7 +82,9 @@ void icb_free_pinned(void *p);
  *   px/pitch/fmt : decoded pixels (RGB8 or BGR8), caller-owned
  *   init_q       : CompressionParams.quality()      target: targetMaxSizeBytes()
  *   has_cached / cached_q / cached_scale : cache.get(key) (LearnedParams.java:8)
- *   out/out_cap  : caller-owned output buffer; out_len <= target on ICB_OK */
+ *   out/out_cap  : caller-owned output buffer; out_len <= target on ICB_OK
+ * init_q > 1 (or NaN) and a cached quality outside [0, 1] return ICB_ERR_INVALID: the reference's
+ * ImageWriteParam.setCompressionQuality throws IllegalArgumentException there. */
 int icb_jpg_fit(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, int fmt,
                 float init_q, int64_t target,
                 int has_cached, float cached_q, double cached_scale,
@@ -144,9 +151,28 @@ int icb_submit_jpg_fit(icb_handle *h, const uint8_t *px, int w, int hgt, int pit
                        int has_cached, float cached_q, double cached_scale,
                        uint8_t *out, size_t out_cap, int64_t *ticket);
 int icb_wait(icb_handle *h, int64_t ticket, icb_result *res);
+/* Non-blocking: *done = 1 once the job has finished (a later icb_wait returns at once), 0 while its
+ * stream still has work.  A fit that needs another phase (cached miss, next scale of the 0.85 loop) is
+ * moved on from here, so a caller that only polls still makes progress.  The slot stays taken until
+ * icb_wait collects the result. */
+int icb_poll(icb_handle *h, int64_t ticket, int *done);
 /* A submitted job holds its work slot until icb_wait returns.  Every entry point takes a slot, so a
  * thread that has slots_per_gpu * n_devices tickets outstanding must wait on one of them before it
- * calls anything else (the call would block for a slot only that thread can free). */
+ * calls anything else (the call would block for a slot only that thread can free).
+ *
+ * Host buffers may be pageable (a Java heap array copied into a native segment, a numpy array): the
+ * submitting thread then copies the pixels into the slot's page-locked staging slice by slice while
+ * the copy engine moves the previous slice, and results are staged the same way on the way back.
+ * Buffers from icb_alloc_pinned skip that copy. */
+
+/* tools/ImageTools.java:7-26 / core/ImageCompressionPng.java:37-66 in the queue: host pixels in,
+ * resized pixels out (dst filled when icb_wait returns).  icb_submit_png_fit applies the dimension
+ * rule first: ICB_NO_FIT means nothing was queued and no ticket was issued. */
+int icb_submit_resize(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt,
+                      uint8_t *dst, int dw, int dh, int dpitch, int64_t *ticket);
+int icb_submit_png_fit(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt,
+                       int min_w, int min_h, uint8_t *dst, size_t dst_cap, int *dw, int *dh,
+                       int64_t *ticket);
 
 /* Device-resident inputs (bench `value`: pixels already in HBM when timing starts). */
 int icb_image_upload(icb_handle *h, int device_index, const uint8_t *px, int w, int hgt, int pitch,
@@ -159,6 +185,57 @@ int icb_submit_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q, 
 int icb_submit_resize_image(icb_handle *h, const icb_image *img, int dw, int dh,
                             uint8_t *dst, int dpitch, int64_t *ticket);
 
+/* The batch executor itself (CompressionBatch.java:64-108: newFixedThreadPool + one task per list line +
+ * awaitTermination) in native code: `threads` worker threads of the library pull items from ONE atomic
+ * cursor and each keeps `inflight` jobs in the per-GPU stream work queues of the handle (all its GPUs).
+ * Returns when every item has a result in item.res (status as from icb_wait; ICB_NO_FIT for a PNG item
+ * already inside the box).  The Java host calls this once per chunk of decoded lines, or keeps its own
+ * pool on icb_submit_* / icb_wait -- both drive the same queues. */
+typedef enum {
+    ICB_ITEM_JPG_FIT = 0,        /* host pixels -> icb_submit_jpg_fit      */
+    ICB_ITEM_JPG_FIT_IMAGE = 1,  /* resident image -> icb_submit_jpg_fit_image */
+    ICB_ITEM_PNG_FIT = 2,        /* host pixels -> icb_submit_png_fit (resized pixels out) */
+    ICB_ITEM_PNG_COMPRESS = 3,   /* host pixels -> icb_submit_png_compress (PNG file out)  */
+    ICB_ITEM_RESIZE_IMAGE = 4    /* resident image -> icb_submit_resize_image (dw, dh given; out may be NULL) */
+} icb_item_kind;
+
+typedef struct {
+    int kind;
+    const uint8_t *px;           /* host pixels (kinds 0, 2, 3) */
+    const icb_image *img;        /* resident image (kinds 1, 4) */
+    int w, h, pitch, fmt;
+    float init_q;                /* CompressionParams.quality()            */
+    int64_t target;              /* CompressionParams.targetMaxSizeBytes() */
+    int has_cached;
+    float cached_q;
+    double cached_scale;
+    int min_w, min_h;            /* CompressionParams.minWidth() / minHeight() (PNG) */
+    uint8_t *out;
+    size_t out_cap;
+    int dw, dh;                  /* out: PNG / resize dimensions (in for kind 4) */
+    icb_result res;              /* out */
+} icb_item;
+
+int icb_run_list(icb_handle *h, icb_item *items, size_t n, int threads, int inflight);
+
+/* SURVEY 8 f3 -- core/ImageCompressionPng.java:70 ImageIO.write(resized, "png", file) on the GPU: the
+ * PNG FILE (signature, IHDR, 8 KB IDAT chunks, IEND) of the given pixels; per-row filter choice by the
+ * minimum sum of absolute values, one dynamic-Huffman deflate block.  A zlib stream is not unique: the
+ * file decodes to exactly the input pixels, its size is close to (not equal to) the JDK writer's.
+ * icb_png_compress is the whole seam compressPngWithTargetSize (:37-75): dimension rule, resize with the
+ * pixels staying in HBM, PNG file out; ICB_NO_FIT = already inside min_w x min_h (returns false, :49-53).
+ * ICB_ERR_CAPACITY: out too small, *out_len (icb_result.out_len) = bytes needed. */
+int icb_png_encode(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, int fmt,
+                   uint8_t *out, size_t out_cap, size_t *out_len);
+int icb_submit_png_encode(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, int fmt,
+                          uint8_t *out, size_t out_cap, int64_t *ticket);
+int icb_png_compress(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt,
+                     int min_w, int min_h, uint8_t *out, size_t out_cap, size_t *out_len,
+                     int *dw, int *dh);
+int icb_submit_png_compress(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt,
+                            int min_w, int min_h, uint8_t *out, size_t out_cap, int *dw, int *dh,
+                            int64_t *ticket);
+
 /* Counters (CompressionBatch.java:56-62 are summed by the Java caller; these are
  * the device-side ones) and per-stage CUDA-event times of the last profiled job. */
 typedef struct {
@@ -170,6 +247,12 @@ typedef struct {
     float last_entropy_ms;
     float last_total_ms;
     int last_transform_launches, last_entropy_launches;
+    /* Kernel clocks, always on: for every finished fit, the GPU-global-timer span from the first CTA's start
+     * to the last CTA's end of [0] the transform, [1] each entropy pass, [2] the emit kernel, summed, and how
+     * many launches went into each sum.  Unlike the profile calls below these are taken INSIDE the running
+     * batch, with other jobs' kernels sharing the GPU: sum / launches is a kernel's in-step duration. */
+    uint64_t kernel_clock_ns[3];
+    uint64_t kernel_clock_launches[3];
 } icb_stats_t;
 int icb_stats(icb_handle *h, icb_stats_t *out);
 
@@ -183,9 +266,15 @@ int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q,
 /* Average duration of the transform kernel alone: the transforms of n resident images (all on one
  * GPU) are enqueued back to back on one slot's stream, reps rounds, between two CUDA events after
  * one untimed round (so neither the launch gap after an idle stream nor the event pair of a single
- * launch is in the figure).  *launches = kernels timed. */
-int icb_profile_transform_series(icb_handle *h, const icb_image *const *imgs, int n, int reps,
+ * launch is in the figure).  list_q > 0: the kernel also writes the survivor lists for that quality, as
+ * it does inside a fit (the production form); 0: coefficients only.  *launches = kernels timed. */
+int icb_profile_transform_series(icb_handle *h, const icb_image *const *imgs, int n, int reps, float list_q,
                                  float *ms_per_launch, int *launches);
+
+/* The resize kernel alone (with_png = 0) or resize + PNG encoder (1) on a resident image: reps runs back to
+ * back on one slot's stream between two CUDA events after two untimed ones; nothing leaves the GPU. */
+int icb_profile_resize_series(icb_handle *h, const icb_image *img, int dw, int dh, int reps, int with_png,
+                              float *ms_per_launch);
 
 /* Device-side stopwatch over all slot streams of one GPU (bench timing with CUDA
  * events although the work runs on library-owned streams): icb_mark(.., 0) before

@@ -38,7 +38,8 @@ extern "C" {
 #endif
 
 /* pixel formats (byte order in memory) */
-enum { ORC_FMT_RGB8 = 0, ORC_FMT_BGR8 = 1, ORC_FMT_RGBA8 = 2, ORC_FMT_ABGR8 = 3 };
+enum { ORC_FMT_RGB8 = 0, ORC_FMT_BGR8 = 1, ORC_FMT_RGBA8 = 2, ORC_FMT_ABGR8 = 3,
+       ORC_FMT_GRAY8 = 4, ORC_FMT_ARGB32 = 5, ORC_FMT_XRGB32 = 6 };    /* 4-6: resize only */
 
 /* "JDK profile" switches: every [JDK-mem] fact lives behind one of these. */
 typedef struct {

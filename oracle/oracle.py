@@ -14,7 +14,7 @@ import numpy as np
 _DIR = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_DIR, "liboracle.so")
 
-FMT_RGB8, FMT_BGR8, FMT_RGBA8, FMT_ABGR8 = 0, 1, 2, 3
+FMT_RGB8, FMT_BGR8, FMT_RGBA8, FMT_ABGR8, FMT_GRAY8, FMT_ARGB32, FMT_XRGB32 = 0, 1, 2, 3, 4, 5, 6
 
 
 class Profile(C.Structure):
@@ -31,11 +31,26 @@ class Geom(C.Structure):
                 ("nblocks", C.c_long)]
 
 
+def _has_avx2() -> bool:
+    try:
+        return " avx2 " in open("/proc/cpuinfo").read().replace("\n", " ")
+    except OSError:
+        return False
+
+
+def build_flags() -> str:
+    """How the oracle is compiled on this host (quoted in bench.py's cpu_baseline.sample)."""
+    return "gcc -O3 -march=x86-64-v3, scalar C" if _has_avx2() else "gcc -O3, scalar C"
+
+
 def build(force: bool = False) -> str:
-    srcs = [os.path.join(_DIR, f) for f in ("jpeg_oracle.c", "resize_oracle.c", "oracle.h", "jpeg_tables.h")]
+    srcs = [os.path.join(_DIR, f) for f in ("jpeg_oracle.c", "resize_oracle.c", "oracle.h", "jpeg_tables.h", "Makefile")]
     stale = force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs)
     if stale:
-        subprocess.run(["make", "-C", _DIR, "-s", "-B", "liboracle.so"], check=True)
+        cmd = ["make", "-C", _DIR, "-s", "-B", "liboracle.so"]
+        if not _has_avx2():
+            cmd.append("ARCH=")                    # a host without AVX2: plain x86-64 code
+        subprocess.run(cmd, check=True)
     return _SO
 
 
@@ -83,7 +98,9 @@ def _u8(a: np.ndarray):
 
 def _img(img: np.ndarray):
     img = np.ascontiguousarray(img, dtype=np.uint8)
-    assert img.ndim == 3 and img.shape[2] in (3, 4)
+    if img.ndim == 2:
+        img = img[:, :, None]
+    assert img.ndim == 3 and img.shape[2] in (1, 3, 4)
     h, w, c = img.shape
     return img, w, h, w * c
 

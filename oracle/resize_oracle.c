@@ -101,6 +101,9 @@ static void fmt_layout(int fmt, int *bpp, int *alpha_off)
     switch (fmt) {
     case ORC_FMT_RGBA8: *bpp = 4; *alpha_off = 3; break;
     case ORC_FMT_ABGR8: *bpp = 4; *alpha_off = 0; break;
+    case ORC_FMT_ARGB32: *bpp = 4; *alpha_off = 3; break;      /* TYPE_INT_ARGB as little-endian bytes B G R A */
+    case ORC_FMT_XRGB32: *bpp = 4; *alpha_off = -1; break;     /* TYPE_INT_RGB: no alpha, four plain bytes */
+    case ORC_FMT_GRAY8: *bpp = 1; *alpha_off = -1; break;      /* TYPE_BYTE_GRAY */
     default:            *bpp = 3; *alpha_off = -1; break;
     }
 }

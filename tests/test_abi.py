@@ -51,7 +51,7 @@ def test_result_and_stats_struct_layout():
     # icb_result / icb_stats_t as the header lays them out on LP64
     assert C.sizeof(api._Result) == 48
     assert api._Result.out_len.offset == 8 and api._Result.scale.offset == 24 and api._Result.device.offset == 40
-    assert C.sizeof(api._Stats) == 64
+    assert C.sizeof(api._Stats) == 112 and api._Stats.kernel_clock_ns.offset == 64
     assert api._Stats.last_transform_ms.offset == 40
 
 

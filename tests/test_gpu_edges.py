@@ -107,8 +107,21 @@ def test_capacity_and_argument_errors(engine):
     assert (engine._L.icb_last_error(h) or b"") != b""
 
 
-def test_quality_clamps_like_the_jdk(engine, oracle):
-    """JPEG.convertToLinearQuality clamps q to (0, 1]; the seam accepts what Java accepts."""
+def test_quality_range_like_the_jdk(engine, oracle):
+    """ImageWriteParam.setCompressionQuality accepts [0, 1] (JPEG.convertToLinearQuality then clamps the
+    low end) and throws IllegalArgumentException outside it: the seam accepts exactly what Java accepts."""
     img = synth.natural_image(91, 96, 64)
-    for q in (0.0, 0.005, 1.0, 1.5):
+    for q in (0.0, 0.005, 1.0):
         assert engine.compress_jpg_to_stream(img, q) == oracle.encode(img, q)
+    for q in (1.5, -0.1, float("nan")):
+        with pytest.raises(api.IcbError) as e:
+            engine.compress_jpg_to_stream(img, q)
+        assert e.value.code == api.ICB_ERR_INVALID
+    for kw in (dict(init_q=1.5), dict(init_q=float("nan")), dict(init_q=0.25, cached=pkg.LearnedParams(1.2, 1.0)),
+               dict(init_q=0.25, cached=pkg.LearnedParams(float("nan"), 1.0))):
+        with pytest.raises(api.IcbError) as e:
+            engine.jpg_fit(img, kw["init_q"], 5000, kw.get("cached"))
+        assert e.value.code == api.ICB_ERR_INVALID
+    # a non-positive initial quality is legal Java: every midpoint is below 0.01, nothing is encoded, no scale fits
+    assert engine.jpg_fit(img, 0.0, 5000).status == api.ICB_NO_FIT
+    assert engine.jpg_fit(img, -1.0, 5000).status == api.ICB_NO_FIT

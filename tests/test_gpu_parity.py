@@ -96,6 +96,6 @@ def test_resize_exact(engine, oracle, src, dst, fmt_c):
     got = engine.resize_to(img, dst[0], dst[1], fmt)
     ref = oracle.resize(img, dst[0], dst[1], fmt=ofmt)
     assert np.array_equal(got, ref)
-    if fmt_c == 3:
+    if fmt_c == 3:      # the stated tolerance: +-1 LSB against the exact (float64) bilinear sample
         f64 = oracle.resize(img, dst[0], dst[1], fmt=ofmt, f64=True)
-        assert np.abs(got.astype(int) - f64.astype(int)).max() <= 2
+        assert np.abs(got.astype(int) - f64.astype(int)).max() <= 1
