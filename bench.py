@@ -48,12 +48,19 @@ POOL = 8            # distinct images per GPU: 8 x 36 MB = 288 MB > 126 MB L2
 def make_pool(w, h, n, seed0):
     """n distinct natural-statistics images (half generated, half mirrored copies)."""
     from image_compression_b200 import synth
+    cache = os.environ.get("ICB_POOL_CACHE")            # A/B sessions: synthesise once per box, not once per run
+    path = cache and os.path.join(cache, f"pool_{w}x{h}_{n}_{seed0}.npy")
+    if path and os.path.exists(path):
+        return list(np.load(path))
     base = [synth.natural_image(seed0 + i, w, h) for i in range((n + 1) // 2)]
     pool = []
     for im in base:
         pool.append(im)
         if len(pool) < n:
             pool.append(np.ascontiguousarray(im[:, ::-1]))
+    if path:
+        os.makedirs(cache, exist_ok=True)
+        np.save(path, np.stack(pool[:n]))
     return pool[:n]
 
 

@@ -91,6 +91,7 @@ struct Slot {
     unsigned long long *h_len = nullptr;                        // pinned: length of the PNG file of the job in flight
     Geom geom{};
     bool busy = false;
+    bool lone = false;                      // the job in flight found no other slot of its GPU busy (enqueue_transform)
     uint64_t gen = 0;
     Job job;
 };
@@ -114,7 +115,7 @@ struct icb_handle {
     PFN_encodeTiled encode_tiled = nullptr;
     std::string last_error;
     std::atomic<uint64_t> images_done{0}, kernels{0}, passes{0}, h2d{0}, d2h{0};
-    // kernel clocks summed over finished jobs (FitState.kt): [0] transform, [1] entropy passes, [2] emit
+    // kernel clocks summed over finished jobs (FitState.kt): [0] transform, [1] entropy passes, [2] unused
     std::atomic<uint64_t> kclk_ns[3], kclk_n[3];
     float last_xf_ms = 0, last_ent_ms = 0, last_total_ms = 0;
     int last_xf_launches = 0, last_ent_launches = 0;
@@ -148,10 +149,14 @@ int fail(icb_handle *h, int code, const char *what, cudaError_t e = cudaSuccess)
 
 // Launch on `st`; with pdl the kernel may start before its predecessor on the stream has finished
 // (programmatic stream serialization) -- it calls griddepcontrol.wait before touching its results.
-bool pdl_enabled()
+// ICB_PDL=1 / 0 forces it on / off; unset: on for a job that has its GPU to itself (latency: each kernel's
+// set-up hides behind its predecessor's tail), off when other slots of the GPU are working -- early-resident
+// CTAs that sit in griddepcontrol.wait hold registers and shared memory other jobs' kernels could use
+// (measured r02, six slots busy: 10.3 k -> 11.0 k images/s with it off)
+int pdl_policy()
 {
-    static const bool on = [] { const char *e = getenv("ICB_PDL"); return !(e && e[0] == '0'); }();
-    return on;
+    static const int v = [] { const char *e = getenv("ICB_PDL"); return !e ? -1 : (e[0] == '0' ? 0 : 1); }();
+    return v;
 }
 
 template <typename... KArgs, typename... Args>
@@ -166,7 +171,7 @@ cudaError_t launch(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, c
     at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     at[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = at;
-    cfg.numAttrs = (pdl && pdl_enabled()) ? 1 : 0;
+    cfg.numAttrs = pdl ? 1 : 0;
     return cudaLaunchKernelEx(&cfg, kern, std::forward<Args>(args)...);
 }
 
@@ -242,8 +247,16 @@ int setup_device(icb_handle *h, DeviceCtx &d)
     unsigned char hdr[HEADER_BYTES + 16];
     build_header_template(hdr, dc_bits, ac_bits, ac_vals);
     CK(cudaMemcpyToSymbol(c_hdr, hdr, HEADER_BYTES));
-    CK(cudaFuncSetAttribute(k_transform<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
-    CK(cudaFuncSetAttribute(k_transform<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
+    const int rs_max = resize_smem_bytes(RS_MAX_SEG, RS_MAX_TW, 3);
+    CK(cudaFuncSetAttribute(k_resize<4, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, rs_max));
+    CK(cudaFuncSetAttribute(k_resize<4, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, rs_max));
+    CK(cudaFuncSetAttribute(k_resize<4, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, rs_max));
+    CK(cudaFuncSetAttribute(k_resize<3, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, rs_max));
+    CK(cudaFuncSetAttribute(k_resize<1, -1>, cudaFuncAttributeMaxDynamicSharedMemorySize, rs_max));
+    CK(cudaFuncSetAttribute(k_transform<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_transform<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_transform<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
+    CK(cudaFuncSetAttribute(k_transform<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
     return ICB_OK;
 }
 
@@ -369,6 +382,7 @@ int enqueue_transform(icb_handle *h, Slot *s, const unsigned char *d_px, int w, 
             for (const Slot &o : h->slots) busy += (o.busy && o.devi == s->devi) ? 1 : 0;
         }
         if (busy <= 1) tile_pick = 128;
+        s->lone = busy <= 1;
     }
     const Geom g = make_geom(w, hgt, pitch, fmt == ICB_FMT_BGR8, tile_pick);
     s->geom = g;
@@ -397,10 +411,14 @@ int enqueue_transform(icb_handle *h, Slot *s, const unsigned char *d_px, int w, 
     const int ntiles = g.nunits;
     static const int xf_cps = [] { const char *e = getenv("ICB_XF_CPS"); return e ? atoi(e) : XF_CTAS; }();   // tuning knob
     const int grid = std::min(ntiles, h->devs[s->devi].sms * std::max(1, std::min(XF_CTAS, xf_cps)));
-    if (g.bgr)
-        k_transform<true><<<grid, XF_THREADS, XF_SMEM_BYTES, s->stream>>>(tmap, g, s->d_coef, tiles_per_row, ntiles, xl);
-    else
-        k_transform<false><<<grid, XF_THREADS, XF_SMEM_BYTES, s->stream>>>(tmap, g, s->d_coef, tiles_per_row, ntiles, xl);
+    xl.st = s->d_state;                     // (kernel clock, with or without lists)
+    if (plan) {
+        if (g.bgr) k_transform<true, true><<<grid, XF_THREADS, XF_SMEM_BYTES, s->stream>>>(tmap, g, s->d_coef, tiles_per_row, ntiles, xl);
+        else k_transform<false, true><<<grid, XF_THREADS, XF_SMEM_BYTES, s->stream>>>(tmap, g, s->d_coef, tiles_per_row, ntiles, xl);
+    } else {
+        if (g.bgr) k_transform<true, false><<<grid, XF_THREADS, XF_SMEM_BYTES, s->stream>>>(tmap, g, s->d_coef, tiles_per_row, ntiles, xl);
+        else k_transform<false, false><<<grid, XF_THREADS, XF_SMEM_BYTES, s->stream>>>(tmap, g, s->d_coef, tiles_per_row, ntiles, xl);
+    }
     CK(cudaGetLastError());
     h->kernels++;
     return ICB_OK;
@@ -494,14 +512,15 @@ int enqueue_passes(icb_handle *h, Slot *s, const FitPlan &pl, bool lists_ready, 
     const int pwave = h->devs[s->devi].sms * PREP_CTAS_PER_SM;
     const int prounds = (pneed + pwave - 1) / pwave;             // units a warp takes
     const dim3 prep_grid((pneed + prounds - 1) / prounds);
+    const bool pdl0 = pdl_policy() < 0 ? s->lone : pdl_policy() == 1;
     if (lists_ready)
         CK(launch(k_job_begin, dim3((g.nunits + BEGIN_THREADS - 1) / BEGIN_THREADS), dim3(BEGIN_THREADS), 0, s->stream,
-                  true, ep, ba));
+                  pdl0, ep, ba));
     else
-        CK(launch(k_entropy_prepare<false>, prep_grid, dim3(PREP_THREADS), 0, s->stream, true, ep, ba));
+        CK(launch(k_entropy_prepare<false>, prep_grid, dim3(PREP_THREADS), 0, s->stream, pdl0, ep, ba));
     h->kernels += 1;
     const int pgrid = pass_grid(g.ntiles, h->devs[s->devi].sms);
-    const bool pdl = pass_ev == nullptr;
+    const bool pdl = pass_ev == nullptr && (pdl_policy() < 0 ? s->lone : pdl_policy() == 1);
     for (int i = 0; i < pl.npasses; i++) {
         if (pass_ev) cudaEventRecord(pass_ev[2 * i], s->stream);
         CK(launch(k_entropy_pass, dim3(pgrid), dim3(ENT_THREADS), 0, s->stream, pdl, ep));
@@ -518,8 +537,7 @@ int enqueue_passes(icb_handle *h, Slot *s, const FitPlan &pl, bool lists_ready, 
         }
     }
     if (emit) {
-        CK(launch(k_entropy_emit, dim3(nctas), dim3(ENT_THREADS), 0, s->stream, pass_ev == nullptr, ep, s->d_out,
-                  dev_cap, g.w, g.h));
+        CK(launch(k_entropy_emit, dim3(nctas), dim3(ENT_THREADS), 0, s->stream, pdl, ep, s->d_out, dev_cap, g.w, g.h));
         h->kernels += 1;
     }
     CK(cudaGetLastError());
@@ -575,8 +593,12 @@ int enqueue_resize(icb_handle *h, Slot *s, const unsigned char *d_src, int w, in
     rp.tw_log2 = tl;
     rp.seg_bytes = (int)seg;
     const int tw = 1 << tl;
-    const dim3 grid((dw + tw - 1) / tw, (dh + RS_ROWS - 1) / RS_ROWS);
+    rp.tiles_x = (dw + tw - 1) / tw;
+    rp.ntiles = rp.tiles_x * ((dh + RS_ROWS - 1) / RS_ROWS);
     const size_t smem = (size_t)resize_smem_bytes(rp.seg_bytes, tw, bpp);
+    // persistent CTAs: as many as fit an SM by shared memory (at most 6), one wave
+    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(6, ((size_t)220 << 10) / smem));
+    const dim3 grid((unsigned)std::min(rp.ntiles, h->devs[s->devi].sms * per_sm));
     switch (fmt) {
     case ICB_FMT_RGBA8: case ICB_FMT_ARGB32: k_resize<4, 3><<<grid, RS_THREADS, smem, s->stream>>>(rp); break;
     case ICB_FMT_ABGR8: k_resize<4, 0><<<grid, RS_THREADS, smem, s->stream>>>(rp); break;
@@ -674,6 +696,12 @@ void collect_output(Slot *s)                                // after the stream 
 // ======================================================================
 namespace {
 
+bool fetch_by_kernel()
+{
+    static const bool v = [] { const char *e = getenv("ICB_FETCH_KERNEL"); return e && e[0] == '1'; }();
+    return v;
+}
+
 long long worst_stream_bytes(const Geom &g)
 {
     return (long long)HEADER_BYTES + 2 + (long long)g.nblocks * 416;     // every byte stuffed
@@ -726,19 +754,30 @@ int fit_enqueue_phase(icb_handle *h, Slot *s)
     // the stream goes back by a kernel that knows best_size (exactly that many bytes, nothing on a phase
     // that failed): into the caller's buffer when it is page-locked and 16-byte aligned, else into the slot's
     // page-locked staging (copied out when the job is collected)
+    // The stream goes back on the copy engine, speculatively: min(out_cap, cap) bytes are queued behind the emit
+    // kernel now (the host learns best_size only after the phase drained; a second, exactly sized copy would cost
+    // a host round trip per image).  A phase that fails copies dead bytes; the caller's buffer past out_len is
+    // unspecified.  ICB_FETCH_KERNEL=1 selects the alternative measured in r02 -- a kernel that knows best_size
+    // and writes exactly that many bytes into the page-locked destination: 12 % slower with six slots busy
+    // (zero-copy stores over PCIe occupy SM store queues that the entropy passes of other jobs want).
+    const bool fetch_kernel = fetch_by_kernel();
     if (j.out && j.out_cap) {
         unsigned char *dst = j.out;
-        long long dcap = (long long)j.out_cap;
-        if (!j.out_pinned || ((uintptr_t)j.out & 15)) {
+        long long dcap = std::min<long long>((long long)j.out_cap, cap);
+        if (!j.out_pinned || (fetch_kernel && ((uintptr_t)j.out & 15))) {
             rc = ensure_pinned(h, s->h_out, s->h_out_cap, round_up((size_t)cap, 16) + 32);
             if (rc) return rc;
             dst = s->h_out;
-            dcap = std::min<long long>((long long)j.out_cap, cap);
             j.stage_stream = true;
         }
-        CK(launch(k_fetch_stream, dim3(8), dim3(FETCH_THREADS), 0, s->stream, true, (const FitState *)s->d_state,
-                  (const unsigned char *)s->d_out, cap, dst, dcap));
-        h->kernels += 1;
+        if (fetch_kernel) {
+            CK(launch(k_fetch_stream, dim3(8), dim3(FETCH_THREADS), 0, s->stream, false, (const FitState *)s->d_state,
+                      (const unsigned char *)s->d_out, cap, dst, dcap));
+            h->kernels += 1;
+        } else if (dcap > 0) {
+            CK(cudaMemcpyAsync(dst, s->d_out, (size_t)dcap, cudaMemcpyDeviceToHost, s->stream));
+            h->d2h += (uint64_t)dcap;
+        }
     }
     CK(cudaMemcpyAsync(s->h_state, s->d_state, sizeof(FitState), cudaMemcpyDeviceToHost, s->stream));
     h->d2h += sizeof(FitState);
@@ -758,7 +797,6 @@ int fit_advance(icb_handle *h, Slot *s)
         };
         if (j.xf_this_phase) add(0, st.kt[0]);
         for (int i = 0; i < st.passes && i < 8; i++) add(1, st.kt[2 + i]);
-        if (st.best_size > 0) add(2, st.kt[10]);
     }
     j.res.n_passes = j.passes;
     j.res.device = h->devs[s->devi].dev;
@@ -795,7 +833,7 @@ int fit_advance(icb_handle *h, Slot *s)
         j.res.out_len = (size_t)st.best_size;
         j.res.status = (size_t)st.best_size <= j.out_cap ? ICB_OK : ICB_ERR_CAPACITY;
         if (j.res.status == ICB_OK && j.out && st.best_size > 0) {
-            h->d2h += (uint64_t)st.best_size;            // k_fetch_stream moved exactly these bytes
+            if (fetch_by_kernel()) h->d2h += (uint64_t)st.best_size;     // k_fetch_stream moved exactly these bytes
             if (j.stage_stream) memcpy(j.out, s->h_out, (size_t)st.best_size);
         }
         return 0;

@@ -159,12 +159,13 @@ struct FitState {
     // pass scratch
     unsigned int done_a;            // finished CTAs of k_entropy_pass
     int pad1, pad2, pad3;
-    // kernel clock (always on): GPU global timer when block 0 of a kernel of this job started its work and
-    // when the kernel's LAST CTA finished -- the duration a kernel really has inside a busy step, with
-    // other jobs' kernels sharing the GPU (bench.py's in-step roofline).  [0] transform, [1] job start /
-    // list kernel, [2..9] entropy passes by iteration, [10] emit
+    // kernel clock (always on, a handful of timer reads per job): GPU global timer when block 0 of a kernel of
+    // this job started its work and when the kernel finished -- the duration a kernel really has inside a busy
+    // step, with other jobs' kernels sharing the GPU (bench.py's in-step roofline).  [0] transform (end = the
+    // job-start kernel's griddepcontrol.wait returning), [1] job start / list kernel (start only), [2..9] entropy
+    // passes by iteration (end = the last CTA's bisection step), [10] emit (start only)
     unsigned long long kt[11][2];
-    unsigned int xf_done, emit_done; // finished CTAs of k_transform / k_entropy_emit (the last one stamps kt[.][1])
+    unsigned int pad_kt[2];
     unsigned long long dbg_k[4];    // ICB_TIMING: globaltimer at survivor-kernel start / emit start / emit end (block 0)
     unsigned long long dbg_w[24];   // ICB_TIMING: clock64 timeline of one warp of the last pass
     unsigned long long dbg_t[8][4]; // per pass: globaltimer at kernel start / tail start / step start / tail end

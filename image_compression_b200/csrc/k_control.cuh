@@ -194,6 +194,7 @@ __global__ void __launch_bounds__(BEGIN_THREADS) k_job_begin(const EntParams p, 
     pdl_launch_dependents();
     if (blockIdx.x == 0 && threadIdx.x < 32) begin_job(p.st, ba);       // touches nothing the transform writes
     pdl_wait();                                                         // lists and unit_info are complete
+    if (blockIdx.x == 0 && threadIdx.x == 0) p.st->kt[0][1] = gtime(); // = the moment the transform grid finished
     const int u = blockIdx.x * BEGIN_THREADS + threadIdx.x;
     if (u < 1 || u >= p.nunits) return;
     const uint4 prev = __ldcg(reinterpret_cast<const uint4 *>(p.unit_info) + (u - 1));   // .y = Y11 | Cb << 16, .z = Cr

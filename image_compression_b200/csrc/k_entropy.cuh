@@ -182,7 +182,10 @@ __global__ void __launch_bounds__(PREP_THREADS, PREP_CTAS_PER_SM) k_entropy_prep
     if (!REBUILD && blockIdx.x == 0 && tid == 0) { p.st->kt[1][0] = gtime(); p.st->kt[1][1] = 0; }
     if (!REBUILD && blockIdx.x == 0 && warp == PREP_WARPS - 1) begin_job(p.st, ba);
     __syncthreads();
-    if (!REBUILD) pdl_wait();       // the coefficients are complete and visible from here on
+    if (!REBUILD) {
+        pdl_wait();                 // the coefficients are complete and visible from here on
+        if (blockIdx.x == 0 && tid == 0) p.st->kt[0][1] = gtime();      // = the moment the transform grid finished
+    }
     unsigned char *ts = s_half[warp];
     const unsigned char *rp = ts + lane * PREP_ROW;
     for (int unit = blockIdx.x * PREP_WARPS + warp; unit < p.nunits; unit += gridDim.x * PREP_WARPS) {
@@ -347,7 +350,9 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
 #endif
     const PassBufs pb = pick_buf(p, c2.x);
     const int kt_slot = 2 + ((c1.x - 1) & 7);       // kernel clock of this pass (FitState.kt)
+#ifndef ICB_NO_KCLK
     if (blockIdx.x == 0 && tid == 0) st->kt[kt_slot][0] = gtime();
+#endif
 #ifdef ICB_TIMING
     const int dbg_pass = (c1.x - 1) & 7;
     if (blockIdx.x == 0 && threadIdx.x == 0) st->dbg_t[dbg_pass][0] = gtime();
@@ -377,14 +382,19 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
       // measured slower, alone and with several fits sharing the GPU: the loop is issue bound.)
       // Plain (.cg) loads, not the non-coherent path: the lists are rewritten by kernels of this same
       // stream chain that may still be running when this grid becomes resident.
+#ifdef ICB_PASS_LDG          // A/B only: the non-coherent path the round-1 kernel used
+#define ICB_ENT_LD __ldg
+#else
+#define ICB_ENT_LD __ldcg
+#endif
       const int u0 = tile * p.unit_group;
       uint32_t rounds0 = 0, rounds = 0;
       uint2 e_first = make_uint2(0u, 0u);
       if (tile < p.ntiles) {
-          rounds0 = (__ldcg(p.ent_cnt + u0) + 63u) >> 6;
+          rounds0 = (ICB_ENT_LD(p.ent_cnt + u0) + 63u) >> 6;
           rounds = rounds0;
-          if (p.unit_group > 1 && u0 + 1 < p.nunits) rounds += (__ldcg(p.ent_cnt + u0 + 1) + 63u) >> 6;
-          e_first = __ldcg(reinterpret_cast<const uint2 *>(p.ent + (size_t)u0 * UNIT_CAP) + lane);
+          if (p.unit_group > 1 && u0 + 1 < p.nunits) rounds += (ICB_ENT_LD(p.ent_cnt + u0 + 1) + 63u) >> 6;
+          e_first = ICB_ENT_LD(reinterpret_cast<const uint2 *>(p.ent + (size_t)u0 * UNIT_CAP) + lane);
       }
       ICB_STAMP();                  // 5 / 10: tile start
       if (tile < p.ntiles) {
@@ -398,7 +408,13 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
 
         // 0xFF bytes that START in window words [0, nw) -- word w+1 must be final already --
         // for the 8 local start bits s; limit = tile bits that exist (a byte must end <= limit)
+        // ICB_PASS_BITS_ONLY (A/B build): the pass stops at the code lengths -- no bit window, no
+        // flush, no 0xFF count.  Sizes are then wrong; the build exists to time what a bit-length-only sizing
+        // pass (the north-star's "bit-length pass with a prefix scan") would cost next to the exact one.
         auto count_ff = [&](uint32_t nw, uint32_t limit) {
+#ifdef ICB_PASS_BITS_ONLY
+            return;
+#endif
             for (uint32_t w = lane; w < nw; w += 32) {
                 uint32_t m = ff_starts(s_win[wbase + w], s_win[wbase + w + 1]);
                 const uint32_t bit0 = (flushed + w) << 5;
@@ -417,6 +433,10 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         // copy finished words of the window to scratch and slide the window; one finished word
         // stays behind so that bytes straddling it can still be counted
         auto flush_some = [&]() {
+#ifdef ICB_PASS_BITS_ONLY
+            flushed = (running >> 5) > 2 ? (running >> 5) - 2 : 0;
+            return;
+#endif
             __syncwarp();
             const uint32_t have = (running >> 5) - flushed;         // finished words in the window
             if (have >= 2) {
@@ -440,9 +460,15 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         // reduction -- cheaper where the word is rarely zero: the first two words of a 64-bit field
         // (measured: pass 25.6 -> 24.8 us alone; -DICB_PASS_OR_BRANCH restores the branches)
         auto or_nz = [&](uint32_t word_idx, uint32_t w) {
+#ifdef ICB_PASS_BITS_ONLY
+            return;
+#endif
             if (w) atomicOr(&s_win[wbase + word_idx], w);
         };
         auto or_any = [&](uint32_t word_idx, uint32_t w) {
+#ifdef ICB_PASS_BITS_ONLY
+            return;
+#endif
 #ifndef ICB_PASS_OR_BRANCH
             asm volatile("red.shared.or.b32 [%0], %1;" :: "r"(win_base + 4u * word_idx), "r"(w) : "memory");
 #else
@@ -551,7 +577,7 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         for (uint32_t r = 0; r < rounds; r++) {
             const uint2 e = e_next;
             const uint32_t rn = r + 1;                                  // next round's entries fly while this one is coded
-            if (rn < rounds) e_next = __ldcg(rn < rounds0 ? ent2 + 32u * rn : ent2 + UNIT_CAP / 2 + 32u * (rn - rounds0));
+            if (rn < rounds) e_next = ICB_ENT_LD(rn < rounds0 ? ent2 + 32u * rn : ent2 + UNIT_CAP / 2 + 32u * (rn - rounds0));
             code_round(e);                                              // (tails are zero-padded by the list writers)
         }
         ICB_STAMP();                // 7 / 12: rounds done
@@ -723,7 +749,9 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
     if (tid == 0) st->dbg_t[dbg_pass][2] = gtime();
 #endif
     if (warp == 0) device_step(st, reinterpret_cast<const FitState *>(s_ctl), 0, s_total[0], s_total[1]);      // :176-189 on the exact size, then the next table slot
+#ifndef ICB_NO_KCLK
     if (tid == 0) st->kt[kt_slot][1] = gtime();
+#endif
 #ifdef ICB_TIMING
     if (tid == 0) st->dbg_t[dbg_pass][3] = gtime();
 #endif
@@ -887,11 +915,6 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_emit(const EntParams p,
     }
     const int tile = blockIdx.x * ENT_WARPS + warp;
     if (tile < p.ntiles) emit_tile(p, pb, st, out, cap, tile, lane);
-    __syncthreads();
-    if (tid == 0) {                                 // kernel clock: the last CTA to finish stamps the end
-        FitState *w = const_cast<FitState *>(st);
-        if (atomicAdd(&w->emit_done, 1u) == gridDim.x - 1u) { w->emit_done = 0; w->kt[10][1] = gtime(); }
-    }
 }
 
 // After the emit kernel: the chosen stream goes to the caller -- exactly best_size bytes of it, and only if the

@@ -32,16 +32,17 @@ struct ResizeParams {
     long long dxl, dyl, xbase, ybase;      // 32.32 fixed point
     int tw_log2;                           // destination pixels per CTA row = 1 << tw_log2 (4 .. 128)
     int seg_bytes;                         // shared-memory bytes per staged source row (multiple of 16)
+    int tiles_x, ntiles;                   // destination tiles per row of tiles, and in all
 };
 
 constexpr int RS_ROWS = 8;                 // destination rows per CTA
 constexpr int RS_THREADS = 256;
-constexpr int RS_MAX_SEG = 2560;           // staged bytes per source row: 16 rows x 2560 B = 40 KB
+constexpr int RS_MAX_SEG = 2560;           // staged bytes per source row: 2 buffers x 16 rows x 2560 B = 80 KB at most
 constexpr int RS_MAX_TW = 128;
 
 __host__ __device__ inline int resize_smem_bytes(int seg_bytes, int tw, int bpp)
 {
-    return 2 * RS_ROWS * seg_bytes + (bpp == 4 ? 0 : RS_ROWS * ((tw * bpp + 15) & ~15)) + 1024;
+    return 2 * (2 * RS_ROWS * seg_bytes) + (bpp == 4 ? 0 : RS_ROWS * ((tw * bpp + 15) & ~15)) + 1024;     // two staging buffers
 }
 
 __device__ __forceinline__ int mul8(int a, int b)       // AlphaMath.c mul8table[a][b]
@@ -92,51 +93,84 @@ __device__ __forceinline__ void rs_premul2(uint32_t p, uint32_t &e, uint32_t &o)
     e = te; o = to;
 }
 
+__device__ __forceinline__ void rs_cp_async16(void *smem_dst, const void *gmem_src)
+{
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((uint32_t)__cvta_generic_to_shared(smem_dst)), "l"(gmem_src)
+                 : "memory");
+}
+
+// geometry of destination tile t: its first pixel, its size, and the staged byte range of the source rows
+struct RsTile {
+    int dx_first, dy_first, ncols, nrows, byte0, nvec;
+};
+
+template <int BPP>
+__device__ __forceinline__ RsTile rs_tile(const ResizeParams &p, int t)
+{
+    const long long half = 1ll << 31;
+    const int tw = 1 << p.tw_log2;
+    RsTile g;
+    const int ty = t / p.tiles_x, tx = t - ty * p.tiles_x;
+    g.dx_first = tx * tw; g.dy_first = ty * RS_ROWS;
+    g.ncols = min(tw, p.dw - g.dx_first); g.nrows = min(RS_ROWS, p.dh - g.dy_first);
+    int xa, xb, f_unused;
+    rs_taps(p.xbase + (long long)g.dx_first * p.dxl - half, p.w, xa, xb, f_unused);
+    const int xs0 = xa;
+    rs_taps(p.xbase + (long long)(g.dx_first + g.ncols - 1) * p.dxl - half, p.w, xa, xb, f_unused);
+    const int xs1 = max(xa, xb);
+    g.byte0 = (xs0 * BPP) & ~15;
+    g.nvec = min(p.seg_bytes, (((xs1 + 1) * BPP + 15) & ~15) - g.byte0) >> 4;     // (the host sized seg_bytes for it)
+    return g;
+}
+
+// Persistent CTAs, two staging buffers: while a tile is interpolated out of one buffer, the source rows of the
+// CTA's next tile stream into the other (cp.async, 16 bytes per request, no registers in between).
 template <int BPP, int AOFF>
 __global__ void __launch_bounds__(RS_THREADS) k_resize(const ResizeParams p)
 {
     extern __shared__ __align__(16) unsigned char rs_smem[];
     const int tid = threadIdx.x;
     const int tw = 1 << p.tw_log2;
-    unsigned char *s_in = rs_smem;                                          // [2 * RS_ROWS][seg_bytes]
-    unsigned char *s_out = rs_smem + 2 * RS_ROWS * p.seg_bytes;             // [RS_ROWS][out_stride]   (BPP != 4)
+    const int stage_bytes = 2 * RS_ROWS * p.seg_bytes;                      // one buffer: [2 * RS_ROWS][seg_bytes]
+    unsigned char *s_out = rs_smem + 2 * stage_bytes;                       // [RS_ROWS][out_stride]   (BPP != 4)
     const int out_stride = BPP == 4 ? 0 : (tw * BPP + 15) & ~15;
     unsigned *s_inc = reinterpret_cast<unsigned *>(s_out + RS_ROWS * out_stride);   // div8 increments
     const long long half = 1ll << 31;
-    const int dx_first = blockIdx.x * tw, dy_first = blockIdx.y * RS_ROWS;
-    const int ncols = min(tw, p.dw - dx_first), nrows = min(RS_ROWS, p.dh - dy_first);
 
     if (AOFF >= 0) s_inc[tid] = tid ? div8_inc(tid) : 0u;
 
-    // ---- stage the source: rows y0 / y1 of every destination row, bytes [byte0, byte1) of each
-    int xa, xb, f_unused;
-    rs_taps(p.xbase + (long long)dx_first * p.dxl - half, p.w, xa, xb, f_unused);
-    const int xs0 = xa;
-    rs_taps(p.xbase + (long long)(dx_first + ncols - 1) * p.dxl - half, p.w, xa, xb, f_unused);
-    const int xs1 = max(xa, xb);
-    const int byte0 = (xs0 * BPP) & ~15;
-    const int nvec = min(p.seg_bytes, (((xs1 + 1) * BPP + 15) & ~15) - byte0) >> 4;     // (the host sized seg_bytes for it)
-    {
-        // warp w stages the two source rows of destination row w: lanes walk the row's vectors, four loads in flight
+    // rows y0 / y1 of every destination row of tile t, bytes [byte0, byte0 + 16 nvec): warp w stages the two
+    // source rows of destination row w, lanes walk the row's vectors
+    auto stage = [&](int t, int buf) {
+        const RsTile g = rs_tile<BPP>(p, t);
         const int lane = tid & 31, rr = tid >> 5;
-        if (rr < nrows) {
+        if (rr < g.nrows) {
             int y0, y1, yf;
-            rs_taps(p.ybase + (long long)(dy_first + rr) * p.dyl - half, p.h, y0, y1, yf);
-            const uint4 *g0 = reinterpret_cast<const uint4 *>(p.src + (size_t)y0 * p.pitch + byte0);
-            const uint4 *g1 = reinterpret_cast<const uint4 *>(p.src + (size_t)y1 * p.pitch + byte0);
-            uint4 *s0 = reinterpret_cast<uint4 *>(s_in + (2 * rr) * p.seg_bytes);
-            uint4 *s1 = reinterpret_cast<uint4 *>(s_in + (2 * rr + 1) * p.seg_bytes);
-            for (int v0 = lane; v0 < nvec; v0 += 64) {
-                const int v1 = v0 + 32;
-                const uint4 a0 = __ldg(g0 + v0), b0 = __ldg(g1 + v0);
-                uint4 a1 = make_uint4(0, 0, 0, 0), b1 = a1;
-                if (v1 < nvec) { a1 = __ldg(g0 + v1); b1 = __ldg(g1 + v1); }
-                s0[v0] = a0; s1[v0] = b0;
-                if (v1 < nvec) { s0[v1] = a1; s1[v1] = b1; }
+            rs_taps(p.ybase + (long long)(g.dy_first + rr) * p.dyl - half, p.h, y0, y1, yf);
+            const unsigned char *g0 = p.src + (size_t)y0 * p.pitch + g.byte0, *g1 = p.src + (size_t)y1 * p.pitch + g.byte0;
+            unsigned char *s0 = rs_smem + buf * stage_bytes + (2 * rr) * p.seg_bytes, *s1 = s0 + p.seg_bytes;
+            for (int v = lane; v < g.nvec; v += 32) {
+                rs_cp_async16(s0 + 16 * v, g0 + 16 * v);
+                rs_cp_async16(s1 + 16 * v, g1 + 16 * v);
             }
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    if ((int)blockIdx.x < p.ntiles) stage(blockIdx.x, 0);
+    int k = 0;
+    for (int t = blockIdx.x; t < p.ntiles; t += gridDim.x, k++) {
+    const int buf = k & 1;
+    if (t + (int)gridDim.x < p.ntiles) {
+        stage(t + gridDim.x, buf ^ 1);
+        asm volatile("cp.async.wait_group 1;" ::: "memory");               // everything but the prefetch has landed
+    } else {
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
     __syncthreads();
+    const RsTile tg = rs_tile<BPP>(p, t);
+    const int dx_first = tg.dx_first, dy_first = tg.dy_first, ncols = tg.ncols, nrows = tg.nrows, byte0 = tg.byte0;
+    const unsigned char *s_in = rs_smem + buf * stage_bytes;
 
     // ---- interpolate: warp rr = destination row rr of the tile, lane l = pixels l, l + 32, ... of that row
     // (neighbouring lanes read neighbouring taps: shared-memory reads are conflict-free or two-way, and every
@@ -222,6 +256,8 @@ __global__ void __launch_bounds__(RS_THREADS) k_resize(const ResizeParams p)
             const int rr = i / tail, b = (nv << 4) + (i - rr * tail);
             p.dst[(size_t)(dy_first + rr) * p.dpitch + xoff + b] = s_out[rr * out_stride + b];
         }
+    }
+    __syncthreads();                            // the buffer just read is the next prefetch target
     }
 }
 

@@ -116,7 +116,8 @@ struct XfLists {
                                     //              last MCU's Y11 / Cb / Cr (k_job_begin links the units with them)
     float list_q;                   // quality whose tables bound the lists (k_entropy_prepare has the rule)
     int table_mode;
-    FitState *st;                   // kernel clock of the job (FitState.kt[0]); nullptr: not a fit job
+    FitState *st;                   // kernel clock of the job: block 0 stamps FitState.kt[0][0]; the END of this kernel is
+                                    // stamped by the job-start kernel when its griddepcontrol.wait returns.  nullptr: none
 };
 
 // survivor test on a column-pass result d = x * 65536 + junk (0 <= junk < 65536): |x| >= t  <=>  d lies
@@ -163,7 +164,7 @@ constexpr int XF_OFF_WTOT = XF_OFF_THR + 1024;
 constexpr int XF_SMEM_BYTES = XF_OFF_WTOT + 64;
 static_assert(XF_OFF_BAR % 16 == 0, "shared-memory carve-up");
 
-template <bool BGR>
+template <bool BGR, bool LISTS>
 __global__ void __launch_bounds__(XF_THREADS, XF_CTAS)
 k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__restrict__ coef,
             int tiles_per_row, int ntiles, const XfLists xl)
@@ -176,7 +177,7 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
     uint32_t *s_wtot = reinterpret_cast<uint32_t *>(smem_raw + XF_OFF_WTOT);      // survivor entries per warp of blocks
 
     const int tid = threadIdx.x, lane = tid & 31;
-    const bool lists = xl.ent != nullptr;
+    constexpr bool lists = LISTS;           // (the coefficient-only instance carries no survivor test at all)
     pdl_launch_dependents();        // the job-start kernel may set up while this grid drains
     if (tid == 0) {
         if (blockIdx.x == 0 && xl.st) xl.st->kt[0][0] = gtime();
@@ -312,10 +313,14 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
             }
             uint32_t P[32];
             const uint4 *thr = s_thr + (bc >= 4 ? 32 : 0);
-            fdct_block_col_m<0>(sw, P, thr, mlo, mhi); fdct_block_col_m<1>(sw, P, thr, mlo, mhi);
-            fdct_block_col_m<2>(sw, P, thr, mlo, mhi); fdct_block_col_m<3>(sw, P, thr, mlo, mhi);
-            fdct_block_col_m<4>(sw, P, thr, mlo, mhi); fdct_block_col_m<5>(sw, P, thr, mlo, mhi);
-            fdct_block_col_m<6>(sw, P, thr, mlo, mhi); fdct_block_col_m<7>(sw, P, thr, mlo, mhi);
+            if (lists) {
+                fdct_block_col_m<0>(sw, P, thr, mlo, mhi); fdct_block_col_m<1>(sw, P, thr, mlo, mhi);
+                fdct_block_col_m<2>(sw, P, thr, mlo, mhi); fdct_block_col_m<3>(sw, P, thr, mlo, mhi);
+                fdct_block_col_m<4>(sw, P, thr, mlo, mhi); fdct_block_col_m<5>(sw, P, thr, mlo, mhi);
+                fdct_block_col_m<6>(sw, P, thr, mlo, mhi); fdct_block_col_m<7>(sw, P, thr, mlo, mhi);
+            } else {
+                fdct_block_bytes(sw, P);
+            }
             if (dummy) {
                 P[0] &= 0xffffu;
 #pragma unroll
@@ -410,9 +415,6 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
                 tma_load_2d(tile, &tmap, tx2 * (TILE_ROW_BYTES / 4), my2 * 16, &full[s]);
             }
         }
-    }
-    if (tid == 0 && xl.st) {        // kernel clock: the last CTA to finish stamps the end
-        if (atomicAdd(&xl.st->xf_done, 1u) == gridDim.x - 1u) { xl.st->xf_done = 0; xl.st->kt[0][1] = gtime(); }
     }
 }
 

@@ -13,10 +13,10 @@ import java.util.Objects;
 import static work.pollochang.compression.image.tools.ImageTools.resizeImage;
 
 /**
- * Drop-in replacement of the reference's ImageCompressionPng: null checks, the "already inside
- * the box" rule and the min(widthRatio, heightRatio) scale are icb_png_target_dims, the resize is
- * the GPU kernel behind ImageTools.resizeImage, and the PNG file is produced by icb_png_encode
- * (GPU row filters + deflate) with ImageIO as the path for rasters the library does not take.
+ * Drop-in replacement of the reference's ImageCompressionPng: the whole method is one call,
+ * icb_png_compress -- the "already inside the box" rule and the min(widthRatio, heightRatio) scale
+ * (icb_png_target_dims), the bilinear resize, and the PNG file (GPU row filters + deflate), with the
+ * resized pixels never leaving the GPU.  ImageIO stays the path for rasters the library does not take.
  * NOT COMPILED IN THE BUILD IMAGE.  The reference's three JUnit cases
  * (ImageCompressionPngTest.java:38-88) hold for this body unchanged.
  */
@@ -28,18 +28,17 @@ public final class ImageCompressionPng {
         Objects.requireNonNull(originalImage, "originalImage must not be null");
         Objects.requireNonNull(outputFile, "outputFile must not be null");
         Objects.requireNonNull(params, "params must not be null");
-        int[] dims = Icb.pngTargetDims(originalImage.getWidth(), originalImage.getHeight(), params.minWidth(),
-                params.minHeight());
-        if (dims == null) return false;
+        Icb.Png png = Icb.pngCompress(originalImage, params.minWidth(), params.minHeight());
+        if (png.status() == Icb.NO_FIT) return false;                       // already inside the box
+        if (png.status() == Icb.OK) {
+            Files.write(outputFile, png.file());
+            return true;
+        }
+        // raster type the library does not take: the stock path with the GPU resize where it applies
         double scale = Math.min((double) params.minWidth() / originalImage.getWidth(),
                 (double) params.minHeight() / originalImage.getHeight());
         BufferedImage resized = resizeImage(originalImage, scale);
         try {
-            byte[] png = Icb.pngEncode(resized);
-            if (png != null) {
-                Files.write(outputFile, png);
-                return true;
-            }
             return ImageIO.write(resized, "png", outputFile.toFile());
         } finally {
             resized.flush();

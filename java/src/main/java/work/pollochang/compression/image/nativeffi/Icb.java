@@ -75,6 +75,11 @@ public final class Icb {
     private static final MethodHandle PNG_ENCODE = h("icb_png_encode", FunctionDescriptor.of(JAVA_INT,
             ADDRESS, ADDRESS, JAVA_INT, JAVA_INT, JAVA_INT, JAVA_INT, ADDRESS, JAVA_LONG, ADDRESS));
 
+    // int icb_png_compress(h, src, w, hgt, pitch, fmt, min_w, min_h, out, out_cap, *out_len, *dw, *dh)
+    private static final MethodHandle PNG_COMPRESS = h("icb_png_compress", FunctionDescriptor.of(JAVA_INT,
+            ADDRESS, ADDRESS, JAVA_INT, JAVA_INT, JAVA_INT, JAVA_INT, JAVA_INT, JAVA_INT, ADDRESS, JAVA_LONG, ADDRESS,
+            ADDRESS, ADDRESS));
+
     private static volatile MemorySegment handle;
 
     /** The process-wide handle; created on first use.  No CUDA device -> IllegalStateException: the
@@ -144,14 +149,20 @@ public final class Icb {
         };
     }
 
-    /** Copies the raster of a byte-backed image into this thread's pinned staging buffer. */
+    /** Copies the raster of a byte- or int-backed image into this thread's pinned staging buffer (an int
+     *  raster lands as little-endian bytes: TYPE_INT_ARGB = B G R A, TYPE_INT_RGB = B G R x). */
     private static MemorySegment stageBytes(BufferedImage img, int bpp) {
         Raster r = img.getRaster();
-        if (!(r.getDataBuffer() instanceof DataBufferByte db)) throw new IllegalArgumentException("not a byte raster");
         long n = (long) img.getWidth() * img.getHeight() * bpp;
         MemorySegment pin = STAGING.get().px(n);
-        MemorySegment.copy(MemorySegment.ofArray(db.getData()), 0, pin, 0, n);
+        if (r.getDataBuffer() instanceof DataBufferByte db) MemorySegment.copy(MemorySegment.ofArray(db.getData()), 0, pin, 0, n);
+        else if (r.getDataBuffer() instanceof java.awt.image.DataBufferInt di) MemorySegment.copy(MemorySegment.ofArray(di.getData()), 0, pin, 0, n);
+        else throw new IllegalArgumentException("raster is neither byte nor int backed");
         return pin;
+    }
+
+    private static int bytesPerPixel(int fmt) {
+        return fmt == FMT_GRAY8 ? 1 : (fmt == FMT_RGB8 || fmt == FMT_BGR8) ? 3 : 4;
     }
 
     /** Result of {@link #jpgFit}. */
@@ -252,6 +263,39 @@ public final class Icb {
             throw e;
         } catch (Throwable t) {
             throw new IllegalStateException(t);
+        }
+    }
+
+    /** Result of {@link #pngCompress}: status OK with the PNG file, NO_FIT (already inside the box), or
+     *  ERR_UNSUPPORTED (raster type not taken: run the stock body). */
+    public record Png(int status, byte[] file, int width, int height) { }
+
+    /** core/ImageCompressionPng.java:37-75 as ONE call: dimension rule, resize and PNG file on the GPU; the
+     *  resized pixels never come back to the host. */
+    public static Png pngCompress(BufferedImage img, int minW, int minH) throws IOException {
+        int fmt = formatOf(img);
+        int w = img.getWidth(), hgt = img.getHeight();
+        int[] d = pngTargetDims(w, hgt, minW, minH);
+        if (d == null) return new Png(NO_FIT, null, 0, 0);                // the rule comes first, whatever the raster type
+        if (fmt < 0) return new Png(ERR_UNSUPPORTED, null, 0, 0);
+        int bpp = bytesPerPixel(fmt);
+        MemorySegment px = stageBytes(img, bpp);
+        long cap = (long) d[0] * d[1] * bpp * 5 / 4 + 65536;
+        try (Arena a = Arena.ofConfined()) {
+            MemorySegment outLen = a.allocate(JAVA_LONG), dw = a.allocate(JAVA_INT), dh = a.allocate(JAVA_INT);
+            while (true) {
+                MemorySegment out = STAGING.get().out(cap);
+                int rc = (int) PNG_COMPRESS.invokeExact(handle(), px, w, hgt, w * bpp, fmt, minW, minH, out, cap, outLen, dw, dh);
+                if (rc == ERR_CAPACITY && outLen.get(JAVA_LONG, 0) > cap) { cap = outLen.get(JAVA_LONG, 0); continue; }
+                if (rc == ERR_OOM) throw new OutOfMemoryError("icb_png_compress");
+                if (rc == ERR_UNSUPPORTED || rc == NO_FIT) return new Png(rc, null, 0, 0);
+                if (rc != OK) throw new IOException("icb_png_compress status " + rc);
+                return new Png(OK, out.asSlice(0, outLen.get(JAVA_LONG, 0)).toArray(JAVA_BYTE), dw.get(JAVA_INT, 0), dh.get(JAVA_INT, 0));
+            }
+        } catch (RuntimeException | Error | IOException e) {
+            throw e;
+        } catch (Throwable t) {
+            throw new IOException(t);
         }
     }
 

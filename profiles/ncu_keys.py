@@ -12,8 +12,11 @@ want = ['gpu__time_duration.sum', 'dram__bytes_read.sum', 'dram__bytes_write.sum
         'sm__inst_executed_pipe_lsu.avg.pct_of_peak_sustained_active',
         'l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum', 'smsp__inst_executed_op_shared_atom.sum',
         'smsp__inst_executed_op_branch.sum', 'launch__waves_per_multiprocessor', 'sm__cycles_elapsed.max']
+# every pipe-utilisation counter the report has (DESIGN.md section 4 argues from these)
+want += [hn for hn in hdr if hn not in want and (hn.startswith('sm__pipe_') and hn.endswith('pct_of_peak_sustained_active')
+         or hn.startswith('sm__inst_executed_pipe_') and hn.endswith('.sum'))]
 for r in rows[2:]:
-    print('--', r[hdr.index('Kernel Name')][:40])
+    print('--', r[hdr.index('Kernel Name')][:60])
     for w in want:
         if w in hdr:
             print('   %-70s %s %s' % (w, r[hdr.index(w)], rows[1][hdr.index(w)]))
