@@ -44,7 +44,7 @@ struct DeviceCtx {
     cudaEvent_t join = nullptr;
 };
 
-enum Phase { PH_IDLE = 0, PH_CACHED, PH_SEARCH, PH_RESIZE, PH_PNG, PH_DONE };
+enum Phase { PH_IDLE = 0, PH_CACHED, PH_SEARCH, PH_RESIZE, PH_PNG, PH_PNG_FETCH, PH_DONE };
 
 struct Job {
     Phase phase = PH_IDLE;
@@ -244,6 +244,21 @@ int setup_device(icb_handle *h, DeviceCtx &d)
     memcpy(huf, ac_enc, sizeof(ac_enc));
     memcpy(huf + 512, dc_enc, sizeof(dc_enc));
     CK(cudaMemcpyToSymbol(g_huf, huf, sizeof(huf)));
+    {   // CRC-32 byte table and the "256 zero bytes" advance operator (k_png.cuh g_crc)
+        static uint32_t crc[256 + 4 * 256];
+        for (uint32_t i = 0; i < 256; i++) {
+            uint32_t c = i;
+            for (int k = 0; k < 8; k++) c = (c & 1u) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+            crc[i] = c;
+        }
+        for (int j = 0; j < 4; j++)
+            for (uint32_t b = 0; b < 256; b++) {
+                uint32_t c = b << (8 * j);
+                for (int k = 0; k < PNG_CRC_SEG; k++) c = crc[c & 0xffu] ^ (c >> 8);
+                crc[256 + 256 * j + b] = c;
+            }
+        CK(cudaMemcpyToSymbol(g_crc, crc, sizeof(crc)));
+    }
     unsigned char hdr[HEADER_BYTES + 16];
     build_header_template(hdr, dc_bits, ac_bits, ac_vals);
     CK(cudaMemcpyToSymbol(c_hdr, hdr, HEADER_BYTES));
@@ -1110,31 +1125,17 @@ int enqueue_png(icb_handle *h, Slot *s, const unsigned char *d_src, int w, int h
     pp.out_cap = (long long)fcap;
     cudaStream_t st = s->stream;
     CK(cudaMemsetAsync(pp.hist, 0, 320 * 4, st));
-    k_png_filter<<<(hgt + 7) / 8, 256, 0, st>>>(pp);
+    k_png_filter<<<hgt, 256, 0, st>>>(pp);
     k_png_hist<<<(pp.npieces + 7) / 8, 256, 0, st>>>(pp);
-    k_png_tree<<<1, 32, 0, st>>>(pp);
+    k_png_tree<<<1, PNG_TREE_THREADS, 0, st>>>(pp);
     k_png_encode<<<(pp.npieces + 7) / 8, 256, 0, st>>>(pp);
     k_png_scan<<<1, 1024, 0, st>>>(pp);
     k_png_merge<<<(pp.npieces + 1 + 7) / 8, 256, 0, st>>>(pp);
     const long long max_idat = ((long long)fcap + PNG_IDAT - 1) / PNG_IDAT;
-    k_png_finish<<<(unsigned)((std::min<long long>(max_idat, ((long long)pp.nfilt * 2) / PNG_IDAT + 2) + 127) / 128), 128, 0, st>>>(pp);
+    k_png_finish<<<(unsigned)((std::min<long long>(max_idat, ((long long)pp.nfilt * 2) / PNG_IDAT + 2) + 7) / 8), 256, 0, st>>>(pp);
     CK(cudaGetLastError());
     h->kernels += 7;
-    // file bytes to the caller: the length is known on the device only
-    if (j.out && j.out_cap) {
-        unsigned char *dst = j.out;
-        long long dcap = (long long)j.out_cap;
-        if (!j.out_pinned || ((uintptr_t)j.out & 15)) {
-            rc = ensure_pinned(h, s->h_out, s->h_out_cap, std::min(fcap, round_up(j.out_cap, 16) + 32));
-            if (rc) return rc;
-            dst = s->h_out;
-            dcap = (long long)std::min(s->h_out_cap, j.out_cap);
-            j.stage_stream = true;
-        }
-        k_fetch_len<<<16, FETCH_THREADS, 0, st>>>(pp.out_len, s->d_file, (long long)fcap, dst, dcap);
-        CK(cudaGetLastError());
-        h->kernels += 1;
-    }
+    // the file's length comes back first; drive_job then fetches exactly that many bytes (PH_PNG_FETCH)
     CK(cudaMemcpyAsync(s->h_len, pp.out_len, 8, cudaMemcpyDeviceToHost, st));
     j.phase = PH_PNG;
     return ICB_OK;
@@ -1164,15 +1165,26 @@ bool drive_job(icb_handle *h, Slot *s, bool wait)
         if (!wait && e == cudaErrorNotReady) return false;
         if (e != cudaSuccess) { status = fail(h, ICB_ERR_CUDA, "stream", e); break; }
         if (s->job.phase == PH_RESIZE) { collect_output(s); s->job.res.status = ICB_OK; break; }
-        if (s->job.phase == PH_PNG) {
+        if (s->job.phase == PH_PNG) {                    // the length is here: fetch the file, exactly that many bytes
             Job &j = s->job;
             j.res.out_len = (size_t)*s->h_len;
             j.res.device = h->devs[s->devi].dev;
-            status = j.res.out_len <= j.out_cap ? ICB_OK : ICB_ERR_CAPACITY;
-            if (status == ICB_OK) {
-                h->d2h += j.res.out_len;
-                if (j.stage_stream) memcpy(j.out, s->h_out, j.res.out_len);
+            if (j.res.out_len > j.out_cap || !j.out) { status = ICB_ERR_CAPACITY; break; }
+            unsigned char *dst = j.out;
+            if (!j.out_pinned) {
+                if (ensure_pinned(h, s->h_out, s->h_out_cap, j.res.out_len + 16)) { status = ICB_ERR_OOM; break; }
+                dst = s->h_out;
+                j.stage_stream = true;
             }
+            e = cudaMemcpyAsync(dst, s->d_file, j.res.out_len, cudaMemcpyDeviceToHost, s->stream);
+            if (e != cudaSuccess) { status = fail(h, ICB_ERR_CUDA, "PNG D2H", e); break; }
+            h->d2h += j.res.out_len + 8;
+            j.phase = PH_PNG_FETCH;
+            continue;
+        }
+        if (s->job.phase == PH_PNG_FETCH) {
+            if (s->job.stage_stream) memcpy(s->job.out, s->h_out, s->job.res.out_len);
+            status = ICB_OK;
             break;
         }
         int rc = fit_advance(h, s);

@@ -197,12 +197,15 @@ __global__ void __launch_bounds__(BEGIN_THREADS) k_job_begin(const EntParams p, 
     if (blockIdx.x == 0 && threadIdx.x == 0) p.st->kt[0][1] = gtime(); // = the moment the transform grid finished
     const int u = blockIdx.x * BEGIN_THREADS + threadIdx.x;
     if (u < 1 || u >= p.nunits) return;
-    const uint4 prev = __ldcg(reinterpret_cast<const uint4 *>(p.unit_info) + (u - 1));   // .y = Y11 | Cb << 16, .z = Cr
-    const uint32_t pos = __ldcg(reinterpret_cast<const uint32_t *>(p.unit_info) + 4 * u);      // Cb | Cr << 16
+    // two independent 32-byte reads, three plain stores: the entries come complete out of unit_info
+    const uint4 *info = reinterpret_cast<const uint4 *>(p.unit_info);
+    const uint4 prev = __ldcg(info + 2 * (u - 1));            // .y = Y11 | Cb << 16, .z = Cr (low half)
+    const uint4 mine0 = __ldcg(info + 2 * u);                  // .x = Cb index | Cr index << 16, .w = Y00 entry
+    const uint4 mine1 = __ldcg(info + 2 * u + 1);              // .x = Cb entry, .y = Cr entry
     uint32_t *list = p.ent + (size_t)u * UNIT_CAP;
-    list[0] |= (prev.y & 0x3fffu) << 18;
-    list[pos & 0xffffu] |= ((prev.y >> 16) & 0x3fffu) << 18;
-    list[pos >> 16] |= (prev.z & 0x3fffu) << 18;
+    list[0] = mine0.w | ((prev.y & 0x3fffu) << 18);
+    list[mine0.x & 0xffffu] = mine1.x | (((prev.y >> 16) & 0x3fffu) << 18);
+    list[mine0.x >> 16] = mine1.y | ((prev.z & 0x3fffu) << 18);
 }
 
 // Between two passes of a long search: when the upper end of the bracket has dropped well below

@@ -58,7 +58,7 @@ struct EntParams {
     FitState *st;
     uint32_t *ent;                  // [nunits][UNIT_CAP] survivor entries, one list per unit (common.cuh)
     unsigned int *ent_cnt;          // [nunits]
-    unsigned short *unit_info;      // [nunits][8] links between the units' DC predictors (k_transform.cuh XfLists)
+    unsigned short *unit_info;      // [nunits][16] links between the units' DC predictors (k_transform.cuh XfLists)
     PassBufs buf[2];                // ping-pong: the best pass so far is never overwritten
     int nblocks, nunits, ntiles, nchunks;
     int unit_group, scr_stride;     // units per entropy tile (Geom.unit_group), scratch words reserved per tile
@@ -961,7 +961,7 @@ __host__ __device__ inline size_t ent_pass_bytes(int ntiles, int nchunks, int sc
 __host__ __device__ inline size_t ent_list_bytes(int nunits)
 {
     const size_t n = (size_t)nunits;
-    return n * (size_t)UNIT_CAP * 4 + ((n + 3) / 4 * 4) * 4 + n * 16 + 256;
+    return n * (size_t)UNIT_CAP * 4 + ((n + 3) / 4 * 4) * 4 + n * 32 + 256;
 }
 
 }  // namespace icb

@@ -67,12 +67,14 @@ __device__ __forceinline__ int png_paeth(int a, int b, int c)
 }
 
 // ---- rows -> filtered rows ----------------------------------------------------------------
-// One warp per row.  PNG sample order is R G B [A]; the source raster may be BGR / ABGR / BGRA (perm).
+// One CTA per row (256 threads walk its pixels).  PNG sample order is R G B [A]; the source raster may be
+// BGR / ABGR / BGRA (perm).
 __global__ void __launch_bounds__(256) k_png_filter(const PngParams p)
 {
-    const int lane = threadIdx.x & 31;
-    const int y = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (y >= p.h) return;
+    __shared__ uint32_t s_sum[8][5];
+    __shared__ int s_best;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int y = blockIdx.x;
     const unsigned char *cur = p.src + (size_t)y * p.pitch;
     const unsigned char *up = y > 0 ? cur - p.pitch : nullptr;
     const int rowbytes = p.w * p.pbpp;
@@ -82,7 +84,7 @@ __global__ void __launch_bounds__(256) k_png_filter(const PngParams p)
         return (row && x >= 0) ? (int)row[(size_t)x * p.sbpp + ((p.perm >> (4 * c)) & 15)] : 0;
     };
     auto mag = [](int v) -> uint32_t { const int s = (int)(signed char)(v & 0xff); return (uint32_t)abs(s); };
-    for (int x = lane; x < p.w; x += 32) {
+    for (int x = tid; x < p.w; x += 256) {
         for (int c = 0; c < p.pbpp; c++) {
             const int v = sample(cur, x, c), a = sample(cur, x - 1, c), b = sample(up, x, c), cc = sample(up, x - 1, c);
             sum[0] += mag(v);
@@ -92,15 +94,26 @@ __global__ void __launch_bounds__(256) k_png_filter(const PngParams p)
             sum[4] += mag(v - png_paeth(a, b, cc));
         }
     }
-    int best = 0;
-    uint32_t best_sum = 0;
 #pragma unroll
     for (int f = 0; f < 5; f++) {
-        const uint32_t s = __reduce_add_sync(0xffffffffu, sum[f]);
-        if (f == 0 || s < best_sum) { best = f; best_sum = s; }     // strict <: ties keep the lower filter type
+        const uint32_t t = __reduce_add_sync(0xffffffffu, sum[f]);
+        if (lane == 0) s_sum[warp][f] = t;
     }
-    if (lane == 0) o[0] = (unsigned char)best;
-    for (int x = lane; x < p.w; x += 32) {
+    __syncthreads();
+    if (tid == 0) {
+        int best = 0;
+        uint32_t best_sum = 0;
+        for (int f = 0; f < 5; f++) {
+            uint32_t t = 0;
+            for (int w = 0; w < 8; w++) t += s_sum[w][f];
+            if (f == 0 || t < best_sum) { best = f; best_sum = t; }     // strict <: ties keep the lower filter type
+        }
+        s_best = best;
+        o[0] = (unsigned char)best;
+    }
+    __syncthreads();
+    const int best = s_best;
+    for (int x = tid; x < p.w; x += 256) {
         for (int c = 0; c < p.pbpp; c++) {
             const int v = sample(cur, x, c), a = sample(cur, x - 1, c), b = sample(up, x, c), cc = sample(up, x - 1, c);
             int pr = 0;
@@ -197,16 +210,21 @@ __global__ void __launch_bounds__(256) k_png_hist(const PngParams p)
 // sort, two-queue Huffman merge, then the length limit: lengths above the limit are cut to it and the
 // Kraft sum is restored on the per-length counts before the lengths are handed out again by rank.
 // work: caller's 8-byte aligned scratch of >= 8 * n + 16 ints.  Symbols with count 0 get length 0.
-__device__ void png_code_lengths(const unsigned int *freq, int n, int maxbits, unsigned char *len, int *work)
+// sorted != nullptr: the symbols with a non-zero count already in (count, symbol) order, m of them (the caller's
+// threads ranked them in parallel); else an insertion sort runs here (small alphabets).
+__device__ void png_code_lengths(const unsigned int *freq, int n, int maxbits, unsigned char *len, int *work,
+                                 const int *sorted = nullptr, int m_sorted = 0)
 {
     // work: sym [0, n) | parent [n, 3n) | depth of the leaves by rank [3n, 4n) | internal weights, 64 bit [4n, 6n) |
     //       depth per node [6n + 8, 8n + 8)
     int *sym = work, *parent = work + n, *depth = work + 3 * n;
     int m = 0;
-    for (int i = 0; i < n; i++) { len[i] = 0; if (freq[i]) sym[m++] = i; }
+    for (int i = 0; i < n; i++) len[i] = 0;
+    if (sorted) { m = m_sorted; for (int i = 0; i < m; i++) sym[i] = sorted[i]; }
+    else for (int i = 0; i < n; i++) if (freq[i]) sym[m++] = i;
     if (m == 0) return;
     if (m == 1) { len[sym[0]] = 1; return; }
-    for (int i = 1; i < m; i++) {                                   // insertion sort by (count, symbol)
+    for (int i = 1; i < m && !sorted; i++) {                        // insertion sort by (count, symbol)
         const int s = sym[i];
         int j = i - 1;
         while (j >= 0 && (freq[sym[j]] > freq[s] || (freq[sym[j]] == freq[s] && sym[j] > s))) { sym[j + 1] = sym[j]; j--; }
@@ -293,17 +311,68 @@ struct PngBitWriter {
     }
 };
 
-// One thread: code lengths and codes of the block, segment 0 (zlib header + block header), Adler-32.
-__global__ void k_png_tree(const PngParams p)
+// One CTA: the threads rank the symbols by count in parallel and sum the Adler-32 partials; thread 0 then builds
+// the code lengths and codes of the block and segment 0 (zlib header + block header).
+constexpr int PNG_TREE_THREADS = 320;
+__global__ void __launch_bounds__(PNG_TREE_THREADS) k_png_tree(const PngParams p)
 {
     __shared__ __align__(8) int s_work[8 * 288 + 64];
     __shared__ unsigned char s_len[288 + 32];
     __shared__ unsigned int s_clfreq[19];
     __shared__ unsigned char s_cllen[19];
     __shared__ uint32_t s_clcode[19];
-    if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    p.hist[256] += 1;                                               // end-of-block
-    png_code_lengths(p.hist, PNG_NLIT, 15, s_len, s_work);
+    __shared__ unsigned int s_freq[288];
+    __shared__ int s_sorted[288];
+    __shared__ int s_m;
+    const int tid = threadIdx.x;
+    if (tid < 288) s_freq[tid] = tid < PNG_NLIT ? p.hist[tid] + (tid == 256 ? 1u : 0u) : 0u;   // + the end-of-block symbol
+    if (tid == 0) s_m = 0;
+    __syncthreads();
+    if (tid < PNG_NLIT && s_freq[tid]) {                            // rank among the used symbols by (count, symbol)
+        const unsigned int f = s_freq[tid];
+        int r = 0;
+        for (int j = 0; j < PNG_NLIT; j++) {
+            const unsigned int g = s_freq[j];
+            r += (g && (g < f || (g == f && j < tid))) ? 1 : 0;
+        }
+        s_sorted[r] = tid;
+        atomicAdd(&s_m, 1);
+    }
+    // Adler-32 of the whole filtered stream from the pieces' partial sums (a, b): A = 1 + sum a_c,
+    // B = sum_c [ b_c + n_c * (1 + sum_{c' < c} a_c') ], everything mod 65521 -- a prefix over the pieces
+    {
+        __shared__ unsigned long long s_pa[PNG_TREE_THREADS], s_pb[PNG_TREE_THREADS];
+        const int per = (p.npieces + PNG_TREE_THREADS - 1) / PNG_TREE_THREADS;
+        const int c0 = min(p.npieces, tid * per), c1 = min(p.npieces, c0 + per);
+        unsigned long long sa = 0;
+        for (int c = c0; c < c1; c++) sa += p.adler[c].x;
+        s_pa[tid] = sa;
+        __syncthreads();
+        if (tid == 0) {                                             // 320 partial sums: a serial prefix is enough
+            unsigned long long run = 1;
+            for (int t = 0; t < PNG_TREE_THREADS; t++) { const unsigned long long v = s_pa[t]; s_pa[t] = run % 65521ull; run += v; }
+            s_pb[0] = run % 65521ull;                               // A
+        }
+        __syncthreads();
+        const unsigned long long A_total = s_pb[0];
+        __syncthreads();
+        unsigned long long before = s_pa[tid], sb = 0;              // 1 + sum of a over the pieces in front
+        for (int c = c0; c < c1; c++) {
+            const uint2 v = p.adler[c];
+            const unsigned long long n = c == p.npieces - 1 ? (unsigned long long)(p.nfilt - (long long)c * PNG_PIECE) : PNG_PIECE;
+            sb = (sb + v.y + n * before) % 65521ull;
+            before = (before + v.x) % 65521ull;
+        }
+        s_pb[tid] = sb;
+        __syncthreads();
+        if (tid == 0) {
+            unsigned long long B = 0;
+            for (int t = 0; t < PNG_TREE_THREADS; t++) B += s_pb[t];
+            p.adler_out[0] = (unsigned int)(((B % 65521ull) << 16) | A_total);
+        }
+    }
+    if (tid != 0) return;
+    png_code_lengths(s_freq, PNG_NLIT, 15, s_len, s_work, s_sorted, s_m);
     unsigned char *dlen = s_len + 288;
     for (int i = 0; i < 30; i++) dlen[i] = 0;
     dlen[0] = 1;                                                    // the one distance the encoder uses (1)
@@ -335,15 +404,6 @@ __global__ void k_png_tree(const PngParams p)
     for (int i = 0; i < nlit; i++) bw.put(s_clcode[s_len[i]] >> 8, (int)(s_clcode[s_len[i]] & 0xff));
     for (int i = 0; i < ndist; i++) bw.put(s_clcode[dlen[i]] >> 8, (int)(s_clcode[dlen[i]] & 0xff));
     p.seg_len[0] = bw.pos;
-    // Adler-32 of the filtered stream from the pieces' partial sums
-    unsigned long long A = 1, B = 0;
-    for (int i = 0; i < p.npieces; i++) {
-        const uint2 s = p.adler[i];
-        const long long n = i == p.npieces - 1 ? p.nfilt - (long long)i * PNG_PIECE : PNG_PIECE;
-        B = (B + (unsigned long long)n * A + s.y) % 65521ull;
-        A = (A + s.x) % 65521ull;
-    }
-    p.adler_out[0] = (unsigned int)((B << 16) | A);
 }
 
 // ---- tokens -> bits ------------------------------------------------------------------------
@@ -483,29 +543,37 @@ __global__ void __launch_bounds__(256) k_png_merge(const PngParams p)
     }
 }
 
+// CRC-32 tables, filled by the host at init: [0..255] the byte table (reflected 0xEDB88320), [256 + 256 j + b] =
+// the register after 256 zero bytes when it starts as b << 8 j -- the CRC register is linear over GF(2), so
+// "advance by one 256-byte segment" is four look-ups, and a chunk's CRC can be folded from 32 lanes' segments.
+__device__ uint32_t g_crc[256 + 4 * 256];
+constexpr int PNG_CRC_SEG = 256;
+
 __device__ __forceinline__ uint32_t png_crc_step(const uint32_t *tab, uint32_t crc, uint32_t byte)
 {
     return tab[(crc ^ byte) & 0xffu] ^ (crc >> 8);
 }
 
-// Signature, IHDR, IEND, and one thread per IDAT chunk: length, type and the CRC-32 of type + data.
-__global__ void __launch_bounds__(128) k_png_finish(const PngParams p)
+__device__ __forceinline__ uint32_t png_crc_adv(const uint32_t *tab, uint32_t c)       // c after PNG_CRC_SEG zero bytes
 {
-    __shared__ uint32_t s_tab[256];
-    for (int i = threadIdx.x; i < 256; i += 128) {
-        uint32_t c = (uint32_t)i;
-        for (int k = 0; k < 8; k++) c = (c & 1u) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
-        s_tab[i] = c;
-    }
+    return tab[256 + (c & 0xffu)] ^ tab[512 + ((c >> 8) & 0xffu)] ^ tab[768 + ((c >> 16) & 0xffu)] ^ tab[1024 + (c >> 24)];
+}
+
+// Signature, IHDR, IEND, and one warp per IDAT chunk: length, type, and the CRC-32 of type + data folded from
+// the lanes' 256-byte segments.
+__global__ void __launch_bounds__(256) k_png_finish(const PngParams p)
+{
+    __shared__ uint32_t s_tab[256 + 4 * 256];
+    for (int i = threadIdx.x; i < 256 + 4 * 256; i += 256) s_tab[i] = g_crc[i];
     __syncthreads();
+    const int lane = threadIdx.x & 31;
     const unsigned long long zbytes = ((p.seg_pos[p.npieces + 1] + 7) >> 3) + 4;
     const unsigned long long nidat = (zbytes + PNG_IDAT - 1) / PNG_IDAT;
     auto put32 = [&](long long off, uint32_t v) {
         for (int i = 0; i < 4; i++)
             if (off + i < p.out_cap) p.out[off + i] = (unsigned char)(v >> (24 - 8 * i));
     };
-    const unsigned long long t = (unsigned long long)blockIdx.x * 128 + threadIdx.x;
-    if (t == 0) {
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
         const unsigned char sig[8] = {0x89, 'P', 'N', 'G', 0x0D, 0x0A, 0x1A, 0x0A};
         unsigned char ihdr[17] = {'I', 'H', 'D', 'R', 0, 0, 0, 0, 0, 0, 0, 0, 8, 0, 0, 0, 0};
         for (int i = 0; i < 4; i++) { ihdr[4 + i] = (unsigned char)(p.w >> (24 - 8 * i)); ihdr[8 + i] = (unsigned char)(p.h >> (24 - 8 * i)); }
@@ -522,18 +590,30 @@ __global__ void __launch_bounds__(128) k_png_finish(const PngParams p)
         for (int i = 0; i < 4; i++) { if (e + 4 + i < p.out_cap) p.out[e + 4 + i] = iend[i]; crc = png_crc_step(s_tab, crc, iend[i]); }
         put32(e + 8, ~crc);
     }
-    if (t < nidat) {
-        const unsigned long long sb0 = t * PNG_IDAT;
-        const uint32_t n = (uint32_t)min((unsigned long long)PNG_IDAT, zbytes - sb0);
-        const long long base = 33 + (long long)t * (PNG_IDAT + 12);
-        if (base + 12 + (long long)n > p.out_cap) return;
+    const unsigned long long t = (unsigned long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (t >= nidat) return;
+    const unsigned long long sb0 = t * PNG_IDAT;
+    const uint32_t n = (uint32_t)min((unsigned long long)PNG_IDAT, zbytes - sb0);
+    const long long base = 33 + (long long)t * (PNG_IDAT + 12);
+    if (base + 12 + (long long)n > p.out_cap) return;
+    const unsigned char *d = p.out + base + 8;
+    static_assert(PNG_IDAT == 32 * PNG_CRC_SEG, "one lane per segment");
+    const uint32_t seg0 = lane * PNG_CRC_SEG;
+    const uint32_t len = n > seg0 ? min((uint32_t)PNG_CRC_SEG, n - seg0) : 0u;
+    uint32_t c = 0;                                                 // this lane's segment from a zero register
+    for (uint32_t i = 0; i < len; i++) c = png_crc_step(s_tab, c, d[seg0 + i]);
+    uint32_t acc = 0xffffffffu;                                     // lane 0 folds: type bytes, then the segments in order
+    const unsigned char idat[4] = {'I', 'D', 'A', 'T'};
+    for (int i = 0; i < 4; i++) acc = png_crc_step(s_tab, acc, idat[i]);
+    for (int l = 0; l < 32; l++) {
+        const uint32_t cl = __shfl_sync(0xffffffffu, c, l), ll = __shfl_sync(0xffffffffu, len, l);
+        if (ll == PNG_CRC_SEG) acc = png_crc_adv(s_tab, acc) ^ cl;
+        else if (ll) { for (uint32_t i = 0; i < ll; i++) acc = png_crc_step(s_tab, acc, 0); acc ^= cl; }
+    }
+    if (lane == 0) {
         put32(base, n);
-        const unsigned char idat[4] = {'I', 'D', 'A', 'T'};
-        uint32_t crc = 0xffffffffu;
-        for (int i = 0; i < 4; i++) { p.out[base + 4 + i] = idat[i]; crc = png_crc_step(s_tab, crc, idat[i]); }
-        const unsigned char *d = p.out + base + 8;
-        for (uint32_t i = 0; i < n; i++) crc = png_crc_step(s_tab, crc, d[i]);
-        put32(base + 8 + n, ~crc);
+        for (int i = 0; i < 4; i++) p.out[base + 4 + i] = idat[i];
+        put32(base + 8 + n, ~acc);
     }
 }
 

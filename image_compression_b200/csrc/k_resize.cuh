@@ -140,12 +140,14 @@ __global__ void __launch_bounds__(RS_THREADS) k_resize(const ResizeParams p)
     if (AOFF >= 0) s_inc[tid] = tid ? div8_inc(tid) : 0u;
 
     // rows y0 / y1 of every destination row of tile t, bytes [byte0, byte0 + 16 nvec): warp w stages the two
-    // source rows of destination row w, lanes walk the row's vectors
-    auto stage = [&](int t, int buf) {
-        const RsTile g = rs_tile<BPP>(p, t);
+    // source rows of destination row w, lanes walk the row's vectors.  The tile's geometry and the warp's row
+    // fraction are returned: the same tile is interpolated one iteration later, nothing is computed twice.
+    auto stage = [&](int t, int buf, RsTile &g, int &yf) {
+        g = rs_tile<BPP>(p, t);
         const int lane = tid & 31, rr = tid >> 5;
+        yf = 0;
         if (rr < g.nrows) {
-            int y0, y1, yf;
+            int y0, y1;
             rs_taps(p.ybase + (long long)(g.dy_first + rr) * p.dyl - half, p.h, y0, y1, yf);
             const unsigned char *g0 = p.src + (size_t)y0 * p.pitch + g.byte0, *g1 = p.src + (size_t)y1 * p.pitch + g.byte0;
             unsigned char *s0 = rs_smem + buf * stage_bytes + (2 * rr) * p.seg_bytes, *s1 = s0 + p.seg_bytes;
@@ -157,18 +159,21 @@ __global__ void __launch_bounds__(RS_THREADS) k_resize(const ResizeParams p)
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
 
-    if ((int)blockIdx.x < p.ntiles) stage(blockIdx.x, 0);
+    RsTile tg_next = {};
+    int yf_next = 0;
+    if ((int)blockIdx.x < p.ntiles) stage(blockIdx.x, 0, tg_next, yf_next);
     int k = 0;
     for (int t = blockIdx.x; t < p.ntiles; t += gridDim.x, k++) {
     const int buf = k & 1;
+    const RsTile tg = tg_next;
+    const int yf = yf_next;
     if (t + (int)gridDim.x < p.ntiles) {
-        stage(t + gridDim.x, buf ^ 1);
+        stage(t + gridDim.x, buf ^ 1, tg_next, yf_next);
         asm volatile("cp.async.wait_group 1;" ::: "memory");               // everything but the prefetch has landed
     } else {
         asm volatile("cp.async.wait_group 0;" ::: "memory");
     }
     __syncthreads();
-    const RsTile tg = rs_tile<BPP>(p, t);
     const int dx_first = tg.dx_first, dy_first = tg.dy_first, ncols = tg.ncols, nrows = tg.nrows, byte0 = tg.byte0;
     const unsigned char *s_in = rs_smem + buf * stage_bytes;
 
@@ -179,8 +184,6 @@ __global__ void __launch_bounds__(RS_THREADS) k_resize(const ResizeParams p)
         const int lane = tid & 31, rr = tid >> 5;
         if (rr < nrows) {
             const int dy = dy_first + rr;
-            int y0, y1, yf;
-            rs_taps(p.ybase + (long long)dy * p.dyl - half, p.h, y0, y1, yf);
             const unsigned char *r0 = s_in + (2 * rr) * p.seg_bytes - byte0, *r1 = r0 + p.seg_bytes;
             const uint32_t wy1 = (uint32_t)yf, wy0 = 256u - wy1;
             const long long dx32 = p.dxl * 32;

@@ -112,8 +112,9 @@ __device__ constexpr unsigned char kZZinv[64] = {
 struct XfLists {
     uint32_t *ent;                  // [nunits][UNIT_CAP]
     unsigned int *ent_cnt;          // [nunits]
-    unsigned short *unit_info;      // [nunits][8]: entry index of the first MCU's Cb / Cr DC entry, raw DC of the
-                                    //              last MCU's Y11 / Cb / Cr (k_job_begin links the units with them)
+    unsigned short *unit_info;      // [nunits][16] what k_job_begin links the units with: [0], [1] entry index of the first
+                                    //   MCU's Cb / Cr DC entry; [2..4] raw DC of the last MCU's Y11 / Cb / Cr; [6..11] the
+                                    //   first MCU's Y00 / Cb / Cr DC entries themselves (32 bits each, predictor field 0)
     float list_q;                   // quality whose tables bound the lists (k_entropy_prepare has the rule)
     int table_mode;
     FitState *st;                   // kernel clock of the job: block 0 stamps FitState.kt[0][0]; the END of this kernel is
@@ -367,9 +368,12 @@ k_transform(const __grid_constant__ CUtensorMap tmap, const Geom g, int16_t *__r
                 int xp = 0;
                 if (pb >= 0) xp = *reinterpret_cast<const short *>(tile + pb * 128 + (pb & 7) * 16);
                 const uint32_t dc = *reinterpret_cast<const unsigned short *>(mine + sw7 * 16);
-                if (bm == 0 && bc >= 4) xl.unit_info[8 * (size_t)t + (bc - 4)] = (unsigned short)rank;
-                if (bm == nm - 1 && bc >= 3) xl.unit_info[8 * (size_t)t + 2 + (bc - 3)] = (unsigned short)dc;
-                out[rank++] = ENTRY_DC | tag | ((uint32_t)xp << 18) | dc;
+                const uint32_t dc_entry = ENTRY_DC | tag | ((uint32_t)xp << 18) | dc;
+                if (bm == 0 && bc >= 4) xl.unit_info[16 * (size_t)t + (bc - 4)] = (unsigned short)rank;
+                if (bm == nm - 1 && bc >= 3) xl.unit_info[16 * (size_t)t + 2 + (bc - 3)] = (unsigned short)dc;
+                if (bm == 0 && (bc == 0 || bc >= 4))
+                    reinterpret_cast<uint32_t *>(xl.unit_info + 16 * (size_t)t + 6)[bc == 0 ? 0 : bc - 3] = dc_entry;
+                out[rank++] = dc_entry;
                 uint32_t m = mlo & ~1u;
                 while (m) {
                     const uint32_t z = __ffs(m) - 1;
