@@ -30,7 +30,7 @@ ABI_SYMBOLS = [
     "icb_subsample_factor", "icb_subsample",
     "icb_submit_jpg_fit", "icb_wait", "icb_poll", "icb_submit_resize", "icb_submit_png_fit",
     "icb_png_encode", "icb_submit_png_encode", "icb_png_compress", "icb_submit_png_compress",
-    "icb_profile_resize_series",
+    "icb_profile_resize_series", "icb_png_encode_device_noalloc",
     "icb_run_list",
     "icb_image_upload", "icb_image_free",
     "icb_submit_jpg_fit_image", "icb_submit_resize_image", "icb_stats", "icb_profile_jpg_fit_image",
@@ -151,6 +151,7 @@ def load_library(build_if_missing: bool = True):
                                    C.POINTER(C.c_size_t), C.POINTER(C.c_int), C.POINTER(C.c_int)]
     L.icb_submit_png_compress.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp,
                                           C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int64)]
+    L.icb_png_encode_device_noalloc.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_size_t, vp, vp]
     L.icb_profile_resize_series.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float)]
     L.icb_run_list.argtypes = [vp, C.POINTER(_Item), C.c_size_t, C.c_int, C.c_int]
     L.icb_image_upload.argtypes = [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]

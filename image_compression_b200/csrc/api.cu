@@ -1884,3 +1884,124 @@ extern "C" int icb_run_list(icb_handle *h, icb_item *items, size_t n, int thread
     }
     return ICB_OK;
 }
+
+// ======================================================================
+//  C ABI, part 4: a PNG encode that allocates nothing
+// ======================================================================
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernels and
+// the same work-arena layout as enqueue_png above, but the arena is the file-scope array below instead of a
+// slot's cudaMalloc'ed d_png, pixels and file are the caller's DEVICE buffers, and the kernels go on the
+// caller's stream.  Every GPU that loads the library holds the array until exit.
+namespace {
+
+constexpr long long NOALLOC_MAX_FILT = 1 << 20;        // filtered bytes h * (1 + w * png_bpp): e.g. 512 x 511 RGBA
+constexpr size_t noalloc_arena_bytes()
+{
+    const size_t np = (size_t)(NOALLOC_MAX_FILT / PNG_PIECE);
+    size_t o = ((size_t)NOALLOC_MAX_FILT + 64 + 255) / 256 * 256;      // filt
+    o += (np + 1) * PNG_PIECE_WORDS * 4;                                // seg_bits
+    o = (o + (np + 1) * 4 + 7) / 8 * 8;                                 // seg_len
+    o += (np + 2) * 8 + np * 8 + 320 * 4 + 320 * 4 + 64;                // seg_pos, adler, hist, codes, misc
+    return (o + 255) / 256 * 256;
+}
+constexpr size_t NOALLOC_ARENA_BYTES = noalloc_arena_bytes();           // 5.3 MB
+
+}  // namespace
+
+// In host code this name is only a stand-in for the symbol, not a device address: the address the kernels
+// get comes from cudaGetSymbolAddress, once per device (noalloc_arena below).
+static __device__ __align__(256) unsigned char g_noalloc_arena[NOALLOC_ARENA_BYTES];
+
+namespace {
+
+std::mutex g_noalloc_mu;
+unsigned char *g_noalloc_ptr[64] = {nullptr};           // per device ordinal: device address of g_noalloc_arena
+
+// set-up, once per device, with that device current: the arena's device address and the CRC tables
+// k_png_finish reads (the same values setup_device stores; a handle need not exist)
+int noalloc_arena(icb_handle *h, int dev, unsigned char **out)
+{
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+        void *ptr = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&ptr, g_noalloc_arena);
+        if (e != cudaSuccess || !ptr) return fail(h, ICB_ERR_CUDA, "cudaGetSymbolAddress(g_noalloc_arena)", e);
+        static uint32_t crc[256 + 4 * 256];
+        for (uint32_t i = 0; i < 256; i++) {
+            uint32_t c = i;
+            for (int k = 0; k < 8; k++) c = (c & 1u) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+            crc[i] = c;
+        }
+        for (int j = 0; j < 4; j++)
+            for (uint32_t b = 0; b < 256; b++) {
+                uint32_t c = b << (8 * j);
+                for (int k = 0; k < PNG_CRC_SEG; k++) c = crc[c & 0xffu] ^ (c >> 8);
+                crc[256 + 256 * j + b] = c;
+            }
+        e = cudaMemcpyToSymbol(g_crc, crc, sizeof(crc));
+        if (e != cudaSuccess) return fail(h, ICB_ERR_CUDA, "cudaMemcpyToSymbol(g_crc)", e);
+        g_noalloc_ptr[dev] = (unsigned char *)ptr;
+    }
+    *out = g_noalloc_ptr[dev];
+    return ICB_OK;
+}
+
+}  // namespace
+
+extern "C" int icb_png_encode_device_noalloc(icb_handle *h, const uint8_t *d_px, int w, int hgt, int pitch, int fmt,
+                                             uint8_t *d_out, size_t out_cap, unsigned long long *d_out_len,
+                                             void *stream)
+{
+    if (!d_px || !d_out || !d_out_len || w < 1 || hgt < 1) return fail(h, ICB_ERR_INVALID, "null argument");
+    if (!fmt_valid(fmt)) return fail(h, ICB_ERR_UNSUPPORTED, "format");
+    const int bpp = bpp_of(fmt);
+    if (pitch < w * bpp) return fail(h, ICB_ERR_INVALID, "pitch smaller than a row");
+    PngParams pp = {};
+    pp.src = d_px; pp.w = w; pp.h = hgt; pp.pitch = pitch; pp.sbpp = bpp;
+    png_layout(fmt, pp.pbpp, pp.perm);
+    pp.nfilt = (long long)hgt * (1 + (long long)w * pp.pbpp);
+    if (pp.nfilt > NOALLOC_MAX_FILT) {
+        char msg[160];
+        snprintf(msg, sizeof msg, "icb_png_encode_device_noalloc: h * (1 + w * png_bpp) = %lld exceeds the static arena's "
+                 "limit of %lld bytes", pp.nfilt, NOALLOC_MAX_FILT);
+        return fail(h, ICB_ERR_CAPACITY, msg);
+    }
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return fail(h, ICB_ERR_NO_DEVICE, "no current device");
+    unsigned char *arena = nullptr;
+    int rc = noalloc_arena(h, dev, &arena);
+    if (rc) return rc;
+    pp.npieces = (int)std::max<long long>(1, pp.nfilt / PNG_PIECE);
+    const size_t np = (size_t)pp.npieces;
+    const size_t o_seg = round_up((size_t)pp.nfilt + 64, 256);
+    const size_t o_len = o_seg + (np + 1) * PNG_PIECE_WORDS * 4, o_pos = round_up(o_len + (np + 1) * 4, 8);
+    const size_t o_adl = o_pos + (np + 2) * 8, o_hist = o_adl + np * 8, o_codes = o_hist + 320 * 4;
+    const size_t o_misc = o_codes + 320 * 4;
+    if (o_misc + 64 > NOALLOC_ARENA_BYTES) return fail(h, ICB_ERR_CAPACITY, "static arena layout");   // (cannot happen)
+    pp.filt = arena;
+    pp.seg_bits = reinterpret_cast<uint32_t *>(arena + o_seg);
+    pp.seg_len = reinterpret_cast<unsigned int *>(arena + o_len);
+    pp.seg_pos = reinterpret_cast<unsigned long long *>(arena + o_pos);
+    pp.adler = reinterpret_cast<uint2 *>(arena + o_adl);
+    pp.hist = reinterpret_cast<unsigned int *>(arena + o_hist);
+    pp.codes = reinterpret_cast<uint32_t *>(arena + o_codes);
+    pp.out_len = d_out_len;
+    pp.adler_out = reinterpret_cast<unsigned int *>(arena + o_misc + 8);
+    pp.out = d_out;
+    pp.out_cap = (long long)out_cap;
+    cudaStream_t st = (cudaStream_t)stream;
+    // the arena keeps the last call's contents: the histogram must start at zero (the kernels write every
+    // other field they read: k_png_tree / k_png_encode zero their bit-stream segments themselves)
+    CK(cudaMemsetAsync(pp.hist, 0, 320 * 4, st));
+    k_png_filter<<<hgt, 256, 0, st>>>(pp);
+    k_png_hist<<<(pp.npieces + 7) / 8, 256, 0, st>>>(pp);
+    k_png_tree<<<1, PNG_TREE_THREADS, 0, st>>>(pp);
+    k_png_encode<<<(pp.npieces + 7) / 8, 256, 0, st>>>(pp);
+    k_png_scan<<<1, 1024, 0, st>>>(pp);
+    k_png_merge<<<(pp.npieces + 1 + 7) / 8, 256, 0, st>>>(pp);
+    k_png_finish<<<(unsigned)((((long long)pp.nfilt * 2) / PNG_IDAT + 2 + 7) / 8), 256, 0, st>>>(pp);
+    CK(cudaGetLastError());
+    if (h) h->kernels += 7;
+    return ICB_OK;
+}

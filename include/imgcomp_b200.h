@@ -236,6 +236,27 @@ int icb_submit_png_compress(icb_handle *h, const uint8_t *src, int w, int hgt, i
                             int min_w, int min_h, uint8_t *out, size_t out_cap, int *dw, int *dh,
                             int64_t *ticket);
 
+/* No counterpart in the reference: added for callers that cannot
+ * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The PNG
+ * encoder of icb_png_encode on DEVICE buffers, allocating nothing: no cudaMalloc / cudaFree / cudaHostAlloc and
+ * no allocating library routine, on any call.  Its work arena (filtered rows, piece bit streams, histogram,
+ * code tables) is a file-scope `static __device__` array of 5.3 MB that every GPU which loads the library
+ * holds until exit; limit: h * (1 + w * png_bytes_per_pixel) <= 1 048 576 filtered bytes (e.g. 512 x 511 RGBA,
+ * 590 x 590 RGB) -- larger images return ICB_ERR_CAPACITY with the sizes in icb_last_error.
+ *   d_px / pitch / fmt : pixels in device memory of the CURRENT device (any icb_fmt), caller-owned
+ *   d_out / out_cap    : device buffer for the PNG file; bytes past out_cap are not written
+ *   d_out_len          : device word that receives the file's length (compare with out_cap after the stream
+ *                        has drained: a larger value means the file did not fit and d_out is incomplete)
+ *   stream             : a cudaStream_t (NULL = the default stream); the seven kernels are queued on it and the
+ *                        call returns without synchronising
+ *   h                  : optional (may be NULL): only receives the error text and the launch counter
+ * The first call on each device looks up the arena's device address (cudaGetSymbolAddress) and uploads the
+ * 5 KB CRC table; make that call outside a graph capture.  Every call shares the one arena, which keeps the last
+ * call's contents (the call clears what must start at zero): calls that overlap on the GPU -- two streams, or
+ * two threads -- race; serialise them on one stream. */
+int icb_png_encode_device_noalloc(icb_handle *h, const uint8_t *d_px, int w, int hgt, int pitch, int fmt,
+                                  uint8_t *d_out, size_t out_cap, unsigned long long *d_out_len, void *stream);
+
 /* Counters (CompressionBatch.java:56-62 are summed by the Java caller; these are
  * the device-side ones) and per-stage CUDA-event times of the last profiled job. */
 typedef struct {
