@@ -230,10 +230,13 @@ __constant__ unsigned char c_ac_vals[2][162] = {
      0xf9, 0xfa}};
 
 // Derived encode tables (jchuff.c jpeg_make_c_derived_tbl), filled by the host at
-// init: entry = (code << 8) | length.  AC: table * 256 + symbol;  DC: 512 + table * 16 + size.
+// init: entry = (code << 8) | length, index = plane * 256 + a * 16 + size with plane = 2 * table + isdc
+// (bits 16-17 of a survivor entry).  AC planes (0, 2): a = zero run, i.e. a * 16 + size = the symbol.  DC planes
+// (1, 3): a = 0 the plain DC code; a = 1 / 2 the EOB of the luminance / chrominance AC table joined in front of
+// it (what a DC entry emits when the block before it ended early) -- at most 4 + 11 bits.
 // Global memory, not __constant__: every CTA of the entropy pass copies the table into shared
 // memory with one coalesced load per thread (an indexed constant load replays 32 times per warp).
-constexpr int HUF_WORDS = 512 + 32;
+constexpr int HUF_WORDS = 1024;
 __device__ __align__(16) unsigned int g_huf[HUF_WORDS];
 
 }  // namespace icb

@@ -288,9 +288,9 @@ __device__ __forceinline__ uint32_t ff_starts(uint32_t a, uint32_t b)
     return a2 & __funnelshift_l(b2, a2, 4);
 }
 
-__global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
+__global__ void __launch_bounds__(ENT_THREADS, 5) k_entropy_pass(const EntParams p)
 {
-    __shared__ __align__(16) uint32_t s_huf[512 + 32];          // AC: table * 256 + run * 16 + size;  DC: 512 + table * 16 + size
+    __shared__ __align__(16) uint32_t s_huf[HUF_WORDS];         // [plane = 2 * table + isdc][run or owed EOB][size] (common.cuh g_huf)
     __shared__ __align__(16) uint2 s_qt[128];       // quantiser by key = 2 * pos + table
     __shared__ int4 s_ctl[6];                       // control block of FitState as the pass found it
     __shared__ __align__(16) uint32_t s_win[ENT_WARPS * ENT_WSTRIDE];
@@ -365,8 +365,8 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
                 reinterpret_cast<const unsigned int *>(&st->tab[c2.z].qtab[0][0])[tid];
     }
 
-    const uint32_t zrl0 = s_huf[0xF0], zrl1 = s_huf[256 + 0xF0];
-    const uint32_t eob0 = s_huf[0], eob1 = s_huf[256];
+    const uint32_t zrl0 = s_huf[0xF0], zrl1 = s_huf[512 + 0xF0];
+    const uint32_t eob0 = s_huf[0], eob1 = s_huf[512];
     const uint32_t lt_mask = (1u << lane) - 1u;
 
     // persistent CTAs: chunks of 8 consecutive tiles (one per warp) are dealt out statically (no
@@ -496,8 +496,9 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
 
         // a2.5 quantise one survivor at the current tables: sign(x) * ((|x| + 4q) / 8q), the division
         // as a multiply-high; a DC entry becomes the difference against its predictor block
-        auto quant = [&](uint32_t e, bool &isdc, uint32_t &key) -> int {
+        auto quant = [&](uint32_t e, bool &isdc, uint32_t &key, uint32_t &plane) -> int {
             isdc = (e & ENTRY_DC) != 0u;
+            plane = (e >> 8) & 0x300u;                                   // (2 * table + isdc) << 8: the entry's code table
             key = (e >> 17) & (isdc ? 1u : 127u);                        // 2 * pos + table
             const int x = (int)(short)(e & 0xffffu);
             const uint2 qt = s_qt[key];
@@ -511,20 +512,17 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         };
         // a2.7 the code of one entry whose previous live entry had key pk: symbol bits, their length
         // (0 for a dead entry), and the number of ZRL codes (16-zero runs) that go in front of it
-        auto mksym = [&](bool live, bool isdc, uint32_t key, int v, uint32_t pk, uint32_t &sym, uint32_t &len,
-                         uint32_t &nz) {
+        auto mksym = [&](bool live, bool isdc, uint32_t key, uint32_t plane, int v, uint32_t pk, uint32_t &sym,
+                         uint32_t &len, uint32_t &nz) {
             const uint32_t nb = 32u - (uint32_t)__clz(abs(v));
             const uint32_t vbits = (uint32_t)(v + (v >> 31)) & ((1u << nb) - 1u);
             const uint32_t r = ((key - pk) >> 1) - 1u;                   // zero run in front of an AC coefficient
-            const uint32_t hidx = isdc ? 512u + (key << 4) + nb : ((key & 1u) << 8) | ((r & 15u) << 4) | nb;
-            const uint32_t code = s_huf[hidx];
+            // second index of the code table: the run of an AC entry; for a DC entry whether the previous block
+            // ended early and in which table (its EOB then sits in front of the DC code, pre-joined in the table)
+            const uint32_t owed = pk < 126u ? 0x10u + ((pk & 1u) << 4) : 0u;
+            const uint32_t code = s_huf[plane | (isdc ? owed : (r & 15u) << 4) | nb];
             sym = ((code >> 8) << nb) | vbits;
             len = (code & 0xffu) + nb;
-            // a DC entry whose previous block ended early carries that block's EOB in front
-            const uint32_t z = (pk & 1u) ? eob1 : eob0;
-            const bool eob = isdc && pk < 126u;
-            sym |= eob ? (z >> 8) << len : 0u;
-            len += eob ? z & 0xffu : 0u;
             nz = (isdc || !live) ? 0u : r >> 4;
             len = live ? len : 0u;
             sym = live ? sym : 0u;
@@ -535,8 +533,8 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
         // per pair, and a pair's two codes usually go into the window as one 64-bit field
         auto code_round = [&](const uint2 ee) {
             bool dc_a, dc_b;
-            uint32_t key_a, key_b;
-            const int v_a = quant(ee.x, dc_a, key_a), v_b = quant(ee.y, dc_b, key_b);
+            uint32_t key_a, key_b, pl_a, pl_b;
+            const int v_a = quant(ee.x, dc_a, key_a, pl_a), v_b = quant(ee.y, dc_b, key_b, pl_b);
             const bool live_a = dc_a || v_a != 0, live_b = dc_b || v_b != 0;   // entries past n are 0: dead
             const uint32_t bal = __ballot_sync(0xffffffffu, live_a || live_b);
             if (bal == 0u) return;
@@ -546,8 +544,8 @@ __global__ void __launch_bounds__(ENT_THREADS) k_entropy_pass(const EntParams p)
             if (!below) pk_a = carry;                                   // key of the previous live entry
             const uint32_t pk_b = live_a ? key_a : pk_a;
             uint32_t sym_a, len_a, nz_a, sym_b, len_b, nz_b;
-            mksym(live_a, dc_a, key_a, v_a, pk_a, sym_a, len_a, nz_a);
-            mksym(live_b, dc_b, key_b, v_b, pk_b, sym_b, len_b, nz_b);
+            mksym(live_a, dc_a, key_a, pl_a, v_a, pk_a, sym_a, len_a, nz_a);
+            mksym(live_b, dc_b, key_b, pl_b, v_b, pk_b, sym_b, len_b, nz_b);
             const uint32_t zl_a = nz_a * (((key_a & 1u) ? zrl1 : zrl0) & 0xffu);
             const uint32_t zl_b = nz_b * (((key_b & 1u) ? zrl1 : zrl0) & 0xffu);
             const uint32_t tot = len_a + zl_a + len_b + zl_b;
