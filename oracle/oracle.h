@@ -108,6 +108,13 @@ int orc_subsample_factor(int w, int h);
 int orc_subsample(const uint8_t *src, int w, int h, int pitch, int bpp, int s,
                   uint8_t *dst, int dpitch);
 
+/* f2 (input staging): the JPEG reader of core/ImageCompression.java:119-155 for the files the CUDA decoder
+ * takes (baseline SOF0, 8 bit, YCbCr 4:2:0, one scan, no restart interval) -- jpeg_decode_oracle.c. */
+enum { ORC_DEC_OK = 0, ORC_DEC_UNSUPPORTED = -4, ORC_DEC_CORRUPT = -1 };
+int orc_jpeg_info(const uint8_t *file, size_t n, int *w, int *h);
+int orc_jpeg_decode_coefficients(const uint8_t *file, size_t n, int16_t *out);
+int orc_jpeg_decode(const uint8_t *file, size_t n, int fmt, uint8_t *dst, int dpitch);
+
 /* a7: ImageCompressionPng.java:49-61.  Returns 0 and the new dims when a resize
  * is due, 1 when the image already fits (reference returns false). */
 int orc_png_target_dims(int w, int h, int min_w, int min_h, int *nw, int *nh, double *scale);

@@ -44,7 +44,8 @@ def build_flags() -> str:
 
 
 def build(force: bool = False) -> str:
-    srcs = [os.path.join(_DIR, f) for f in ("jpeg_oracle.c", "resize_oracle.c", "oracle.h", "jpeg_tables.h", "Makefile")]
+    srcs = [os.path.join(_DIR, f) for f in ("jpeg_oracle.c", "resize_oracle.c", "jpeg_decode_oracle.c", "oracle.h",
+                                            "jpeg_tables.h", "Makefile")]
     stale = force or not os.path.exists(_SO) or any(os.path.getmtime(s) > os.path.getmtime(_SO) for s in srcs)
     if stale:
         cmd = ["make", "-C", _DIR, "-s", "-B", "liboracle.so"]
@@ -89,6 +90,9 @@ def lib():
         L.orc_subsample.argtypes = [u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, u8p, C.c_int]
         L.orc_png_target_dims.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int),
                                           C.POINTER(C.c_int), C.POINTER(C.c_double)]
+        L.orc_jpeg_info.argtypes = [u8p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+        L.orc_jpeg_decode_coefficients.argtypes = [u8p, C.c_size_t, i16p]
+        L.orc_jpeg_decode.argtypes = [u8p, C.c_size_t, C.c_int, u8p, C.c_int]
     return _lib
 
 
@@ -216,3 +220,39 @@ def resize(img: np.ndarray, dw: int, dh: int, fmt: int = FMT_RGB8, f64: bool = F
     rc = fn(_u8(img), w, h, pitch, fmt, _u8(dst), dw, dh, dw * c)
     assert rc == 0, rc
     return dst
+
+
+# ---- f2: the JPEG reader of core/ImageCompression.java:119-155 (jpeg_decode_oracle.c) ----
+DEC_UNSUPPORTED = -4
+
+
+def jpeg_info(data: bytes):
+    """(w, h) of a file the decoder takes; raises ValueError(code) for unsupported / corrupt files."""
+    buf = np.frombuffer(data, np.uint8)
+    w, h = C.c_int(0), C.c_int(0)
+    rc = lib().orc_jpeg_info(_u8(buf), buf.size, C.byref(w), C.byref(h))
+    if rc:
+        raise ValueError(rc)
+    return w.value, h.value
+
+
+def jpeg_decode(data: bytes, fmt: int = FMT_RGB8) -> np.ndarray:
+    w, h = jpeg_info(data)
+    buf = np.frombuffer(data, np.uint8)
+    out = np.empty((h, w, 3), np.uint8)
+    rc = lib().orc_jpeg_decode(_u8(buf), buf.size, fmt, _u8(out), w * 3)
+    if rc:
+        raise ValueError(rc)
+    return out
+
+
+def jpeg_decode_coefficients(data: bytes) -> np.ndarray:
+    """Huffman-decoded coefficients, [6 * mcus][64] int16, natural order, DC prediction undone, not dequantised."""
+    w, h = jpeg_info(data)
+    buf = np.frombuffer(data, np.uint8)
+    nb = 6 * ((w + 15) // 16) * ((h + 15) // 16)
+    out = np.empty((nb, 64), np.int16)
+    rc = lib().orc_jpeg_decode_coefficients(_u8(buf), buf.size, out.ctypes.data_as(C.POINTER(C.c_int16)))
+    if rc:
+        raise ValueError(rc)
+    return out

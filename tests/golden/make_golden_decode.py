@@ -1,0 +1,60 @@
+#!/usr/bin/env python
+"""Generates tests/golden/jpeg_decode.npz (run once, in the build container): baseline 4:2:0 JPEG files written
+by Pillow / libjpeg-turbo from the synthetic images, and the pixels Pillow / libjpeg-turbo decodes from them
+(islow IDCT, fancy upsampling: bit-exact with the IJG-6b decoder the JDK's ImageIO reader wraps).  An
+INDEPENDENT implementation: neither oracle/ nor the CUDA library takes part.
+
+    python tests/golden/make_golden_decode.py
+"""
+import io
+import os
+import sys
+
+import numpy as np
+from PIL import Image
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+from image_compression_b200 import synth  # noqa: E402
+
+CASES = [  # (seed, w, h, quality, kind)
+    (41, 64, 48, 92, "natural"), (42, 101, 75, 92, "natural"), (43, 200, 133, 75, "natural"),
+    (44, 17, 9, 92, "natural"), (45, 333, 251, 50, "natural"), (46, 16, 16, 98, "noise"),
+    (47, 130, 66, 100, "noise"), (48, 5, 3, 92, "natural"), (49, 3, 40, 92, "natural"),
+    (50, 257, 31, 30, "natural"), (51, 96, 96, 10, "natural"), (52, 48, 160, 95, "noise"),
+]
+
+
+def make(seed, w, h, kind):
+    if kind == "noise":
+        return np.random.default_rng(seed).integers(0, 256, (h, w, 3), dtype=np.uint8)
+    return synth.natural_image(seed, w, h)
+
+
+def main():
+    out = {}
+    for i, (seed, w, h, q, kind) in enumerate(CASES):
+        img = make(seed, w, h, kind)
+        bio = io.BytesIO()
+        Image.fromarray(img).save(bio, "JPEG", quality=q, subsampling=2, optimize=(i % 3 == 2))
+        data = bio.getvalue()
+        dec = np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))
+        assert dec.shape == (h, w, 3)
+        out[f"file_{i}"] = np.frombuffer(data, np.uint8)
+        out[f"pixels_{i}"] = dec
+    # files the decoder must refuse (the caller keeps the stock host decode): progressive, 4:4:4, restart interval, gray
+    img = make(60, 48, 32, "natural")
+    for name, kw in (("progressive", dict(progressive=True, subsampling=2)), ("s444", dict(subsampling=0)),
+                     ("s422", dict(subsampling=1)), ("restart", dict(subsampling=2, restart_marker_rows=1))):
+        bio = io.BytesIO()
+        Image.fromarray(img).save(bio, "JPEG", quality=90, **kw)
+        out["unsup_" + name] = np.frombuffer(bio.getvalue(), np.uint8)
+    bio = io.BytesIO()
+    Image.fromarray(img[:, :, 0]).save(bio, "JPEG", quality=90)
+    out["unsup_gray"] = np.frombuffer(bio.getvalue(), np.uint8)
+    np.savez_compressed(os.path.join(HERE, "jpeg_decode.npz"), **out)
+    print("wrote", len(CASES), "cases")
+
+
+if __name__ == "__main__":
+    main()
