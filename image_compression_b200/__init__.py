@@ -34,5 +34,6 @@ from .api import (  # noqa: F401
     load_library,
     png_target_dims,
     subsample_factor,
+    jpg_file_info,
     resize_dims,
 )

@@ -31,6 +31,7 @@ ABI_SYMBOLS = [
     "icb_submit_jpg_fit", "icb_wait", "icb_poll", "icb_submit_resize", "icb_submit_png_fit",
     "icb_png_encode", "icb_submit_png_encode", "icb_png_compress", "icb_submit_png_compress",
     "icb_profile_resize_series", "icb_png_encode_device_noalloc",
+    "icb_jpg_file_info", "icb_jpg_decode", "icb_jpg_file_fit", "icb_submit_jpg_file_fit",
     "icb_run_list",
     "icb_image_upload", "icb_image_free",
     "icb_submit_jpg_fit_image", "icb_submit_resize_image", "icb_stats", "icb_profile_jpg_fit_image",
@@ -67,7 +68,7 @@ class _Item(C.Structure):
                 ("res", _Result)]
 
 
-ITEM_KINDS = {"jpg_fit": 0, "jpg_fit_image": 1, "png_fit": 2, "png_compress": 3, "resize_image": 4}
+ITEM_KINDS = {"jpg_fit": 0, "jpg_fit_image": 1, "png_fit": 2, "png_compress": 3, "resize_image": 4, "jpg_file_fit": 5}
 
 
 class ItemList:
@@ -86,6 +87,16 @@ class ItemList:
 
     def dims(self):
         return [(int(it.dw), int(it.dh)) for it in self.arr]
+
+
+def jpg_file_info(data):
+    """(w, h) of a JPEG file the GPU reader takes (host parse only); IcbError otherwise."""
+    buf = data if isinstance(data, np.ndarray) else np.frombuffer(data, np.uint8)
+    w, h = C.c_int(0), C.c_int(0)
+    rc = load_library().icb_jpg_file_info(buf.ctypes.data, buf.size, C.byref(w), C.byref(h))
+    if rc:
+        raise IcbError(rc, "not a file the GPU JPEG reader takes")
+    return w.value, h.value
 
 
 def library_path() -> str:
@@ -152,6 +163,13 @@ def load_library(build_if_missing: bool = True):
     L.icb_submit_png_compress.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, vp,
                                           C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int64)]
     L.icb_png_encode_device_noalloc.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, C.c_size_t, vp, vp]
+    L.icb_jpg_file_info.argtypes = [vp, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.icb_jpg_decode.argtypes = [vp, vp, C.c_size_t, C.c_int, vp, C.c_size_t, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.icb_jpg_file_fit.argtypes = [vp, vp, C.c_size_t, C.c_float, C.c_int64, C.c_int, C.c_float, C.c_double, vp, C.c_size_t,
+                                   C.POINTER(C.c_size_t), C.POINTER(C.c_float), C.POINTER(C.c_double), C.POINTER(C.c_int),
+                                   C.POINTER(C.c_int), C.POINTER(C.c_int)]
+    L.icb_submit_jpg_file_fit.argtypes = [vp, vp, C.c_size_t, C.c_float, C.c_int64, C.c_int, C.c_float, C.c_double, vp,
+                                          C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int64)]
     L.icb_profile_resize_series.argtypes = [vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_float)]
     L.icb_run_list.argtypes = [vp, C.POINTER(_Item), C.c_size_t, C.c_int, C.c_int]
     L.icb_image_upload.argtypes = [vp, C.c_int, vp, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(vp)]
@@ -594,6 +612,40 @@ class Engine:
             raise self._err(rc)
         return bool(d.value)
 
+    # ---- the JPEG reader of core/ImageCompression.java:119-155 on the GPU ----
+    def jpg_decode(self, data, fmt: int = FMT_RGB8) -> np.ndarray:
+        """ImageIO's reader.read for a baseline 4:2:0 file -> (h, w, 3) pixels; IcbError(ICB_ERR_UNSUPPORTED) for the
+        files the caller keeps decoding on the host."""
+        buf = data if isinstance(data, np.ndarray) else np.frombuffer(data, np.uint8)
+        w, h = jpg_file_info(buf)
+        out = np.empty((h, w, 3), np.uint8)
+        ww, hh = C.c_int(0), C.c_int(0)
+        rc = self._L.icb_jpg_decode(self._h, buf.ctypes.data, buf.size, fmt, out.ctypes.data, out.size, w * 3,
+                                    C.byref(ww), C.byref(hh))
+        if rc:
+            raise self._err(rc)
+        return out
+
+    def submit_jpg_file_fit(self, data, init_q: float, target: int, out: np.ndarray,
+                            cached: Optional[LearnedParams] = None) -> int:
+        buf = data if isinstance(data, np.ndarray) else np.frombuffer(data, np.uint8)
+        t, w, h = C.c_int64(0), C.c_int(0), C.c_int(0)
+        rc = self._L.icb_submit_jpg_file_fit(self._h, buf.ctypes.data, buf.size, C.c_float(init_q), int(target),
+                                             1 if cached else 0, C.c_float(cached.quality if cached else 0.0),
+                                             C.c_double(cached.scale if cached else 1.0), out.ctypes.data, out.size,
+                                             C.byref(w), C.byref(h), C.byref(t))
+        if rc:
+            raise self._err(rc)
+        self._inflight[t.value] = (buf, out)
+        return t.value
+
+    def jpg_file_fit(self, data, init_q: float, target: int, cached: Optional[LearnedParams] = None) -> FitResult:
+        """decodeImageWithSubsampling + compressJpgWithTargetSize on the file bytes; .data = the JFIF output"""
+        out = np.empty(max(int(target), 1), np.uint8)
+        r = self.wait(self.submit_jpg_file_fit(data, init_q, target, out, cached))
+        r.data = bytes(out[: r.out_len]) if r.status == ICB_OK else None
+        return r
+
     # ---- the batch executor in native code (CompressionBatch.java:64-108) ----
     def make_items(self, specs) -> ItemList:
         """specs: dicts with kind ("jpg_fit" | "jpg_fit_image" | "png_fit" | "png_compress" | "resize_image"),
@@ -607,6 +659,10 @@ class Engine:
             if kind in ("jpg_fit_image", "resize_image"):
                 h = sp["image"]
                 it.img = getattr(h, "value", h)
+            elif kind == "jpg_file_fit":
+                buf = sp["file"] if isinstance(sp["file"], np.ndarray) else np.frombuffer(sp["file"], np.uint8)
+                it.px, it.pitch = buf.ctypes.data, buf.size
+                keep.append(buf)
             else:
                 image, w, hh, pitch, fmt = _image_args(sp["image"], sp.get("fmt"))
                 it.px, it.w, it.h, it.pitch, it.fmt = image.ctypes.data, w, hh, pitch, fmt

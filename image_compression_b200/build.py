@@ -12,6 +12,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libimgcomp_b200.so")
 SOURCES = ["api.cu"]
 DEPS = ["api.cu", "common.cuh", "xf_arith.cuh", "k_transform.cuh", "k_entropy.cuh", "k_control.cuh", "k_resize.cuh",
+        "k_png.cuh", "k_decode.cuh", "jpeg_parse.h",
         os.path.join("..", "..", "include", "imgcomp_b200.h")]
 
 

@@ -22,6 +22,8 @@
 #include "../../include/imgcomp_b200.h"
 #include "common.cuh"
 #include "k_control.cuh"
+#include "k_decode.cuh"
+#include "jpeg_parse.h"
 #include "k_entropy.cuh"
 #include "k_png.cuh"
 #include "k_resize.cuh"
@@ -66,6 +68,8 @@ struct Job {
     long long dev_cap = 0;                  // capacity handed to the kernels
     int passes = 0;
     bool xf_this_phase = false;             // the phase in flight ran the transform (its kernel clock is fresh)
+    bool from_file = false;                 // the pixels come out of the GPU JPEG reader: its verdict counts
+    unsigned int dec_nblocks = 0;
     icb_result res{};
 };
 
@@ -89,6 +93,14 @@ struct Slot {
     unsigned char *d_png = nullptr;   size_t png_cap = 0;       // PNG encoder work arena (k_png.cuh)
     unsigned char *d_file = nullptr;  size_t file_cap = 0;      // the PNG file as it is assembled
     unsigned long long *h_len = nullptr;                        // pinned: length of the PNG file of the job in flight
+    // GPU JPEG reader (k_decode.cuh): the file, its unstuffed scan, per-subsequence states, planes, tables
+    unsigned char *d_file_in = nullptr; size_t file_in_cap = 0;
+    unsigned char *d_bits = nullptr;    size_t bits_cap = 0;
+    unsigned char *d_sub = nullptr;     size_t sub_cap = 0;
+    unsigned char *d_planes = nullptr;  size_t planes_cap = 0;
+    unsigned char *d_dec = nullptr;     size_t dec_cap = 0;     // decoded raster when the decode rule subsamples it
+    DecTables *d_dectab = nullptr;      DecTables *h_dectab = nullptr;      // h_*: pinned
+    DecState *d_decst = nullptr;        DecState *h_decst = nullptr;
     Geom geom{};
     bool busy = false;
     bool lone = false;                      // the job in flight found no other slot of its GPU busy (enqueue_transform)
@@ -1010,6 +1022,10 @@ void icb_shutdown(icb_handle *h)
         cudaFree(s.d_out); cudaFree(s.d_state); cudaFree(s.d_ent);
         if (s.h_state) cudaFreeHost(s.h_state);
         cudaFree(s.d_png); cudaFree(s.d_file);
+        cudaFree(s.d_file_in); cudaFree(s.d_bits); cudaFree(s.d_sub); cudaFree(s.d_planes); cudaFree(s.d_dec);
+        cudaFree(s.d_dectab); cudaFree(s.d_decst);
+        if (s.h_dectab) cudaFreeHost(s.h_dectab);
+        if (s.h_decst) cudaFreeHost(s.h_decst);
         if (s.h_len) cudaFreeHost(s.h_len);
         if (s.h_in) cudaFreeHost(s.h_in);
         if (s.h_out) cudaFreeHost(s.h_out);
@@ -1174,6 +1190,27 @@ int check_resize_args(icb_handle *h, const void *src, int w, int hgt, int pitch,
     return ICB_OK;
 }
 
+// After the stream drained: what the GPU JPEG reader (k_decode.cuh) says about the job's file.  The fixed point of
+// the synchronisation rounds must have been reached, the stream must hold the image's blocks, and the last block
+// must end inside the last byte (the padding) of the entropy-coded data.
+int decode_verdict(icb_handle *h, Slot *s)
+{
+    const DecState &ds = *s->h_decst;
+    static const bool dbg = getenv("ICB_DEC_DEBUG") != nullptr;
+    if (dbg) {
+        int r = 1;
+        while (r < DEC_ROUNDS && ds.active[r]) r++;
+        fprintf(stderr, "icb decode: %u bytes of scan, rounds until nothing changed %d, blocks %u / %u, end bit %u of %u\n",
+                ds.total_bytes, r, ds.blocks_found, s->job.dec_nblocks, ds.end_bit, ds.total_bytes * 8u);
+    }
+    if (ds.active[DEC_ROUNDS - 1]) return fail(h, ICB_ERR_UNSUPPORTED, "JPEG reader: no fixed point within the synchronisation rounds");
+    if (ds.blocks_found < s->job.dec_nblocks) return fail(h, ICB_ERR_INVALID, "JPEG reader: entropy-coded data ends early");
+    const unsigned int total_bits = ds.total_bytes * 8u;
+    if (ds.end_bit > total_bits || total_bits - ds.end_bit >= 16u)
+        return fail(h, ICB_ERR_INVALID, "JPEG reader: data left over after the last block");
+    return ICB_OK;
+}
+
 // Drives the job that holds slot s: wait = false returns false as soon as the stream still has work.
 // On true the job is finished and s->job.res is final.
 bool drive_job(icb_handle *h, Slot *s, bool wait)
@@ -1210,7 +1247,14 @@ bool drive_job(icb_handle *h, Slot *s, bool wait)
             break;
         }
         int rc = fit_advance(h, s);
-        if (rc == 0) { status = s->job.res.status; break; }
+        if (rc == 0) {
+            status = s->job.res.status;
+            if (s->job.from_file) {                  // the pixels the fit ran on: did the GPU reader decode them?
+                const int dv = decode_verdict(h, s);
+                if (dv) { status = dv; s->job.res.out_len = 0; }
+            }
+            break;
+        }
         if (rc < 0) { status = rc; cudaStreamSynchronize(s->stream); break; }
     }
     s->job.res.status = status;
@@ -1854,6 +1898,10 @@ int submit_item(icb_handle *h, icb_item *it, int64_t *ticket)
     case ICB_ITEM_PNG_COMPRESS:
         return icb_submit_png_compress(h, it->px, it->w, it->h, it->pitch, it->fmt, it->min_w, it->min_h, it->out,
                                        it->out_cap, &it->dw, &it->dh, ticket);
+    case ICB_ITEM_JPG_FILE_FIT:
+        return icb_submit_jpg_file_fit(h, it->px, (size_t)(it->pitch > 0 ? it->pitch : 0), it->init_q, it->target,
+                                       it->has_cached, it->cached_q, it->cached_scale, it->out, it->out_cap, &it->dw,
+                                       &it->dh, ticket);
     case ICB_ITEM_RESIZE_IMAGE:
         if (!it->img) return ICB_ERR_INVALID;
         return icb_submit_resize_image(h, it->img, it->dw, it->dh, it->out, it->out ? it->dw * bpp_of(it->img->fmt) : 0,
@@ -2027,3 +2075,201 @@ extern "C" int icb_png_encode_device_noalloc(icb_handle *h, const uint8_t *d_px,
     if (h) h->kernels += 7;
     return ICB_OK;
 }
+
+// ======================================================================
+//  C ABI, part 5: the JPEG reader on the GPU (core/ImageCompression.java:119-155)
+// ======================================================================
+namespace {
+
+int map_parse(icb_handle *h, int jp)
+{
+    if (jp == JP_OK) return ICB_OK;
+    if (jp == JP_UNSUPPORTED)
+        return fail(h, ICB_ERR_UNSUPPORTED, "JPEG reader takes baseline 8-bit YCbCr 4:2:0, one scan, no restart interval");
+    return fail(h, ICB_ERR_INVALID, "not a JPEG file / truncated header");
+}
+
+// file bytes (host) -> decoded raster in d_out (pitch out_pitch, RGB8 or BGR8), all queued on the slot's stream
+int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const JpegHeader &hd, unsigned char *d_out,
+                   int out_pitch, bool bgr)
+{
+    cudaStream_t st = s->stream;
+    const int mcu_cols = (hd.w + 15) / 16, mcu_rows = (hd.h + 15) / 16;
+    const size_t nblocks = (size_t)mcu_cols * mcu_rows * 6;
+    const size_t scan_bytes = n - hd.scan_off;
+    static const unsigned int sub_bits = [] {
+        const char *e = getenv("ICB_DEC_SUB");
+        const int v = e ? atoi(e) : DEC_SUB_BITS;
+        return (unsigned int)(v >= 256 && v <= 4096 && v % 32 == 0 ? v : DEC_SUB_BITS);   // (11 bits of block count: >= 4 bits a block)
+    }();
+    const unsigned int nsub_max = (unsigned int)((scan_bytes * 8 + sub_bits - 1) / sub_bits);
+    if (nsub_max >= (1u << 18)) return fail(h, ICB_ERR_UNSUPPORTED, "JPEG reader: scan too long for the subsequence records");
+    const int nchunks = (int)((scan_bytes + DEC_CHUNK - 1) / DEC_CHUNK);
+    if (!s->d_dectab) {
+        if (cudaMalloc((void **)&s->d_dectab, sizeof(DecTables)) != cudaSuccess ||
+            cudaMalloc((void **)&s->d_decst, sizeof(DecState)) != cudaSuccess ||
+            cudaMallocHost((void **)&s->h_dectab, sizeof(DecTables)) != cudaSuccess ||
+            cudaMallocHost((void **)&s->h_decst, sizeof(DecState)) != cudaSuccess)
+            return fail(h, ICB_ERR_OOM, "decode tables");
+    }
+    int rc = ensure(h, s->d_file_in, s->file_in_cap, round_up(n, 256) + 256);
+    if (!rc) rc = ensure(h, s->d_bits, s->bits_cap, round_up(scan_bytes, 256) + 512);
+    const size_t sub_bytes = round_up((size_t)nsub_max * 8, 256);
+    const size_t nmcu = nblocks / 6, ndc = (nmcu + DEC_DC_THREADS - 1) / DEC_DC_THREADS;
+    const size_t o_base = sub_bytes, o_chunk = o_base + round_up((size_t)nsub_max * 4, 256);
+    const size_t o_mcu = o_chunk + round_up((size_t)(nchunks + 1) * 4, 256), o_cta = o_mcu + round_up(nmcu * 12, 256);
+    if (!rc) rc = ensure(h, s->d_sub, s->sub_cap, o_cta + round_up(ndc * 12, 256));
+    const size_t ysz = (size_t)mcu_cols * 16 * mcu_rows * 16;
+    if (!rc) rc = ensure(h, s->d_planes, s->planes_cap, ysz + ysz / 2 + 256);
+    if (!rc) rc = ensure(h, s->d_coef, s->coef_cap, nblocks * 128);
+    if (rc) return rc;
+    jpeg_build_tables(hd, *s->h_dectab);
+    CK(cudaMemcpyAsync(s->d_dectab, s->h_dectab, sizeof(DecTables), cudaMemcpyHostToDevice, st));
+    rc = upload(h, s, s->d_file_in, (int)std::min<size_t>(n, 0x7fffffff), file, (int)n, 1, (int)n, 1);
+    if (rc) return rc;
+    DecParams dp = {};
+    dp.file = s->d_file_in; dp.file_len = (unsigned int)n; dp.scan_off = (unsigned int)hd.scan_off;
+    dp.bits = s->d_bits;
+    dp.rec = reinterpret_cast<unsigned long long *>(s->d_sub);
+    dp.sub_bits = sub_bits;
+    dp.blk_base = reinterpret_cast<unsigned int *>(s->d_sub + o_base);
+    dp.chunk_drop = reinterpret_cast<unsigned int *>(s->d_sub + o_chunk);
+    dp.mcu_pref = reinterpret_cast<int *>(s->d_sub + o_mcu);
+    dp.cta_pref = reinterpret_cast<int *>(s->d_sub + o_cta);
+    dp.coef = s->d_coef;
+    dp.planes = s->d_planes;
+    dp.rgb = d_out; dp.rgb_pitch = out_pitch; dp.bgr = bgr ? 1 : 0;
+    dp.w = hd.w; dp.h = hd.h; dp.mcu_cols = mcu_cols; dp.mcu_rows = mcu_rows;
+    dp.nblocks = (unsigned int)nblocks;
+    dp.nsub_max = nsub_max;
+    dp.tab = s->d_dectab;
+    dp.st = s->d_decst;
+    // state: everything zero, the scan ends at the end of the file unless a marker turns up earlier
+    CK(cudaMemsetAsync(s->d_decst, 0, sizeof(DecState), st));
+    CK(cudaMemsetAsync(&s->d_decst->scan_end, 0xff, 4, st));
+    CK(cudaMemsetAsync(s->d_coef, 0, nblocks * 128, st));
+    CK(cudaMemsetAsync(s->d_sub, 0xff, sub_bytes, st));              // no record yet
+    k_dec_scan<<<nchunks, 256, 0, st>>>(dp);
+    k_dec_offsets<<<1, 1024, 0, st>>>(dp, nchunks);
+    k_dec_unstuff<<<nchunks, 256, 0, st>>>(dp);
+    const unsigned int sgrid = (nsub_max + 127) / 128;
+    for (int r = 0; r < DEC_ROUNDS; r++) k_dec_sync<<<sgrid, 128, 0, st>>>(dp, r);
+    k_dec_blocks<<<1, 1024, 0, st>>>(dp);
+    k_dec_write<<<sgrid, 128, 0, st>>>(dp);
+    k_dec_dc_local<<<(unsigned int)ndc, DEC_DC_THREADS, 0, st>>>(dp);
+    k_dec_dc_cta<<<1, 1024, 0, st>>>(dp, (int)ndc);
+    k_dec_idct<<<(unsigned int)((nblocks + 127) / 128), 128, 0, st>>>(dp);
+    k_dec_color<<<dim3((hd.w + 255) / 256, (hd.h + 7) / 8), 256, 0, st>>>(dp);
+    CK(cudaGetLastError());
+    h->kernels += 9 + DEC_ROUNDS;
+    CK(cudaMemcpyAsync(s->h_decst, s->d_decst, sizeof(DecState), cudaMemcpyDeviceToHost, st));
+    s->job.dec_nblocks = (unsigned int)nblocks;
+    return ICB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int icb_jpg_file_info(const uint8_t *file, size_t n, int *w, int *hgt)
+{
+    JpegHeader hd;
+    const int jp = jpeg_parse(file, n, hd);
+    if (jp) return jp == JP_UNSUPPORTED ? ICB_ERR_UNSUPPORTED : ICB_ERR_INVALID;
+    if (w) *w = hd.w;
+    if (hgt) *hgt = hd.h;
+    return ICB_OK;
+}
+
+int icb_jpg_decode(icb_handle *h, const uint8_t *file, size_t n, int fmt, uint8_t *dst, size_t dst_cap, int dpitch,
+                   int *w, int *hgt)
+{
+    if (!h) return ICB_ERR_INVALID;
+    if (!file || !dst || n > 0x7ffffff0u) return fail(h, ICB_ERR_INVALID, "bad arguments");
+    if (fmt != ICB_FMT_RGB8 && fmt != ICB_FMT_BGR8) return fail(h, ICB_ERR_UNSUPPORTED, "format");
+    JpegHeader hd;
+    int rc = map_parse(h, jpeg_parse(file, n, hd));
+    if (rc) return rc;
+    if (w) *w = hd.w;
+    if (hgt) *hgt = hd.h;
+    if (dpitch < hd.w * 3 || dst_cap < (size_t)dpitch * (hd.h - 1) + (size_t)hd.w * 3) return fail(h, ICB_ERR_CAPACITY, "dst too small");
+    Slot *s = acquire_slot(h);
+    const int dp = dev_pitch(hd.w, 3);
+    if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "cudaSetDevice");
+    s->job = Job();
+    if (!rc) rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)dp * hd.h + 16);
+    if (!rc) rc = enqueue_decode(h, s, file, n, hd, s->d_rgb, dp, fmt == ICB_FMT_BGR8);
+    if (!rc) {
+        cudaError_t e = cudaMemcpy2DAsync(dst, dpitch, s->d_rgb, dp, (size_t)hd.w * 3, hd.h, cudaMemcpyDeviceToHost, s->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s->stream);
+        if (e != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "decode", e);
+        h->d2h += (uint64_t)hd.w * 3 * hd.h;
+    } else {
+        cudaStreamSynchronize(s->stream);
+    }
+    if (!rc) rc = decode_verdict(h, s);
+    h->images_done++;
+    release_slot(h, s);
+    return rc;
+}
+
+int icb_submit_jpg_file_fit(icb_handle *h, const uint8_t *file, size_t n, float init_q, int64_t target, int has_cached,
+                            float cached_q, double cached_scale, uint8_t *out, size_t out_cap, int *w, int *hgt,
+                            int64_t *ticket)
+{
+    if (!h) return ICB_ERR_INVALID;
+    if (!file || !ticket || n > 0x7ffffff0u) return fail(h, ICB_ERR_INVALID, "bad arguments");
+    int rc = check_fit_qualities(h, init_q, has_cached, cached_q);
+    if (rc) return rc;
+    JpegHeader hd;
+    rc = map_parse(h, jpeg_parse(file, n, hd));
+    if (rc) return rc;
+    // core/ImageCompression.java:140-153: the decode rule -- what the seam sees is the subsampled raster
+    const int sf = icb_subsample_factor(hd.w, hd.h);
+    const int fw = (hd.w + sf - 1) / sf, fh = (hd.h + sf - 1) / sf;
+    if (w) *w = fw;
+    if (hgt) *hgt = fh;
+    Slot *s = acquire_slot(h);
+    if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "cudaSetDevice");
+    s->job = Job();
+    const int fp = dev_pitch(fw, 3);
+    if (!rc) rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)fp * fh + 16);
+    unsigned int nblk = 0;
+    if (!rc && sf == 1) {
+        rc = enqueue_decode(h, s, file, n, hd, s->d_rgb, fp, false);
+    } else if (!rc) {
+        const int dp = dev_pitch(hd.w, 3);
+        rc = ensure(h, s->d_dec, s->dec_cap, (size_t)dp * hd.h + 16);
+        if (!rc) rc = enqueue_decode(h, s, file, n, hd, s->d_dec, dp, false);
+        if (!rc) {
+            k_subsample<3><<<dim3((fw + 127) / 128, (fh + 7) / 8), 256, 0, s->stream>>>(s->d_dec, dp, sf, s->d_rgb, fw, fh, fp);
+            h->kernels++;
+            if (cudaGetLastError() != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "subsample");
+        }
+    }
+    nblk = s->job.dec_nblocks;
+    if (!rc) rc = start_fit(h, s, s->d_rgb, fw, fh, fp, ICB_FMT_RGB8, init_q, target, has_cached, cached_q, cached_scale, out, out_cap);
+    if (rc) { cudaStreamSynchronize(s->stream); release_slot(h, s); return rc; }
+    s->job.from_file = true;
+    s->job.dec_nblocks = nblk;
+    *ticket = make_ticket(s);
+    return ICB_OK;
+}
+
+int icb_jpg_file_fit(icb_handle *h, const uint8_t *file, size_t n, float init_q, int64_t target, int has_cached,
+                     float cached_q, double cached_scale, uint8_t *out, size_t out_cap, size_t *out_len, float *best_q,
+                     double *scale, int *used_cache, int *w, int *hgt)
+{
+    int64_t t = 0;
+    int rc = icb_submit_jpg_file_fit(h, file, n, init_q, target, has_cached, cached_q, cached_scale, out, out_cap, w, hgt, &t);
+    if (rc) return rc;
+    icb_result r;
+    rc = icb_wait(h, t, &r);
+    if (out_len) *out_len = r.out_len;
+    if (best_q) *best_q = r.best_q;
+    if (scale) *scale = r.scale;
+    if (used_cache) *used_cache = r.used_cache;
+    return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,614 @@
+// k_decode.cuh -- SURVEY section 8 row f2 (input staging): the JPEG reader in front of the JPG seam, on the GPU.
+//
+// Replaces reader.read(0, param) of core/ImageCompression.java:119-155 for the files that make up the reference's
+// workload (baseline SOF0, 8 bit, YCbCr 4:2:0, one interleaved scan, no restart interval): the caller uploads the
+// FILE (a few MB) instead of the decoded raster (36 MB for 12 MP), which is what bounds the end-to-end rate on a
+// PCIe link.  Anything else is refused on the host (ICB_ERR_UNSUPPORTED: the caller keeps the stock ImageIO decode).
+// Arithmetic = the JDK reader's libjavajpeg = IJG libjpeg 6b with its defaults [JDK-mem], restated in
+// oracle/jpeg_decode_oracle.c and pinned there against libjpeg-turbo: jdhuff.c decode_mcu, jidctint.c
+// jpeg_idct_islow with jddctmgr.c's dequantisation and the & RANGE_MASK range limit, jdsample.c
+// h2v2_fancy_upsample with jdmainct.c's context rows, jdcolor.c ycc_rgb_convert.
+//
+// A Huffman stream has no entry points, so it is decoded the self-synchronising way (Weissenberger & Schmidt,
+// ICPP 2018, restated from the paper): the unstuffed bit stream is cut into subsequences of DEC_SUB_BITS bits, one
+// thread each.  Round 0 decodes every subsequence from a guessed state (symbol boundary, first block of an MCU) and
+// each thread carries on into the following subsequences until it arrives in a state somebody already decoded
+// from; round r > 0 repeats that for every subsequence whose left neighbour's exit state is not the one it was
+// decoded from.  Thread 0 starts exact and correct records are never overwritten by wrong ones, so the exact
+// prefix grows every round -- by as much as the code needs to re-synchronise (bit position, zigzag index and the
+// block's place in the 4:2:0 MCU: a few thousand bits on photographs).  The fixed point is the sequential decode;
+// a job that has not reached it after DEC_ROUNDS rounds reports ICB_ERR_UNSUPPORTED (host decode).  Then: block counts -> prefix -> a last
+// decode that writes the coefficients, DC prediction as a scan over MCUs, IDCT into planes, upsample + colour.
+// Kernels, all on the job's stream:
+//   k_dec_scan     per 4 KB of file: stuffed-zero count, position of the first marker
+//   k_dec_offsets  prefix of those counts (one CTA)
+//   k_dec_unstuff  the entropy-coded bytes without the stuffed zeros, zero padded
+//   k_dec_sync     one synchronisation round (DEC_ROUNDS launches, no-ops once nothing changes)
+//   k_dec_blocks   blocks in front of every subsequence (one CTA)
+//   k_dec_write    coefficients (quantised, natural order, DC as differences) into the block array
+//   k_dec_dc_local / k_dec_dc_cta   per-component prefix of the DC differences over the MCUs
+//   k_dec_idct     DC prediction undone, dequantise + islow inverse DCT, one thread per block -> Y / Cb / Cr planes
+//   k_dec_color    fancy h2v2 upsampling + YCbCr -> RGB, eight pixels per thread -> the decoded raster
+#pragma once
+
+#include "common.cuh"
+
+namespace icb {
+
+constexpr int DEC_SUB_BITS = 2048;          // bits per subsequence (a multiple of 32); ICB_DEC_SUB overrides per process
+constexpr int DEC_ROUNDS = 10;              // synchronisation rounds queued per job (<= 32: five bits of the record)
+constexpr int DEC_CARRY = 8;                // subsequences a thread carries on through per round
+constexpr int DEC_CHUNK = 4096;             // file bytes per CTA of the scan / unstuff kernels
+constexpr int DEC_LUT_BITS = 10;
+
+// Huffman decode tables of one file, built on the host (api.cu build_dec_tables): per table t = class * 2 + id
+// (0, 1 DC; 2, 3 AC) a look-up by the next DEC_LUT_BITS bits -> (length << 8) | symbol, 0 = longer than the
+// look-up; and jdhuff.c's maxcode / valoffset / huffval for the long codes.
+struct DecTables {
+    unsigned short lut[4][1 << DEC_LUT_BITS];
+    int maxcode[4][18];
+    int valoff[4][18];
+    unsigned char huffval[4][256];
+    unsigned short qt[3][64];               // per component, natural order
+    unsigned char tab_dc[6], tab_ac[6];     // table index (0..3) of block k of an MCU: Y Y Y Y Cb Cr
+    unsigned char pad[4];
+};
+
+struct DecState {
+    unsigned int scan_end;                  // file offset of the first marker after the scan header (atomicMin)
+    unsigned int total_bytes;               // unstuffed entropy-coded bytes
+    unsigned int active[DEC_ROUNDS];        // subsequences re-decoded in round r
+    unsigned int end_bit;                   // bit position at which the last block of the image ended
+    unsigned int blocks_found;              // blocks the whole stream holds
+    int error;                              // != 0: not decodable here
+    int pad;
+};
+
+struct DecParams {
+    const unsigned char *file;              // the file in HBM
+    unsigned int file_len, scan_off;
+    unsigned int *chunk_drop;               // [nchunks + 1] stuffed zeros per chunk, then their exclusive prefix
+    unsigned char *bits;                    // unstuffed entropy-coded bytes (+ 64 zero bytes)
+    unsigned long long *rec;                // [nsub_max] one record per subsequence (dec_rec)
+    unsigned int sub_bits;                  // bits per subsequence
+    unsigned int *blk_base;                 // [nsub_max] blocks in front of each subsequence
+    int *mcu_pref;                          // [mcus][3] DC differences in front of each MCU inside its CTA of k_dec_dc_local
+    int *cta_pref;                          // [ceil(mcus / DEC_DC_THREADS)][3] ... and in front of that CTA
+    int16_t *coef;                          // [nblocks][64] natural order
+    unsigned char *planes;                  // Y [mcu_rows * 16][mcu_cols * 16], then Cb, Cr [mcu_rows * 8][mcu_cols * 8]
+    unsigned char *rgb;                     // decoded raster
+    int rgb_pitch, bgr;
+    int w, h, mcu_cols, mcu_rows;
+    unsigned int nblocks;
+    unsigned int nsub_max;                  // subsequences the file could hold at most
+    const DecTables *tab;
+    DecState *st;
+};
+
+// ---- entropy-coded segment: stuffed zeros out, first marker found ----------------------------------------
+__global__ void __launch_bounds__(256) k_dec_scan(const DecParams p)
+{
+    __shared__ unsigned int s_cnt;
+    if (threadIdx.x == 0) s_cnt = 0;
+    __syncthreads();
+    const unsigned int base = p.scan_off + blockIdx.x * DEC_CHUNK + threadIdx.x * 16;
+    unsigned int drops = 0;
+    if (base < p.file_len) {
+        unsigned int prev = base > 0 ? p.file[base - 1] : 0;
+        const unsigned int n = min(16u, p.file_len - base);
+        for (unsigned int i = 0; i < n; i++) {
+            const unsigned int b = p.file[base + i];
+            if (prev == 0xFFu && base + i > p.scan_off) {
+                if (b == 0u) drops++;
+                else if (b != 0xFFu) atomicMin(&p.st->scan_end, base + i - 1);      // a marker: the scan ends here
+            }
+            prev = b;
+        }
+    }
+    drops = __reduce_add_sync(0xffffffffu, drops);
+    if ((threadIdx.x & 31) == 0 && drops) atomicAdd(&s_cnt, drops);
+    __syncthreads();
+    if (threadIdx.x == 0) p.chunk_drop[blockIdx.x] = s_cnt;
+}
+
+__global__ void __launch_bounds__(1024) k_dec_offsets(const DecParams p, int nchunks)
+{
+    __shared__ unsigned int s_part[1024];
+    const int tid = threadIdx.x;
+    const int per = (nchunks + 1023) / 1024;
+    const int i0 = min(nchunks, tid * per), i1 = min(nchunks, i0 + per);
+    unsigned int mine = 0;
+    for (int i = i0; i < i1; i++) mine += p.chunk_drop[i];
+    s_part[tid] = mine;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        const unsigned int t = tid >= o ? s_part[tid - o] : 0u;
+        __syncthreads();
+        s_part[tid] += t;
+        __syncthreads();
+    }
+    unsigned int run = s_part[tid] - mine;
+    for (int i = i0; i < i1; i++) { const unsigned int c = p.chunk_drop[i]; p.chunk_drop[i] = run; run += c; }
+}
+
+__global__ void __launch_bounds__(256) k_dec_unstuff(const DecParams p)
+{
+    __shared__ unsigned int s_warp[8];
+    const unsigned int end = min(p.st->scan_end, p.file_len);
+    const unsigned int chunk0 = p.scan_off + blockIdx.x * DEC_CHUNK;
+    if (chunk0 >= end) return;
+    const unsigned int base = chunk0 + threadIdx.x * 16;
+    unsigned int keep = 0, bytes[16];
+    unsigned int n = 0;
+    if (base < end) {
+        n = min(16u, end - base);
+        unsigned int prev = base > p.scan_off ? p.file[base - 1] : 0;
+        for (unsigned int i = 0; i < n; i++) {
+            const unsigned int b = p.file[base + i];
+            if (!(prev == 0xFFu && b == 0u && base + i > p.scan_off)) bytes[keep++] = b;
+            prev = b;
+        }
+    }
+    // exclusive prefix of keep over the CTA
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned int incl = keep;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    unsigned int off = incl - keep;
+    for (int w = 0; w < warp; w++) off += s_warp[w];
+    const unsigned int out0 = (chunk0 - p.scan_off) - p.chunk_drop[blockIdx.x] + off;
+    for (unsigned int i = 0; i < keep; i++) p.bits[out0 + i] = (unsigned char)bytes[i];
+    if (n && base + n == end) {                                  // the thread that holds the last byte of the scan
+        const unsigned int total = out0 + keep;
+        p.st->total_bytes = total;
+        for (unsigned int i = 0; i < 64; i++) p.bits[total + i] = 0;
+    }
+}
+
+// ---- Huffman decode of one subsequence ----------------------------------------------------------------
+// Per subsequence ONE 64-bit record, written whole (atomicMin), so that entry state, exit state and block count
+// always belong to the same decode:
+//   [63:59] DEC_ROUNDS - 1 - round   [58:41] owner = the thread that wrote it     (priority: later rounds win,
+//   [40:26] entry state              [25:11] exit state      [10:0] blocks completed    inside a round the leftmost)
+// A state is 15 bits: bit offset past the subsequence's nominal start / end (6 bits; a symbol overshoots by < 32)
+// and bz = block-of-MCU * 64 + zigzag index (9 bits).
+constexpr unsigned long long DEC_REC_NONE = ~0ull;
+constexpr unsigned int DEC_STATE_NONE = 0x7fffu;
+
+__device__ __forceinline__ unsigned long long dec_rec(int round, unsigned int owner, unsigned int entry, unsigned int exit_,
+                                                      unsigned int nblk)
+{
+    return ((unsigned long long)(unsigned int)(DEC_ROUNDS - 1 - round) << 59) | ((unsigned long long)(owner & 0x3ffffu) << 41) |
+           ((unsigned long long)entry << 26) | ((unsigned long long)exit_ << 11) | (unsigned long long)(nblk & 0x7ffu);
+}
+__device__ __forceinline__ unsigned int dec_rec_entry(unsigned long long r) { return (unsigned int)(r >> 26) & 0x7fffu; }
+__device__ __forceinline__ unsigned int dec_rec_exit(unsigned long long r) { return (unsigned int)(r >> 11) & 0x7fffu; }
+__device__ __forceinline__ unsigned int dec_rec_nblk(unsigned long long r) { return (unsigned int)r & 0x7ffu; }
+
+// Bit reader: a 64-bit window whose top bit is stream bit `pos`; `have` valid bits.  One 32-bit word (big-endian
+// byte order in memory) is pulled in through the read-only path whenever fewer than 32 bits are left, so a symbol
+// (code <= 16 bits + value <= 15 bits) always sits in the top 32 bits.
+struct DecBits {
+    const unsigned int *words;
+    unsigned long long win;
+    unsigned int pos, have, next;          // next = index of the word that enters the window next
+
+    __device__ __forceinline__ void open(const unsigned char *bits, unsigned int pbit)
+    {
+        words = reinterpret_cast<const unsigned int *>(bits);
+        pos = pbit;
+        next = pbit >> 5;
+        const unsigned int a = __byte_perm(__ldg(words + next), 0, 0x0123), b = __byte_perm(__ldg(words + next + 1), 0, 0x0123);
+        next += 2;
+        win = (((unsigned long long)a << 32) | b) << (pbit & 31u);
+        have = 64u - (pbit & 31u);
+    }
+    __device__ __forceinline__ unsigned int peek() const { return (unsigned int)(win >> 32); }
+    __device__ __forceinline__ void skip(unsigned int n)
+    {
+        win <<= n;
+        pos += n;
+        have -= n;
+        if (have < 32u) {
+            const unsigned int w = __byte_perm(__ldg(words + next), 0, 0x0123);
+            next++;
+            win |= (unsigned long long)w << (32u - have);
+            have += 32u;
+        }
+    }
+};
+
+__constant__ unsigned char c_dec_zz[64] = {
+    0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28,
+    35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
+
+struct DecSmem {
+    unsigned short lut[4][1 << DEC_LUT_BITS];
+    int maxcode[4][18];
+    int valoff[4][18];
+    unsigned char huffval[4][256];
+    unsigned char tab_dc[8], tab_ac[8];
+    unsigned char zz[64];
+};
+
+__device__ __forceinline__ void dec_load_tables(DecSmem &s, const DecTables *t)
+{
+    const unsigned int *src = reinterpret_cast<const unsigned int *>(t->lut);
+    unsigned int *dst = reinterpret_cast<unsigned int *>(s.lut);
+    for (int i = threadIdx.x; i < 4 * (1 << DEC_LUT_BITS) / 2; i += blockDim.x) dst[i] = src[i];
+    for (int i = threadIdx.x; i < 4 * 18; i += blockDim.x) {
+        (&s.maxcode[0][0])[i] = (&t->maxcode[0][0])[i];
+        (&s.valoff[0][0])[i] = (&t->valoff[0][0])[i];
+    }
+    for (int i = threadIdx.x; i < 4 * 256; i += blockDim.x) (&s.huffval[0][0])[i] = (&t->huffval[0][0])[i];
+    if (threadIdx.x < 6) { s.tab_dc[threadIdx.x] = t->tab_dc[threadIdx.x]; s.tab_ac[threadIdx.x] = t->tab_ac[threadIdx.x]; }
+    if (threadIdx.x < 64) s.zz[threadIdx.x] = c_dec_zz[threadIdx.x];
+    __syncthreads();
+}
+
+// one Huffman symbol of table tb at the head of `peek` (jdhuff.c jpeg_huff_decode): -> symbol, code length in len
+__device__ __forceinline__ unsigned int dec_symbol(const DecSmem &s, int tb, unsigned int peek, unsigned int &len)
+{
+    const unsigned int e = s.lut[tb][peek >> (32 - DEC_LUT_BITS)];
+    if (e) { len = e >> 8; return e & 0xffu; }
+    for (int l = DEC_LUT_BITS + 1; l <= 16; l++) {
+        const int code = (int)(peek >> (32 - l));
+        if (code <= s.maxcode[tb][l]) { len = (unsigned int)l; return s.huffval[tb][(code + s.valoff[tb][l]) & 255]; }
+    }
+    len = 16;                                                   // not a code: corrupt data, decoded as a zero like IJG
+    return 0;
+}
+
+// Decodes from state (pbit, bz = block-of-MCU * 64 + zigzag index) until a symbol starts at or after end_bit.
+// WRITE: coefficients go to coef (block index blk counts from the caller's base; blocks >= nblocks are dropped).
+template <bool WRITE>
+__device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *bits, unsigned int &pbit, unsigned int &bz,
+                                        unsigned int &nblk, unsigned int end_bit, int16_t *coef, unsigned int blk,
+                                        unsigned int nblocks, DecState *st)
+{
+    unsigned int b = bz >> 6, z = bz & 63u;
+    DecBits br;
+    br.open(bits, pbit);
+    while (br.pos < end_bit) {
+        if (WRITE && blk >= nblocks) break;
+        const unsigned int peek = br.peek();
+        unsigned int len;
+        const bool dc = z == 0;
+        const unsigned int rs = dec_symbol(s, dc ? s.tab_dc[b] : s.tab_ac[b], peek, len);
+        const unsigned int sz = rs & 15u, r = dc ? 0u : rs >> 4;
+        // the value bits follow the code inside the same 32-bit window (jdhuff.c HUFF_EXTEND)
+        int v = 0;
+        if (WRITE && sz) {
+            const unsigned int rb = (peek << len) >> (32u - sz);
+            v = rb < (1u << (sz - 1)) ? (int)rb - (int)(1u << sz) + 1 : (int)rb;
+        }
+        br.skip(len + sz);
+        if (dc) {
+            if (WRITE) coef[(size_t)blk * 64] = (int16_t)v;
+            z = 1;
+        } else if (sz) {
+            z += r;
+            if (WRITE && z < 64) coef[(size_t)blk * 64 + s.zz[z]] = (int16_t)v;
+            z++;
+        } else {
+            z = r == 15u ? z + 16 : 64;                         // ZRL or end of block
+        }
+        if (z >= 64) {                                          // block complete
+            z = 0;
+            b = b == 5 ? 0 : b + 1;
+            nblk++;
+            blk++;
+            if (WRITE && blk == nblocks) st->end_bit = br.pos;
+        }
+    }
+    pbit = br.pos;
+    bz = (b << 6) | z;
+}
+
+// One synchronisation round.  A thread whose entry state (the exit state of its left neighbour; thread 0: the
+// start of the scan) differs from the one its record was decoded from decodes its subsequence again and carries on
+// into the following ones -- at most DEC_CARRY of them per round -- until it meets a record that was decoded from
+// exactly the state it arrives with: from there on the records are already what this thread would write.
+__global__ void __launch_bounds__(128) k_dec_sync(const DecParams p, int round)
+{
+    __shared__ DecSmem s;
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned int total_bits = p.st->total_bytes * 8u;
+    const unsigned int S = p.sub_bits;
+    const unsigned int nsub = min(p.nsub_max, (total_bits + S - 1) / S);
+    unsigned int entry = DEC_STATE_NONE;
+    bool active = false;
+    if (i < nsub) {
+        if (i == 0) entry = 0;                                   // offset 0, first block of an MCU, DC next
+        else if (round == 0) entry = 0;                          // the guess
+        else entry = dec_rec_exit(p.rec[i - 1]);
+        active = round == 0 || entry != dec_rec_entry(p.rec[i]);
+    }
+    if (!__syncthreads_or(active ? 1 : 0)) return;
+    dec_load_tables(s, p.tab);
+    if (!active) return;
+    if (round > 0) p.st->active[round] = 1;
+    for (unsigned int k = i; k < nsub && k < i + DEC_CARRY; k++) {
+        if (k > i && dec_rec_entry(p.rec[k]) == entry) break;   // joined what is already recorded
+        const unsigned int start = k * S, end = min(start + S, total_bits);
+        unsigned int pbit = start + (entry >> 9), bz = entry & 0x1ffu, nblk = 0;
+        dec_run<false>(s, p.bits, pbit, bz, nblk, end, nullptr, 0, 0, nullptr);
+        const unsigned int exit_ = (min(pbit - end, 63u) << 9) | bz;
+        atomicMin(&p.rec[k], dec_rec(round, i, entry, exit_, nblk));
+        entry = exit_;
+    }
+}
+
+// blocks in front of every subsequence (exclusive prefix of the per-subsequence block counts), one CTA
+__global__ void __launch_bounds__(1024) k_dec_blocks(const DecParams p)
+{
+    __shared__ unsigned int s_part[1024];
+    const int tid = threadIdx.x;
+    const unsigned int total_bits = p.st->total_bytes * 8u;
+    const unsigned int nsub = min(p.nsub_max, (total_bits + p.sub_bits - 1) / p.sub_bits);
+    const unsigned int per = (nsub + 1023) / 1024;
+    const unsigned int i0 = min(nsub, tid * per), i1 = min(nsub, i0 + per);
+    unsigned int mine = 0;
+    for (unsigned int i = i0; i < i1; i++) mine += dec_rec_nblk(p.rec[i]);
+    s_part[tid] = mine;
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        const unsigned int t = tid >= o ? s_part[tid - o] : 0u;
+        __syncthreads();
+        s_part[tid] += t;
+        __syncthreads();
+    }
+    unsigned int run = s_part[tid] - mine;
+    for (unsigned int i = i0; i < i1; i++) { p.blk_base[i] = run; run += dec_rec_nblk(p.rec[i]); }
+    if (tid == 1023) p.st->blocks_found = s_part[1023];
+}
+
+__global__ void __launch_bounds__(128) k_dec_write(const DecParams p)
+{
+    __shared__ DecSmem s;
+    dec_load_tables(s, p.tab);
+    const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const unsigned int total_bits = p.st->total_bytes * 8u;
+    const unsigned int S = p.sub_bits;
+    const unsigned int start = i * S;
+    if (i >= p.nsub_max || start >= total_bits) return;
+    const unsigned int entry = dec_rec_entry(p.rec[i]);
+    unsigned int pbit = start + (entry >> 9), bz = entry & 0x1ffu, nblk = 0;
+    const unsigned int end = min(start + S, total_bits);
+    dec_run<true>(s, p.bits, pbit, bz, nblk, end, p.coef, p.blk_base[i], p.nblocks, p.st);
+}
+
+// ---- DC differences -> DC values (jdhuff.c last_dc_val): per component a prefix over the MCUs --------------
+// k_dec_dc_local: one thread per MCU, the sums of its DC differences (Y: four blocks) scanned inside the CTA;
+// k_dec_dc_cta: the CTA totals scanned by one CTA; the IDCT kernel adds CTA prefix + MCU prefix + the
+// differences of the blocks in front of its own inside the MCU.
+constexpr int DEC_DC_THREADS = 256;
+
+__global__ void __launch_bounds__(DEC_DC_THREADS) k_dec_dc_local(const DecParams p)
+{
+    __shared__ int s_w[3][DEC_DC_THREADS / 32];
+    const unsigned int nm = p.nblocks / 6;
+    const unsigned int m = blockIdx.x * DEC_DC_THREADS + threadIdx.x;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int v[3] = {0, 0, 0};
+    if (m < nm) {
+        const int16_t *c = p.coef + (size_t)m * 6 * 64;
+        v[0] = c[0] + c[64] + c[128] + c[192];
+        v[1] = c[256];
+        v[2] = c[320];
+    }
+    int incl[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        int x = v[k];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int t = __shfl_up_sync(0xffffffffu, x, o);
+            if (lane >= o) x += t;
+        }
+        incl[k] = x;
+        if (lane == 31) s_w[k][warp] = x;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+        int base = 0, tot = 0;
+        for (int w = 0; w < DEC_DC_THREADS / 32; w++) { if (w < warp) base += s_w[k][w]; tot += s_w[k][w]; }
+        if (m < nm) p.mcu_pref[(size_t)m * 3 + k] = base + incl[k] - v[k];
+        if (threadIdx.x == 0) p.cta_pref[(size_t)blockIdx.x * 3 + k] = tot;
+    }
+}
+
+__global__ void __launch_bounds__(1024) k_dec_dc_cta(const DecParams p, int nctas)
+{
+    __shared__ int s_part[3][1024];
+    const int tid = threadIdx.x;
+    const int per = (nctas + 1023) / 1024;
+    const int i0 = min(nctas, tid * per), i1 = min(nctas, i0 + per);
+    int mine[3] = {0, 0, 0};
+    for (int i = i0; i < i1; i++)
+        for (int k = 0; k < 3; k++) mine[k] += p.cta_pref[(size_t)i * 3 + k];
+    for (int k = 0; k < 3; k++) s_part[k][tid] = mine[k];
+    __syncthreads();
+    for (int o = 1; o < 1024; o <<= 1) {
+        int t[3] = {0, 0, 0};
+        if (tid >= o) for (int k = 0; k < 3; k++) t[k] = s_part[k][tid - o];
+        __syncthreads();
+        for (int k = 0; k < 3; k++) s_part[k][tid] += t[k];
+        __syncthreads();
+    }
+    int run[3];
+    for (int k = 0; k < 3; k++) run[k] = s_part[k][tid] - mine[k];
+    for (int i = i0; i < i1; i++)
+        for (int k = 0; k < 3; k++) { const int c = p.cta_pref[(size_t)i * 3 + k]; p.cta_pref[(size_t)i * 3 + k] = run[k]; run[k] += c; }
+}
+
+// ---- jidctint.c jpeg_idct_islow ----------------------------------------------------------------------
+__device__ __forceinline__ void dec_idct_1d(const int (&in)[8], int (&out)[8], int shift)
+{
+    int z1, z2, z3, z4, z5, tmp0, tmp1, tmp2, tmp3, tmp10, tmp11, tmp12, tmp13;
+    z2 = in[2]; z3 = in[6];
+    z1 = (z2 + z3) * 4433;
+    tmp2 = z1 + z3 * (-15137);
+    tmp3 = z1 + z2 * 6270;
+    z2 = in[0]; z3 = in[4];
+    tmp0 = (z2 + z3) << 13;
+    tmp1 = (z2 - z3) << 13;
+    tmp10 = tmp0 + tmp3; tmp13 = tmp0 - tmp3; tmp11 = tmp1 + tmp2; tmp12 = tmp1 - tmp2;
+    tmp0 = in[7]; tmp1 = in[5]; tmp2 = in[3]; tmp3 = in[1];
+    z1 = tmp0 + tmp3; z2 = tmp1 + tmp2; z3 = tmp0 + tmp2; z4 = tmp1 + tmp3;
+    z5 = (z3 + z4) * 9633;
+    tmp0 *= 2446; tmp1 *= 16819; tmp2 *= 25172; tmp3 *= 12299;
+    z1 *= -7373; z2 *= -20995; z3 *= -16069; z4 *= -3196;
+    z3 += z5; z4 += z5;
+    tmp0 += z1 + z3; tmp1 += z2 + z4; tmp2 += z2 + z3; tmp3 += z1 + z4;
+    const int rnd = 1 << (shift - 1);
+    out[0] = (tmp10 + tmp3 + rnd) >> shift; out[7] = (tmp10 - tmp3 + rnd) >> shift;
+    out[1] = (tmp11 + tmp2 + rnd) >> shift; out[6] = (tmp11 - tmp2 + rnd) >> shift;
+    out[2] = (tmp12 + tmp1 + rnd) >> shift; out[5] = (tmp12 - tmp1 + rnd) >> shift;
+    out[3] = (tmp13 + tmp0 + rnd) >> shift; out[4] = (tmp13 - tmp0 + rnd) >> shift;
+}
+
+__device__ __forceinline__ unsigned int dec_range_limit(int x)     // jdmaster.c range-limit table at index x & RANGE_MASK
+{
+    const int v = x & 1023;
+    return (unsigned int)(v < 128 ? v + 128 : (v < 512 ? 255 : (v < 896 ? 0 : v - 896)));
+}
+
+// one thread = one block: 64 coefficients (natural order) -> 8 x 8 samples of the block's plane
+__global__ void __launch_bounds__(128) k_dec_idct(const DecParams p)
+{
+    __shared__ short s_qt[3][64];
+    for (int i = threadIdx.x; i < 192; i += blockDim.x) (&s_qt[0][0])[i] = (short)(&p.tab->qt[0][0])[i];
+    __syncthreads();
+    const unsigned int blk = blockIdx.x * blockDim.x + threadIdx.x;
+    if (blk >= p.nblocks) return;
+    const unsigned int m = blk / 6, k = blk - m * 6;
+    const int mx = (int)(m % (unsigned int)p.mcu_cols), my = (int)(m / (unsigned int)p.mcu_cols);
+    const int comp = k < 4 ? 0 : (int)k - 3;
+    const int yw = p.mcu_cols * 16, cw = p.mcu_cols * 8;
+    unsigned char *dst;
+    int pitch;
+    if (k < 4) {
+        dst = p.planes + (size_t)(my * 16 + (int)(k >> 1) * 8) * yw + mx * 16 + (int)(k & 1) * 8;
+        pitch = yw;
+    } else {
+        const size_t ysz = (size_t)yw * p.mcu_rows * 16, csz = (size_t)cw * p.mcu_rows * 8;
+        dst = p.planes + ysz + (k == 5 ? csz : 0) + (size_t)(my * 8) * cw + mx * 8;
+        pitch = cw;
+    }
+    const uint4 *src = reinterpret_cast<const uint4 *>(p.coef + (size_t)blk * 64);
+    int ws[64];
+    // columns first (pass 1), on dequantised coefficients; rows of the input are 8 shorts = one uint4
+    short cf[64];
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        const uint4 v = src[r];
+        const unsigned int w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            cf[8 * r + 2 * j] = (short)(w4[j] & 0xffffu);
+            cf[8 * r + 2 * j + 1] = (short)(w4[j] >> 16);
+        }
+    }
+    {   // DC value = differences of every earlier block of the component + its own (stored back as the JCOEF short)
+        int dc = p.cta_pref[(size_t)(m / DEC_DC_THREADS) * 3 + comp] + p.mcu_pref[(size_t)m * 3 + comp];
+        const int16_t *mc = p.coef + (size_t)m * 6 * 64;
+        if (k < 4) { for (unsigned int j = 0; j <= k; j++) dc += mc[64 * j]; }
+        else dc += mc[64 * k];
+        cf[0] = (short)dc;
+    }
+#pragma unroll
+    for (int c = 0; c < 8; c++) {
+        int in[8], o[8];
+#pragma unroll
+        for (int r = 0; r < 8; r++) in[r] = (int)cf[8 * r + c] * (int)s_qt[comp][8 * r + c];
+        dec_idct_1d(in, o, 11);
+#pragma unroll
+        for (int r = 0; r < 8; r++) ws[8 * r + c] = o[r];
+    }
+#pragma unroll
+    for (int r = 0; r < 8; r++) {
+        int in[8], o[8];
+#pragma unroll
+        for (int c = 0; c < 8; c++) in[c] = ws[8 * r + c];
+        dec_idct_1d(in, o, 18);
+        uint2 out;
+        out.x = dec_range_limit(o[0]) | (dec_range_limit(o[1]) << 8) | (dec_range_limit(o[2]) << 16) | (dec_range_limit(o[3]) << 24);
+        out.y = dec_range_limit(o[4]) | (dec_range_limit(o[5]) << 8) | (dec_range_limit(o[6]) << 16) | (dec_range_limit(o[7]) << 24);
+        *reinterpret_cast<uint2 *>(dst + (size_t)r * pitch) = out;
+    }
+}
+
+// ---- jdsample.c h2v2_fancy_upsample + jdcolor.c ycc_rgb_convert: one thread = 8 pixels of a row ----------
+__global__ void __launch_bounds__(256) k_dec_color(const DecParams p)
+{
+    const int x0 = (blockIdx.x * 32 + (threadIdx.x & 31)) * 8;
+    const int y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x0 >= p.w || y >= p.h) return;
+    const int yw = p.mcu_cols * 16, cw = p.mcu_cols * 8;
+    const size_t ysz = (size_t)yw * p.mcu_rows * 16, csz = (size_t)cw * p.mcu_rows * 8;
+    const unsigned char *Y = p.planes + (size_t)y * yw + x0;
+    const int dsw = (p.w + 1) >> 1, dsh = (p.h + 1) >> 1;
+    const int cy = y >> 1;
+    int cn = (y & 1) ? cy + 1 : cy - 1;                      // jdmainct.c context rows: clamped to the real rows
+    cn = max(0, min(cn, dsh - 1));
+    const bool fancy = dsw > 2;
+    const int cx0 = x0 >> 1;
+    int cb[8], cr[8];
+#pragma unroll
+    for (int pl = 0; pl < 2; pl++) {
+        const unsigned char *P = p.planes + ysz + (pl ? csz : 0);
+        const unsigned char *r0 = P + (size_t)cy * cw, *r1 = P + (size_t)cn * cw;
+        int *res = pl ? cr : cb;
+        if (!fancy) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) res[i] = r0[min(cx0 + (i >> 1), cw - 1)];
+        } else {
+            int sum[6];                                       // 3 * cur + near for columns cx0 - 1 .. cx0 + 4
+#pragma unroll
+            for (int j = 0; j < 6; j++) {
+                const int cx = min(max(cx0 - 1 + j, 0), cw - 1);
+                sum[j] = 3 * r0[cx] + r1[cx];
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int cx = cx0 + j, cur = sum[j + 1];
+                res[2 * j] = cx == 0 ? (cur * 4 + 8) >> 4 : (cur * 3 + sum[j] + 8) >> 4;
+                res[2 * j + 1] = cx == dsw - 1 ? (cur * 4 + 7) >> 4 : (cur * 3 + sum[j + 2] + 7) >> 4;
+            }
+        }
+    }
+    unsigned char px[24];
+    const uint2 yv = *reinterpret_cast<const uint2 *>(Y);
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const int yy = (int)(((i < 4 ? yv.x : yv.y) >> (8 * (i & 3))) & 0xffu);
+        const int cbx = cb[i] - 128, crx = cr[i] - 128;
+        int r = yy + ((91881 * crx + 32768) >> 16);
+        int b = yy + ((116130 * cbx + 32768) >> 16);
+        int g = yy + ((-22554 * cbx + 32768 - 46802 * crx) >> 16);
+        r = min(max(r, 0), 255); g = min(max(g, 0), 255); b = min(max(b, 0), 255);
+        px[3 * i] = (unsigned char)(p.bgr ? b : r); px[3 * i + 1] = (unsigned char)g; px[3 * i + 2] = (unsigned char)(p.bgr ? r : b);
+    }
+    unsigned char *o = p.rgb + (size_t)y * p.rgb_pitch + (size_t)x0 * 3;
+    if (x0 + 8 <= p.w) {
+        uint2 *o8 = reinterpret_cast<uint2 *>(o);
+#pragma unroll
+        for (int j = 0; j < 3; j++) {
+            uint2 v;
+            v.x = px[8 * j] | (px[8 * j + 1] << 8) | (px[8 * j + 2] << 16) | ((unsigned int)px[8 * j + 3] << 24);
+            v.y = px[8 * j + 4] | (px[8 * j + 5] << 8) | (px[8 * j + 6] << 16) | ((unsigned int)px[8 * j + 7] << 24);
+            o8[j] = v;
+        }
+    } else {
+        for (int i = 0; i < (p.w - x0) * 3; i++) o[i] = px[i];
+    }
+}
+
+}  // namespace icb

@@ -196,7 +196,9 @@ typedef enum {
     ICB_ITEM_JPG_FIT_IMAGE = 1,  /* resident image -> icb_submit_jpg_fit_image */
     ICB_ITEM_PNG_FIT = 2,        /* host pixels -> icb_submit_png_fit (resized pixels out) */
     ICB_ITEM_PNG_COMPRESS = 3,   /* host pixels -> icb_submit_png_compress (PNG file out)  */
-    ICB_ITEM_RESIZE_IMAGE = 4    /* resident image -> icb_submit_resize_image (dw, dh given; out may be NULL) */
+    ICB_ITEM_RESIZE_IMAGE = 4,   /* resident image -> icb_submit_resize_image (dw, dh given; out may be NULL) */
+    ICB_ITEM_JPG_FILE_FIT = 5    /* JPEG file bytes -> icb_submit_jpg_file_fit: px = the file, pitch = its length in
+                                    bytes; dw, dh receive the dimensions of the decoded (subsampled) raster */
 } icb_item_kind;
 
 typedef struct {
@@ -235,6 +237,29 @@ int icb_png_compress(icb_handle *h, const uint8_t *src, int w, int hgt, int pitc
 int icb_submit_png_compress(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, int fmt,
                             int min_w, int min_h, uint8_t *out, size_t out_cap, int *dw, int *dh,
                             int64_t *ticket);
+
+/* SURVEY 8 f2 (input staging) -- core/ImageCompression.java:119-155 decodeImageWithSubsampling on the GPU:
+ * reader.read(0, param) of the ImageIO JPEG reader (libjavajpeg = IJG 6b: sequential Huffman decode, islow inverse
+ * DCT, fancy h2v2 upsampling, YCbCr -> RGB) for baseline 8-bit YCbCr 4:2:0 files with one scan and no restart
+ * interval, so that the caller uploads the FILE instead of the decoded raster (12 MP: ~6 MB instead of 36 MB over
+ * PCIe).  ICB_ERR_UNSUPPORTED = any other kind of JPEG (progressive, 4:4:4 / 4:2:2, gray, CMYK, restart markers,
+ * 12 bit) or a stream the parallel decoder did not resolve: the caller decodes on the host as before and calls the
+ * pixel entry points.  ICB_ERR_INVALID = not a JPEG / truncated.
+ *   icb_jpg_file_info   header parse on the host (:128-129 reader.getWidth / getHeight), no device needed
+ *   icb_jpg_decode      the decoded raster (RGB8 or BGR8 = TYPE_3BYTE_BGR) back on the host: test / parity entry
+ *   icb_jpg_file_fit    :119-155 + core/ImageCompressionJpg.java:77-122 in one call: decode, the source-subsampling
+ *                       rule of :140-153 (icb_subsample_factor), then exactly icb_jpg_fit on the pixels, which never
+ *                       leave the GPU.  *w, *hgt = dimensions of the raster the seam saw (for CacheTools.createKey). */
+int icb_jpg_file_info(const uint8_t *file, size_t n, int *w, int *hgt);
+int icb_jpg_decode(icb_handle *h, const uint8_t *file, size_t n, int fmt, uint8_t *dst, size_t dst_cap, int dpitch,
+                   int *w, int *hgt);
+int icb_jpg_file_fit(icb_handle *h, const uint8_t *file, size_t n, float init_q, int64_t target,
+                     int has_cached, float cached_q, double cached_scale,
+                     uint8_t *out, size_t out_cap, size_t *out_len,
+                     float *best_q, double *scale, int *used_cache, int *w, int *hgt);
+int icb_submit_jpg_file_fit(icb_handle *h, const uint8_t *file, size_t n, float init_q, int64_t target,
+                            int has_cached, float cached_q, double cached_scale,
+                            uint8_t *out, size_t out_cap, int *w, int *hgt, int64_t *ticket);
 
 /* No counterpart in the reference: added for callers that cannot
  * call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The PNG
