@@ -2153,7 +2153,9 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     k_dec_offsets<<<1, 1024, 0, st>>>(dp, nchunks);
     k_dec_unstuff<<<nchunks, 256, 0, st>>>(dp);
     const unsigned int sgrid = (nsub_max + 127) / 128;
-    for (int r = 0; r < DEC_ROUNDS; r++) k_dec_sync<<<sgrid, 128, 0, st>>>(dp, r);
+    // rounds queued: DEC_ROUNDS unless ICB_DEC_ROUNDS asks for fewer (A/B runs); the verdict reads the last one queued
+    static const int nrounds = [] { const char *e = getenv("ICB_DEC_ROUNDS"); const int v = e ? atoi(e) : DEC_ROUNDS; return v >= 2 && v <= DEC_ROUNDS ? v : DEC_ROUNDS; }();
+    for (int r = 0; r < nrounds; r++) k_dec_sync<<<sgrid, 128, 0, st>>>(dp, r == 0 ? 0 : DEC_ROUNDS - nrounds + r);
     k_dec_blocks<<<1, 1024, 0, st>>>(dp);
     k_dec_write<<<sgrid, 128, 0, st>>>(dp);
     k_dec_dc_local<<<(unsigned int)ndc, DEC_DC_THREADS, 0, st>>>(dp);

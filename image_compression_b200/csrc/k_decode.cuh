@@ -42,10 +42,13 @@ constexpr int DEC_CHUNK = 4096;             // file bytes per CTA of the scan / 
 constexpr int DEC_LUT_BITS = 10;
 
 // Huffman decode tables of one file, built on the host (api.cu build_dec_tables): per table t = class * 2 + id
-// (0, 1 DC; 2, 3 AC) a look-up by the next DEC_LUT_BITS bits -> (length << 8) | symbol, 0 = longer than the
-// look-up; and jdhuff.c's maxcode / valoffset / huffval for the long codes.
+// (0, 1 DC; 2, 3 AC) a look-up by the next DEC_LUT_BITS bits -> (length << 8) | symbol; 0xF000 | k = a longer code whose
+// next six bits index second-level table k; 0 = not in either (more than DEC_LUT2 long prefixes, or no such code):
+// jdhuff.c's maxcode / valoffset / huffval loop settles those.
+constexpr int DEC_LUT2 = 16;                // second-level tables per Huffman table (distinct 10-bit prefixes of long codes)
 struct DecTables {
     unsigned short lut[4][1 << DEC_LUT_BITS];
+    unsigned short lut2[4][DEC_LUT2][64];   // codes of 11..16 bits: lut = 0xF000 | index, then the next six bits -> (length << 8) | symbol
     int maxcode[4][18];
     int valoff[4][18];
     unsigned char huffval[4][256];
@@ -229,6 +232,7 @@ __constant__ unsigned char c_dec_zz[64] = {
 
 struct DecSmem {
     unsigned short lut[4][1 << DEC_LUT_BITS];
+    unsigned short lut2[4][DEC_LUT2][64];
     int maxcode[4][18];
     int valoff[4][18];
     unsigned char huffval[4][256];
@@ -241,6 +245,11 @@ __device__ __forceinline__ void dec_load_tables(DecSmem &s, const DecTables *t)
     const unsigned int *src = reinterpret_cast<const unsigned int *>(t->lut);
     unsigned int *dst = reinterpret_cast<unsigned int *>(s.lut);
     for (int i = threadIdx.x; i < 4 * (1 << DEC_LUT_BITS) / 2; i += blockDim.x) dst[i] = src[i];
+    {
+        const unsigned int *src2 = reinterpret_cast<const unsigned int *>(t->lut2);
+        unsigned int *dst2 = reinterpret_cast<unsigned int *>(s.lut2);
+        for (int i = threadIdx.x; i < 4 * DEC_LUT2 * 64 / 2; i += blockDim.x) dst2[i] = src2[i];
+    }
     for (int i = threadIdx.x; i < 4 * 18; i += blockDim.x) {
         (&s.maxcode[0][0])[i] = (&t->maxcode[0][0])[i];
         (&s.valoff[0][0])[i] = (&t->valoff[0][0])[i];
@@ -254,7 +263,8 @@ __device__ __forceinline__ void dec_load_tables(DecSmem &s, const DecTables *t)
 // one Huffman symbol of table tb at the head of `peek` (jdhuff.c jpeg_huff_decode): -> symbol, code length in len
 __device__ __forceinline__ unsigned int dec_symbol(const DecSmem &s, int tb, unsigned int peek, unsigned int &len)
 {
-    const unsigned int e = s.lut[tb][peek >> (32 - DEC_LUT_BITS)];
+    unsigned int e = s.lut[tb][peek >> (32 - DEC_LUT_BITS)];
+    if (e >= 0xF000u) e = s.lut2[tb][e & 0xffu][(peek >> (32 - DEC_LUT_BITS - 6)) & 63u];
     if (e) { len = e >> 8; return e & 0xffu; }
     for (int l = DEC_LUT_BITS + 1; l <= 16; l++) {
         const int code = (int)(peek >> (32 - l));

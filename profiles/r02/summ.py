@@ -14,6 +14,10 @@ for src in (sys.argv[1:] or ["-"]):
             1e3 * re_.get("ms_per_launch", 0), re_.get("ms_per_launch_in_step") and round(1e3 * re_["ms_per_launch_in_step"], 2),
             re_.get("ms_per_launch_effective") and round(1e3 * re_["ms_per_launch_effective"], 2),
             d.get("in_step", {}).get("concurrency") and round(d["in_step"]["concurrency"], 2), d.get("gpu_launches")))
+        if d.get("e2e_pixels"):
+            print("   e2e input: %s" % d["e2e"].get("input", "")[:110])
+            print("   e2e_pixels: %.0f img/s | e2e_file_error: %s | e2e parity: %s" % (
+                d["e2e_pixels"]["images_per_s"], d.get("e2e_file_error"), str(d["e2e"].get("parity_check"))[:150]))
         for k, v in (d.get("other_configs") or {}).items():
             if "error" in v:
                 print("   %s ERROR %s" % (k, v["error"][:300]))
