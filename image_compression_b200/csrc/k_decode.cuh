@@ -35,9 +35,9 @@
 
 namespace icb {
 
-constexpr int DEC_SUB_BITS = 2048;          // bits per subsequence (a multiple of 32); ICB_DEC_SUB overrides per process
+constexpr int DEC_SUB_BITS = 4096;          // bits per subsequence (a multiple of 32); ICB_DEC_SUB overrides per process
 constexpr int DEC_ROUNDS = 10;              // synchronisation rounds queued per job (<= 32: five bits of the record)
-constexpr int DEC_CARRY = 8;                // subsequences a thread carries on through per round
+constexpr int DEC_CARRY = 4;                // subsequences a thread carries on through per round
 constexpr int DEC_CHUNK = 4096;             // file bytes per CTA of the scan / unstuff kernels
 constexpr int DEC_LUT_BITS = 10;
 
@@ -74,6 +74,7 @@ struct DecParams {
     unsigned char *bits;                    // unstuffed entropy-coded bytes (+ 64 zero bytes)
     unsigned long long *rec;                // [nsub_max] one record per subsequence (dec_rec)
     unsigned int sub_bits;                  // bits per subsequence
+    unsigned int carry;                     // subsequences a thread carries on through per round
     unsigned int *blk_base;                 // [nsub_max] blocks in front of each subsequence
     int *mcu_pref;                          // [mcus][3] DC differences in front of each MCU inside its CTA of k_dec_dc_local
     int *cta_pref;                          // [ceil(mcus / DEC_DC_THREADS)][3] ... and in front of that CTA
@@ -176,22 +177,23 @@ __global__ void __launch_bounds__(256) k_dec_unstuff(const DecParams p)
 // ---- Huffman decode of one subsequence ----------------------------------------------------------------
 // Per subsequence ONE 64-bit record, written whole (atomicMin), so that entry state, exit state and block count
 // always belong to the same decode:
-//   [63:59] DEC_ROUNDS - 1 - round   [58:41] owner = the thread that wrote it     (priority: later rounds win,
-//   [40:26] entry state              [25:11] exit state      [10:0] blocks completed    inside a round the leftmost)
+//   [63:59] DEC_ROUNDS - 1 - round   [58:42] owner = the thread that wrote it     (priority: later rounds win,
+//   [41:27] entry state              [26:12] exit state      [11:0] blocks completed    inside a round the leftmost)
 // A state is 15 bits: bit offset past the subsequence's nominal start / end (6 bits; a symbol overshoots by < 32)
-// and bz = block-of-MCU * 64 + zigzag index (9 bits).
+// and bz = block-of-MCU * 64 + zigzag index (9 bits).  12 bits of block count: a block takes at least 4 bits, so a
+// subsequence of up to 8192 bits; 17 bits of owner: up to 131 071 subsequences per scan.
 constexpr unsigned long long DEC_REC_NONE = ~0ull;
 constexpr unsigned int DEC_STATE_NONE = 0x7fffu;
 
 __device__ __forceinline__ unsigned long long dec_rec(int round, unsigned int owner, unsigned int entry, unsigned int exit_,
                                                       unsigned int nblk)
 {
-    return ((unsigned long long)(unsigned int)(DEC_ROUNDS - 1 - round) << 59) | ((unsigned long long)(owner & 0x3ffffu) << 41) |
-           ((unsigned long long)entry << 26) | ((unsigned long long)exit_ << 11) | (unsigned long long)(nblk & 0x7ffu);
+    return ((unsigned long long)(unsigned int)(DEC_ROUNDS - 1 - round) << 59) | ((unsigned long long)(owner & 0x1ffffu) << 42) |
+           ((unsigned long long)entry << 27) | ((unsigned long long)exit_ << 12) | (unsigned long long)(nblk & 0xfffu);
 }
-__device__ __forceinline__ unsigned int dec_rec_entry(unsigned long long r) { return (unsigned int)(r >> 26) & 0x7fffu; }
-__device__ __forceinline__ unsigned int dec_rec_exit(unsigned long long r) { return (unsigned int)(r >> 11) & 0x7fffu; }
-__device__ __forceinline__ unsigned int dec_rec_nblk(unsigned long long r) { return (unsigned int)r & 0x7ffu; }
+__device__ __forceinline__ unsigned int dec_rec_entry(unsigned long long r) { return (unsigned int)(r >> 27) & 0x7fffu; }
+__device__ __forceinline__ unsigned int dec_rec_exit(unsigned long long r) { return (unsigned int)(r >> 12) & 0x7fffu; }
+__device__ __forceinline__ unsigned int dec_rec_nblk(unsigned long long r) { return (unsigned int)r & 0xfffu; }
 
 // Bit reader: a 64-bit window whose top bit is stream bit `pos`; `have` valid bits.  One 32-bit word (big-endian
 // byte order in memory) is pulled in through the read-only path whenever fewer than 32 bits are left, so a symbol
@@ -343,7 +345,7 @@ __global__ void __launch_bounds__(128) k_dec_sync(const DecParams p, int round)
     dec_load_tables(s, p.tab);
     if (!active) return;
     if (round > 0) p.st->active[round] = 1;
-    for (unsigned int k = i; k < nsub && k < i + DEC_CARRY; k++) {
+    for (unsigned int k = i; k < nsub && k < i + p.carry; k++) {
         if (k > i && dec_rec_entry(p.rec[k]) == entry) break;   // joined what is already recorded
         const unsigned int start = k * S, end = min(start + S, total_bits);
         unsigned int pbit = start + (entry >> 9), bz = entry & 0x1ffu, nblk = 0;
