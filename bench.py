@@ -533,7 +533,7 @@ def leg_files(eng, pool, w, h, q, target, batch, args, dist, local, rank, local_
         bio = io.BytesIO()
         Image.fromarray(im).save(bio, "JPEG", quality=92, subsampling=2)
         files.append(np.frombuffer(bio.getvalue(), np.uint8))
-    fslots = max(args.slots, 16)                     # the decode kernels are latency bound: more jobs in flight
+    fslots = max(args.slots, 24)                     # the decode kernels are latency bound: more jobs in flight
     T = args.threads
     inflight = max(1, fslots // T)
     engf = pkg.Engine(devices=[local_dev], slots_per_gpu=fslots, max_w=w, max_h=h)

@@ -596,30 +596,29 @@ __global__ void __launch_bounds__(256) k_dec_color(const DecParams p)
             }
         }
     }
-    unsigned char px[24];
     const uint2 yv = *reinterpret_cast<const uint2 *>(Y);
+    unsigned int c[24];                                      // the 24 output bytes, one per register
 #pragma unroll
     for (int i = 0; i < 8; i++) {
         const int yy = (int)(((i < 4 ? yv.x : yv.y) >> (8 * (i & 3))) & 0xffu);
         const int cbx = cb[i] - 128, crx = cr[i] - 128;
-        int r = yy + ((91881 * crx + 32768) >> 16);
-        int b = yy + ((116130 * cbx + 32768) >> 16);
-        int g = yy + ((-22554 * cbx + 32768 - 46802 * crx) >> 16);
-        r = min(max(r, 0), 255); g = min(max(g, 0), 255); b = min(max(b, 0), 255);
-        px[3 * i] = (unsigned char)(p.bgr ? b : r); px[3 * i + 1] = (unsigned char)g; px[3 * i + 2] = (unsigned char)(p.bgr ? r : b);
+        const int r = min(max(yy + ((91881 * crx + 32768) >> 16), 0), 255);
+        const int b = min(max(yy + ((116130 * cbx + 32768) >> 16), 0), 255);
+        const int g = min(max(yy + ((-22554 * cbx + 32768 - 46802 * crx) >> 16), 0), 255);
+        c[3 * i] = (unsigned int)(p.bgr ? b : r); c[3 * i + 1] = (unsigned int)g; c[3 * i + 2] = (unsigned int)(p.bgr ? r : b);
     }
+    unsigned int wv[6];
+#pragma unroll
+    for (int j = 0; j < 6; j++) wv[j] = c[4 * j] | (c[4 * j + 1] << 8) | (c[4 * j + 2] << 16) | (c[4 * j + 3] << 24);
     unsigned char *o = p.rgb + (size_t)y * p.rgb_pitch + (size_t)x0 * 3;
     if (x0 + 8 <= p.w) {
         uint2 *o8 = reinterpret_cast<uint2 *>(o);
-#pragma unroll
-        for (int j = 0; j < 3; j++) {
-            uint2 v;
-            v.x = px[8 * j] | (px[8 * j + 1] << 8) | (px[8 * j + 2] << 16) | ((unsigned int)px[8 * j + 3] << 24);
-            v.y = px[8 * j + 4] | (px[8 * j + 5] << 8) | (px[8 * j + 6] << 16) | ((unsigned int)px[8 * j + 7] << 24);
-            o8[j] = v;
-        }
+        o8[0] = make_uint2(wv[0], wv[1]); o8[1] = make_uint2(wv[2], wv[3]); o8[2] = make_uint2(wv[4], wv[5]);
     } else {
-        for (int i = 0; i < (p.w - x0) * 3; i++) o[i] = px[i];
+        const int nb = (p.w - x0) * 3;                       // ragged right edge: byte stores, fully unrolled
+#pragma unroll
+        for (int i = 0; i < 21; i++)
+            if (i < nb) o[i] = (unsigned char)(wv[i >> 2] >> (8 * (i & 3)));
     }
 }
 
