@@ -191,6 +191,59 @@ public final class Icb {
         }
     }
 
+    private static final MethodHandle JPG_FILE_INFO = h("icb_jpg_file_info",
+            FunctionDescriptor.of(JAVA_INT, ADDRESS, JAVA_LONG, ADDRESS, ADDRESS));
+    private static final MethodHandle JPG_FILE_FIT = h("icb_jpg_file_fit", FunctionDescriptor.of(JAVA_INT,
+            ADDRESS, ADDRESS, JAVA_LONG, JAVA_FLOAT, JAVA_LONG, JAVA_INT, JAVA_FLOAT, JAVA_DOUBLE, ADDRESS, JAVA_LONG,
+            ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS, ADDRESS));
+
+    /** Result of {@link #jpgFileFit}: the fit plus the dimensions of the raster the seam saw (for CacheTools.createKey). */
+    public record FileFit(Fit fit, int width, int height) { }
+
+    /**
+     * Dimensions of a JPEG file the GPU reader takes (core/ImageCompression.java:128-129), or null when the file is of
+     * another kind (progressive, 4:4:4, gray, CMYK, restart markers): the caller then decodes with ImageIO as before.
+     */
+    public static int[] jpgFileInfo(byte[] file) throws IOException {
+        try (Arena a = Arena.ofConfined()) {
+            MemorySegment f = a.allocate(file.length);
+            f.copyFrom(MemorySegment.ofArray(file));
+            MemorySegment w = a.allocate(JAVA_INT), hgt = a.allocate(JAVA_INT);
+            int rc = (int) JPG_FILE_INFO.invokeExact(f, (long) file.length, w, hgt);
+            return rc == OK ? new int[] {w.get(JAVA_INT, 0), hgt.get(JAVA_INT, 0)} : null;
+        } catch (RuntimeException | Error e) {
+            throw e;
+        } catch (Throwable t) {
+            throw new IOException(t);
+        }
+    }
+
+    /**
+     * core/ImageCompression.java:119-155 (decode with the source-subsampling rule) + core/ImageCompressionJpg.java:77-122
+     * in one call: the FILE goes to the GPU, is decoded there and fitted; the decoded pixels never exist on the host.
+     * status ERR_UNSUPPORTED = decode on the host and call {@link #jpgFit} instead.
+     */
+    public static FileFit jpgFileFit(byte[] file, float initQuality, long target, boolean hasCached, float cachedQuality,
+                                     double cachedScale) throws IOException {
+        MemorySegment in = STAGING.get().px(file.length);            // the thread's page-locked input segment
+        in.copyFrom(MemorySegment.ofArray(file));
+        long cap = Math.max(target, 0) + 16;
+        MemorySegment out = STAGING.get().out(cap);
+        try (Arena a = Arena.ofConfined()) {
+            MemorySegment outLen = a.allocate(JAVA_LONG), bestQ = a.allocate(JAVA_FLOAT), scale = a.allocate(JAVA_DOUBLE),
+                    used = a.allocate(JAVA_INT), w = a.allocate(JAVA_INT), hgt = a.allocate(JAVA_INT);
+            int rc = (int) JPG_FILE_FIT.invokeExact(handle(), in, (long) file.length, initQuality, target,
+                    hasCached ? 1 : 0, cachedQuality, cachedScale, out, cap, outLen, bestQ, scale, used, w, hgt);
+            byte[] bytes = rc == OK ? out.asSlice(0, outLen.get(JAVA_LONG, 0)).toArray(JAVA_BYTE) : null;
+            return new FileFit(new Fit(rc, bytes, bestQ.get(JAVA_FLOAT, 0), scale.get(JAVA_DOUBLE, 0), used.get(JAVA_INT, 0) != 0),
+                    w.get(JAVA_INT, 0), hgt.get(JAVA_INT, 0));
+        } catch (RuntimeException | Error e) {
+            throw e;
+        } catch (Throwable t) {
+            throw new IOException(t);
+        }
+    }
+
     /** core/ImageCompressionJpg.java:136-147 compressJpgToStream: one encode at an explicit quality. */
     public static byte[] jpgEncode(BufferedImage img, float quality) throws IOException {
         int fmt = formatOf(img);

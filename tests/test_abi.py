@@ -106,3 +106,20 @@ def test_product_package_never_touches_the_oracle():
             if fn.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 text = open(os.path.join(dirpath, fn), errors="replace").read()
                 assert "liboracle" not in text and "from oracle" not in text and "import oracle" not in text, fn
+
+
+def test_jpeg_header_parse_needs_no_device():
+    """icb_jpg_file_info (core/ImageCompression.java:128-129 reader.getWidth / getHeight): host arithmetic only"""
+    z = np.load(os.path.join(ROOT, "tests", "golden", "jpeg_decode.npz"))
+    n = len([k for k in z.files if k.startswith("file_")])
+    for i in range(n):
+        h, w = z[f"pixels_{i}"].shape[:2]
+        assert pkg.jpg_file_info(z[f"file_{i}"]) == (w, h)
+    for name in ("progressive", "s444", "s422", "restart", "gray"):
+        with pytest.raises(pkg.IcbError) as ei:
+            pkg.jpg_file_info(z["unsup_" + name])
+        assert ei.value.code == api.ICB_ERR_UNSUPPORTED
+    for junk in (b"", b"\xff\xd8", b"not a jpeg at all", z["file_0"].tobytes()[:100]):
+        with pytest.raises(pkg.IcbError) as ei:
+            pkg.jpg_file_info(junk if junk else np.zeros(0, np.uint8))
+        assert ei.value.code == api.ICB_ERR_INVALID
