@@ -26,6 +26,7 @@ from __future__ import annotations
 import argparse
 import json
 import os
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")   # before anything starts CUDA (icb_init asks for the same; torch may come first)
 import statistics
 import subprocess
 import sys
@@ -138,10 +139,24 @@ def dist_setup():
     if world > 1:
         import torch
         import torch.distributed as dist_mod
+        import datetime
         torch.cuda.set_device(local)
-        dist_mod.init_process_group(backend="nccl", device_id=torch.device("cuda", local))
+        dist_mod.init_process_group(backend="nccl", device_id=torch.device("cuda", local),
+                                    timeout=datetime.timedelta(seconds=300))
         dist = dist_mod
+        # host-side barrier for the stretch in which rank 0 alone drives EVERY GPU: an NCCL barrier would park a
+        # spinning kernel of the waiting ranks on the very GPUs rank 0 is using (measured r02: the leg never ended)
+        global _HOST_GROUP
+        _HOST_GROUP = dist_mod.new_group(backend="gloo", timeout=datetime.timedelta(seconds=300))
     return rank, local, world, dist
+
+
+_HOST_GROUP = None
+
+
+def host_barrier(dist):
+    if dist is not None:
+        dist.barrier(group=_HOST_GROUP)
 
 
 def barrier(dist):
@@ -718,7 +733,7 @@ def run_gpu(args):
             except Exception as e:                                   # a leg must never lose the headline
                 other[name] = {"error": repr(e)}
     eng.close()
-    barrier(dist)
+    host_barrier(dist)                  # (the other ranks wait on the host while rank 0 runs its legs)
 
     # ---- one process, all GPUs (the Java host's shape, CompressionBatch.java:64-90)
     one = None
@@ -728,7 +743,7 @@ def run_gpu(args):
                 one = one_process_all_gpus(world, pool, w, h, q, target, slots, batch)
             except Exception as e:
                 one = {"error": repr(e)}
-        barrier(dist)
+        host_barrier(dist)
 
     if rank == 0:
         line = {
@@ -802,7 +817,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="cfg1", choices=sorted(WORKLOADS))
     ap.add_argument("--batch", type=int, default=128, help="images per GPU per step")
-    ap.add_argument("--slots", type=int, default=6, help="stream work-queue slots per GPU")
+    ap.add_argument("--slots", type=int, default=8, help="stream work-queue slots per GPU (r02 A/B: 6 -> 12.6k, 8 -> 13.0k, 12 -> 13.1k img/s resident)")
     ap.add_argument("--threads", type=int, default=2, help="executor threads per GPU (each keeps slots/threads jobs in flight)")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-check", action="store_true")

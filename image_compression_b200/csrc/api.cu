@@ -47,6 +47,11 @@ struct DeviceCtx {
     cudaEvent_t join = nullptr;
 };
 
+struct DecJob {                          // per-job block of the JPEG reader in device memory: parameters + the file's tables
+    DecParams p;
+    DecTables t;
+};
+
 enum Phase { PH_IDLE = 0, PH_CACHED, PH_SEARCH, PH_RESIZE, PH_PNG, PH_PNG_FETCH, PH_DONE };
 
 struct Job {
@@ -100,8 +105,10 @@ struct Slot {
     unsigned char *d_sub = nullptr;     size_t sub_cap = 0;
     unsigned char *d_planes = nullptr;  size_t planes_cap = 0;
     unsigned char *d_dec = nullptr;     size_t dec_cap = 0;     // decoded raster when the decode rule subsamples it
-    DecTables *d_dectab = nullptr;      DecTables *h_dectab = nullptr;      // h_*: pinned
+    DecJob *d_decjob = nullptr;         DecJob *h_decjob = nullptr;         // h_*: pinned
     DecState *d_decst = nullptr;        DecState *h_decst = nullptr;
+    size_t dec_scan_cap = 0; int dec_w_cap = 0, dec_h_cap = 0;              // what the slot's decode graph is sized for
+    cudaGraphExec_t dec_graph = nullptr; uint64_t dec_graph_key = 0;
     Geom geom{};
     bool busy = false;
     bool lone = false;                      // the job in flight found no other slot of its GPU busy (enqueue_transform)
@@ -312,6 +319,13 @@ int ensure(icb_handle *h, T *&p, size_t &cap, size_t need)
     return ICB_OK;
 }
 
+// icb_run_list's workers hold several tickets each; a worker that WAITED here for a slot (of one particular GPU, for a
+// resident image) while holding tickets could wait for a slot only another waiting worker can free -- measured r02 on two
+// GPUs: four workers, all blocked, none collecting.  Inside the executor acquire_slot therefore does not wait: the
+// submit call comes back with ICB_BUSY_INTERNAL and the worker collects its oldest job before it tries again.
+thread_local bool tl_acquire_nowait = false;
+constexpr int ICB_BUSY_INTERNAL = 2;
+
 // A free slot on the GPU with the fewest busy slots (devi >= 0: on that GPU); on a tie the GPU after the one
 // taken last (so equally loaded GPUs take turns), and on a GPU its lowest free slot -- a caller that runs one job
 // at a time keeps coming back to arenas that are sized for its images already instead of walking through every
@@ -339,6 +353,7 @@ Slot *acquire_slot(icb_handle *h, int devi = -1)
             h->rr = nd > 0 ? (best->devi + 1) % nd : 0;
             return best;
         }
+        if (tl_acquire_nowait) return nullptr;          // (icb_run_list: the worker collects one of its own jobs first)
         h->cv.wait(lk);
     }
 }
@@ -1028,8 +1043,9 @@ void icb_shutdown(icb_handle *h)
         if (s.h_state) cudaFreeHost(s.h_state);
         cudaFree(s.d_png); cudaFree(s.d_file);
         cudaFree(s.d_file_in); cudaFree(s.d_bits); cudaFree(s.d_sub); cudaFree(s.d_planes); cudaFree(s.d_dec);
-        cudaFree(s.d_dectab); cudaFree(s.d_decst);
-        if (s.h_dectab) cudaFreeHost(s.h_dectab);
+        cudaFree(s.d_decjob); cudaFree(s.d_decst);
+        if (s.dec_graph) cudaGraphExecDestroy(s.dec_graph);
+        if (s.h_decjob) cudaFreeHost(s.h_decjob);
         if (s.h_decst) cudaFreeHost(s.h_decst);
         if (s.h_len) cudaFreeHost(s.h_len);
         if (s.h_in) cudaFreeHost(s.h_in);
@@ -1076,6 +1092,7 @@ int icb_submit_jpg_fit(icb_handle *h, const uint8_t *px, int w, int hgt, int pit
     if (rc) return rc;
     if (!ticket) return ICB_ERR_INVALID;
     Slot *s = acquire_slot(h);
+    if (!s) return ICB_BUSY_INTERNAL;
     const int dp = dev_pitch(w, 3);
     if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "cudaSetDevice");
     if (!rc) rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)dp * hgt + 16);
@@ -1095,6 +1112,7 @@ int icb_submit_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q, 
     int rc = check_fit_qualities(h, init_q, has_cached, cached_q);
     if (rc) return rc;
     Slot *s = acquire_slot(h, img->devi);
+    if (!s) return ICB_BUSY_INTERNAL;
     rc = start_fit(h, s, img->d_px, img->w, img->h, img->pitch, img->fmt, init_q, target, has_cached, cached_q,
                    cached_scale, out, out_cap);
     if (rc) { cudaStreamSynchronize(s->stream); release_slot(h, s); return rc; }
@@ -1288,6 +1306,7 @@ int icb_submit_resize_image(icb_handle *h, const icb_image *img, int dw, int dh,
     const int bpp = bpp_of(img->fmt);
     if (dst && dpitch < dw * bpp) return fail(h, ICB_ERR_INVALID, "dpitch smaller than a row");
     Slot *s = acquire_slot(h, img->devi);
+    if (!s) return ICB_BUSY_INTERNAL;
     int rc = cudaSetDevice(h->devs[s->devi].dev) == cudaSuccess ? ICB_OK : fail(h, ICB_ERR_CUDA, "cudaSetDevice");
     if (!rc) rc = start_resize(h, s, img->d_px, img->w, img->h, img->pitch, img->fmt, dw, dh, dst, dpitch);
     if (rc) { cudaStreamSynchronize(s->stream); release_slot(h, s); return rc; }
@@ -1303,6 +1322,7 @@ int icb_submit_resize(icb_handle *h, const uint8_t *src, int w, int hgt, int pit
     if (!ticket) return ICB_ERR_INVALID;
     const int bpp = bpp_of(fmt);
     Slot *s = acquire_slot(h);
+    if (!s) return ICB_BUSY_INTERNAL;
     const int sp = (int)round_up((size_t)w * bpp, 16);
     if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "cudaSetDevice");
     if (!rc) rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)sp * hgt + 16);
@@ -1335,6 +1355,7 @@ int icb_submit_png_encode(icb_handle *h, const uint8_t *px, int w, int hgt, int 
     const int bpp = bpp_of(fmt);
     if (pitch < w * bpp) return fail(h, ICB_ERR_INVALID, "pitch smaller than a row");
     Slot *s = acquire_slot(h);
+    if (!s) return ICB_BUSY_INTERNAL;
     const int sp = (int)round_up((size_t)w * bpp, 16);
     int rc = cudaSetDevice(h->devs[s->devi].dev) == cudaSuccess ? ICB_OK : fail(h, ICB_ERR_CUDA, "cudaSetDevice");
     if (!rc) rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)sp * hgt + 16);
@@ -1372,6 +1393,7 @@ int icb_submit_png_compress(icb_handle *h, const uint8_t *src, int w, int hgt, i
     const int rc0 = icb_png_target_dims(w, hgt, min_w, min_h, dw, dh, nullptr);
     if (rc0) return rc0;                                            // ICB_NO_FIT: the seam returns false, nothing queued
     Slot *s = acquire_slot(h);
+    if (!s) return ICB_BUSY_INTERNAL;
     const int sp = (int)round_up((size_t)w * bpp, 16), np = (int)round_up((size_t)*dw * bpp, 16);
     int rc = cudaSetDevice(h->devs[s->devi].dev) == cudaSuccess ? ICB_OK : fail(h, ICB_ERR_CUDA, "cudaSetDevice");
     if (!rc) rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)sp * hgt + 16);
@@ -1476,6 +1498,7 @@ int icb_jpg_encode(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, 
     if (bad_quality(q)) return fail(h, ICB_ERR_INVALID, "quality outside [0, 1]");     // ImageWriteParam.setCompressionQuality
     const FitPlan pl = make_plan(MODE_SINGLE, q, 0, 1, false);
     Slot *s = acquire_slot(h);
+    if (!s) return ICB_BUSY_INTERNAL;
     rc = stage_and_transform(h, s, px, w, hgt, pitch, fmt, &pl);
     long long cap = 0;
     if (!rc) {
@@ -1516,6 +1539,7 @@ int icb_jpg_sizes(icb_handle *h, const uint8_t *px, int w, int hgt, int pitch, i
     if (!qs || !sizes || n < 0) return ICB_ERR_INVALID;
     for (int i = 0; i < n; i++) if (bad_quality(qs[i])) return fail(h, ICB_ERR_INVALID, "quality outside [0, 1]");
     Slot *s = acquire_slot(h);
+    if (!s) return ICB_BUSY_INTERNAL;
     rc = stage_and_transform(h, s, px, w, hgt, pitch, fmt, nullptr);
     for (int i = 0; i < n && !rc; i++) {        // one transform; every size from the coefficients in HBM
         rc = enqueue_passes(h, s, make_plan(MODE_SINGLE, qs[i], 0, 1, false), false, false, 0);
@@ -1538,6 +1562,7 @@ int icb_jpg_coefficients(icb_handle *h, const uint8_t *px, int w, int hgt, int p
     if (rc) return rc;
     if (!out) return ICB_ERR_INVALID;
     Slot *s = acquire_slot(h);
+    if (!s) return ICB_BUSY_INTERNAL;
     rc = stage_and_transform(h, s, px, w, hgt, pitch, fmt, nullptr);
     if (!rc) {
         const size_t need = (size_t)s->geom.nblocks * 64;
@@ -1583,6 +1608,7 @@ int icb_subsample(icb_handle *h, const uint8_t *src, int w, int hgt, int pitch, 
     const int dw = (w + sfac - 1) / sfac, dh = (hgt + sfac - 1) / sfac;
     if (pitch < w * bpp || dpitch < dw * bpp) return fail(h, ICB_ERR_INVALID, "pitch smaller than a row");
     Slot *s = acquire_slot(h);
+    if (!s) return ICB_BUSY_INTERNAL;
     int rc = ICB_OK;
     do {
         if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess) { rc = ICB_ERR_CUDA; break; }
@@ -1726,6 +1752,7 @@ int icb_profile_resize_series(icb_handle *h, const icb_image *img, int dw, int d
 {
     if (!h || !img || dw < 1 || dh < 1 || reps < 1 || !ms_per_launch) return ICB_ERR_INVALID;
     Slot *s = acquire_slot(h, img->devi);
+    if (!s) return ICB_BUSY_INTERNAL;
     int rc = ICB_OK;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     do {
@@ -1762,6 +1789,7 @@ int icb_profile_jpg_fit_image(icb_handle *h, const icb_image *img, float init_q,
     if (!h || !img || reps < 1) return ICB_ERR_INVALID;
     if (img->fmt != ICB_FMT_RGB8 && img->fmt != ICB_FMT_BGR8) return fail(h, ICB_ERR_UNSUPPORTED, "format");
     Slot *s = acquire_slot(h, img->devi);
+    if (!s) return ICB_BUSY_INTERNAL;
     int rc = ICB_OK;
     cudaEvent_t e0 = nullptr, e1 = nullptr, e2 = nullptr, pe[16] = {nullptr};
     float xf = 0, ent = 0, entk = 0;
@@ -1940,7 +1968,14 @@ extern "C" int icb_run_list(icb_handle *h, icb_item *items, size_t n, int thread
             icb_item *it = &items[k];
             if ((int)pending.size() == inflight) finish();
             int64_t t = 0;
-            const int rc = submit_item(h, it, &t);
+            int rc;
+            while (true) {
+                tl_acquire_nowait = !pending.empty();       // holding tickets: never wait for a slot
+                rc = submit_item(h, it, &t);
+                tl_acquire_nowait = false;
+                if (rc != ICB_BUSY_INTERNAL) break;
+                finish();                                   // frees a slot (ours), then try again
+            }
             if (rc != ICB_OK) {                     // ICB_NO_FIT from the PNG rule, or an error: nothing was queued
                 it->res = icb_result{};
                 it->res.status = rc;
@@ -2095,6 +2130,42 @@ int map_parse(icb_handle *h, int jp)
 }
 
 // file bytes (host) -> decoded raster in d_out (pitch out_pitch, RGB8 or BGR8), all queued on the slot's stream
+// The decode chain of one slot as a CUDA graph.  Every kernel reads its parameters from a block in device memory
+// (DecJob: uploaded per job together with the file's tables), grids and memset sizes follow the slot's CAPACITIES
+// (longest scan / largest image seen so far, rounded up; surplus CTAs leave at once), so the graph is captured once
+// per slot and replayed: a job costs one upload of the block, one of the file, one graph launch -- 3 driver calls
+// instead of 30 (measured r02: ~200 us of serialised driver time per file job with plain launches).
+int dec_rounds()
+{
+    static const int v = [] { const char *e = getenv("ICB_DEC_ROUNDS"); const int x = e ? atoi(e) : DEC_ROUNDS; return x >= 2 && x <= DEC_ROUNDS ? x : DEC_ROUNDS; }();
+    return v;
+}
+
+void launch_decode_chain(Slot *s, cudaStream_t st, size_t sub_bytes_cap, size_t nblocks_cap, int nchunks_cap, unsigned int nsub_cap,
+                         int w_cap, int h_cap)
+{
+    const DecParams *pp = &s->d_decjob->p;
+    // state: everything zero, the scan ends at the end of the file unless a marker turns up earlier; no record yet
+    cudaMemsetAsync(s->d_decst, 0, sizeof(DecState), st);
+    cudaMemsetAsync(&s->d_decst->scan_end, 0xff, 4, st);
+    cudaMemsetAsync(s->d_coef, 0, nblocks_cap * 128, st);
+    cudaMemsetAsync(s->d_sub, 0xff, sub_bytes_cap, st);
+    k_dec_scan<<<nchunks_cap, 256, 0, st>>>(pp);
+    k_dec_offsets<<<1, 1024, 0, st>>>(pp);
+    k_dec_unstuff<<<nchunks_cap, 256, 0, st>>>(pp);
+    const unsigned int sgrid = (nsub_cap + 127) / 128;
+    const int nrounds = dec_rounds();
+    for (int r = 0; r < nrounds; r++) k_dec_sync<<<sgrid, 128, 0, st>>>(pp, r == 0 ? 0 : DEC_ROUNDS - nrounds + r);
+    k_dec_blocks<<<1, 1024, 0, st>>>(pp);
+    k_dec_write<<<sgrid, 128, 0, st>>>(pp);
+    const size_t ndc = (nblocks_cap / 6 + DEC_DC_THREADS - 1) / DEC_DC_THREADS;
+    k_dec_dc_local<<<(unsigned int)ndc, DEC_DC_THREADS, 0, st>>>(pp);
+    k_dec_dc_cta<<<1, 1024, 0, st>>>(pp);
+    k_dec_idct<<<(unsigned int)((nblocks_cap + 127) / 128), 128, 0, st>>>(pp);
+    k_dec_color<<<dim3((w_cap + 255) / 256, (h_cap + 7) / 8), 256, 0, st>>>(pp);
+}
+
+// file bytes (host) -> decoded raster in d_out (pitch out_pitch, RGB8 or BGR8), all queued on the slot's stream
 int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const JpegHeader &hd, unsigned char *d_out,
                    int out_pitch, bool bgr)
 {
@@ -2107,37 +2178,43 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
         const int v = e ? atoi(e) : DEC_SUB_BITS;
         return (unsigned int)(v >= 256 && v <= 8192 && v % 32 == 0 ? v : DEC_SUB_BITS);   // (12 bits of block count: >= 4 bits a block)
     }();
-    const unsigned int nsub_max = (unsigned int)((scan_bytes * 8 + sub_bits - 1) / sub_bits);
-    if (nsub_max >= (1u << 17)) return fail(h, ICB_ERR_UNSUPPORTED, "JPEG reader: scan too long for the subsequence records");
-    const int nchunks = (int)((scan_bytes + DEC_CHUNK - 1) / DEC_CHUNK);
-    if (!s->d_dectab) {
-        if (cudaMalloc((void **)&s->d_dectab, sizeof(DecTables)) != cudaSuccess ||
+    static const unsigned int carry = [] { const char *e = getenv("ICB_DEC_CARRY"); const int v = e ? atoi(e) : DEC_CARRY; return (unsigned int)(v >= 1 && v <= 64 ? v : DEC_CARRY); }();
+    static const bool use_graph = [] { const char *e = getenv("ICB_DEC_GRAPH"); return !(e && e[0] == '0'); }();
+    if ((scan_bytes * 8 + sub_bits - 1) / sub_bits >= (1u << 17))
+        return fail(h, ICB_ERR_UNSUPPORTED, "JPEG reader: scan too long for the subsequence records");
+    // capacities of the slot: they only grow, in steps (1 MB of scan, 256 blocks of 16 pixels), so that slots settle
+    const size_t scan_cap = std::max(s->dec_scan_cap, round_up(scan_bytes, (size_t)1 << 20));
+    const int wc = std::max(s->dec_w_cap, (int)round_up((size_t)hd.w, 256)), hc = std::max(s->dec_h_cap, (int)round_up((size_t)hd.h, 256));
+    const size_t nblocks_cap = (size_t)((wc + 15) / 16) * ((hc + 15) / 16) * 6;
+    const unsigned int nsub_cap = (unsigned int)std::min<size_t>((scan_cap * 8 + sub_bits - 1) / sub_bits, (1u << 17) - 1);
+    const int nchunks_cap = (int)((scan_cap + DEC_CHUNK - 1) / DEC_CHUNK);
+    if (!s->d_decjob) {
+        if (cudaMalloc((void **)&s->d_decjob, sizeof(DecJob)) != cudaSuccess ||
             cudaMalloc((void **)&s->d_decst, sizeof(DecState)) != cudaSuccess ||
-            cudaMallocHost((void **)&s->h_dectab, sizeof(DecTables)) != cudaSuccess ||
+            cudaMallocHost((void **)&s->h_decjob, sizeof(DecJob)) != cudaSuccess ||
             cudaMallocHost((void **)&s->h_decst, sizeof(DecState)) != cudaSuccess)
             return fail(h, ICB_ERR_OOM, "decode tables");
     }
-    int rc = ensure(h, s->d_file_in, s->file_in_cap, round_up(n, 256) + 256);
-    if (!rc) rc = ensure(h, s->d_bits, s->bits_cap, round_up(scan_bytes, 256) + 512);
-    const size_t sub_bytes = round_up((size_t)nsub_max * 8, 256);
-    const size_t nmcu = nblocks / 6, ndc = (nmcu + DEC_DC_THREADS - 1) / DEC_DC_THREADS;
-    const size_t o_base = sub_bytes, o_chunk = o_base + round_up((size_t)nsub_max * 4, 256);
-    const size_t o_mcu = o_chunk + round_up((size_t)(nchunks + 1) * 4, 256), o_cta = o_mcu + round_up(nmcu * 12, 256);
-    if (!rc) rc = ensure(h, s->d_sub, s->sub_cap, o_cta + round_up(ndc * 12, 256));
-    const size_t ysz = (size_t)mcu_cols * 16 * mcu_rows * 16;
-    if (!rc) rc = ensure(h, s->d_planes, s->planes_cap, ysz + ysz / 2 + 256);
-    if (!rc) rc = ensure(h, s->d_coef, s->coef_cap, nblocks * 128);
+    int rc = ensure(h, s->d_file_in, s->file_in_cap, round_up(n, (size_t)1 << 20) + 256);
+    if (!rc) rc = ensure(h, s->d_bits, s->bits_cap, scan_cap + 512);
+    const size_t sub_bytes = round_up((size_t)nsub_cap * 8, 256);
+    const size_t nmcu_cap = nblocks_cap / 6, ndc_cap = (nmcu_cap + DEC_DC_THREADS - 1) / DEC_DC_THREADS;
+    const size_t o_base = sub_bytes, o_chunk = o_base + round_up((size_t)nsub_cap * 4, 256);
+    const size_t o_mcu = o_chunk + round_up((size_t)(nchunks_cap + 1) * 4, 256), o_cta = o_mcu + round_up(nmcu_cap * 12, 256);
+    if (!rc) rc = ensure(h, s->d_sub, s->sub_cap, o_cta + round_up(ndc_cap * 12, 256));
+    if (!rc) rc = ensure(h, s->d_planes, s->planes_cap, nblocks_cap * 64 + 256);
+    if (!rc) rc = ensure(h, s->d_coef, s->coef_cap, nblocks_cap * 128);
     if (rc) return rc;
-    jpeg_build_tables(hd, *s->h_dectab);
-    CK(cudaMemcpyAsync(s->d_dectab, s->h_dectab, sizeof(DecTables), cudaMemcpyHostToDevice, st));
-    rc = upload(h, s, s->d_file_in, (int)std::min<size_t>(n, 0x7fffffff), file, (int)n, 1, (int)n, 1);
-    if (rc) return rc;
-    DecParams dp = {};
+    s->dec_scan_cap = scan_cap; s->dec_w_cap = wc; s->dec_h_cap = hc;
+
+    DecJob &job = *s->h_decjob;
+    jpeg_build_tables(hd, job.t);
+    DecParams &dp = job.p;
+    dp = DecParams{};
     dp.file = s->d_file_in; dp.file_len = (unsigned int)n; dp.scan_off = (unsigned int)hd.scan_off;
     dp.bits = s->d_bits;
     dp.rec = reinterpret_cast<unsigned long long *>(s->d_sub);
     dp.sub_bits = sub_bits;
-    static const unsigned int carry = [] { const char *e = getenv("ICB_DEC_CARRY"); const int v = e ? atoi(e) : DEC_CARRY; return (unsigned int)(v >= 1 && v <= 64 ? v : DEC_CARRY); }();
     dp.carry = carry;
     dp.blk_base = reinterpret_cast<unsigned int *>(s->d_sub + o_base);
     dp.chunk_drop = reinterpret_cast<unsigned int *>(s->d_sub + o_chunk);
@@ -2148,29 +2225,37 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     dp.rgb = d_out; dp.rgb_pitch = out_pitch; dp.bgr = bgr ? 1 : 0;
     dp.w = hd.w; dp.h = hd.h; dp.mcu_cols = mcu_cols; dp.mcu_rows = mcu_rows;
     dp.nblocks = (unsigned int)nblocks;
-    dp.nsub_max = nsub_max;
-    dp.tab = s->d_dectab;
+    dp.nsub_max = (unsigned int)((scan_bytes * 8 + sub_bits - 1) / sub_bits);
+    dp.nchunks = (int)((scan_bytes + DEC_CHUNK - 1) / DEC_CHUNK);
+    dp.tab = &s->d_decjob->t;
     dp.st = s->d_decst;
-    // state: everything zero, the scan ends at the end of the file unless a marker turns up earlier
-    CK(cudaMemsetAsync(s->d_decst, 0, sizeof(DecState), st));
-    CK(cudaMemsetAsync(&s->d_decst->scan_end, 0xff, 4, st));
-    CK(cudaMemsetAsync(s->d_coef, 0, nblocks * 128, st));
-    CK(cudaMemsetAsync(s->d_sub, 0xff, sub_bytes, st));              // no record yet
-    k_dec_scan<<<nchunks, 256, 0, st>>>(dp);
-    k_dec_offsets<<<1, 1024, 0, st>>>(dp, nchunks);
-    k_dec_unstuff<<<nchunks, 256, 0, st>>>(dp);
-    const unsigned int sgrid = (nsub_max + 127) / 128;
-    // rounds queued: DEC_ROUNDS unless ICB_DEC_ROUNDS asks for fewer (A/B runs); the verdict reads the last one queued
-    static const int nrounds = [] { const char *e = getenv("ICB_DEC_ROUNDS"); const int v = e ? atoi(e) : DEC_ROUNDS; return v >= 2 && v <= DEC_ROUNDS ? v : DEC_ROUNDS; }();
-    for (int r = 0; r < nrounds; r++) k_dec_sync<<<sgrid, 128, 0, st>>>(dp, r == 0 ? 0 : DEC_ROUNDS - nrounds + r);
-    k_dec_blocks<<<1, 1024, 0, st>>>(dp);
-    k_dec_write<<<sgrid, 128, 0, st>>>(dp);
-    k_dec_dc_local<<<(unsigned int)ndc, DEC_DC_THREADS, 0, st>>>(dp);
-    k_dec_dc_cta<<<1, 1024, 0, st>>>(dp, (int)ndc);
-    k_dec_idct<<<(unsigned int)((nblocks + 127) / 128), 128, 0, st>>>(dp);
-    k_dec_color<<<dim3((hd.w + 255) / 256, (hd.h + 7) / 8), 256, 0, st>>>(dp);
-    CK(cudaGetLastError());
-    h->kernels += 9 + DEC_ROUNDS;
+    CK(cudaMemcpyAsync(s->d_decjob, s->h_decjob, sizeof(DecJob), cudaMemcpyHostToDevice, st));
+    rc = upload(h, s, s->d_file_in, (int)std::min<size_t>(n, 0x7fffffff), file, (int)n, 1, (int)n, 1);
+    if (rc) return rc;
+
+    if (use_graph) {
+        // the graph stands for these buffers and capacities; anything else: capture again
+        const uint64_t key = ((uint64_t)(uintptr_t)s->d_coef * 0x9E3779B97F4A7C15ull) ^ ((uint64_t)(uintptr_t)s->d_sub * 0xC2B2AE3D27D4EB4Full) ^
+                             ((uint64_t)(uintptr_t)s->d_decst << 7) ^ ((uint64_t)scan_cap << 3) ^ ((uint64_t)wc << 40) ^ ((uint64_t)hc << 20) ^
+                             (uint64_t)dec_rounds();
+        if (!s->dec_graph || s->dec_graph_key != key) {
+            if (s->dec_graph) { cudaGraphExecDestroy(s->dec_graph); s->dec_graph = nullptr; }
+            cudaGraph_t g = nullptr;
+            CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            launch_decode_chain(s, st, sub_bytes, nblocks_cap, nchunks_cap, nsub_cap, wc, hc);
+            cudaError_t e = cudaStreamEndCapture(st, &g);
+            if (e != cudaSuccess || !g) return fail(h, ICB_ERR_CUDA, "decode graph capture", e);
+            e = cudaGraphInstantiate(&s->dec_graph, g, 0);
+            cudaGraphDestroy(g);
+            if (e != cudaSuccess) { s->dec_graph = nullptr; return fail(h, ICB_ERR_CUDA, "decode graph instantiate", e); }
+            s->dec_graph_key = key;
+        }
+        CK(cudaGraphLaunch(s->dec_graph, st));
+    } else {
+        launch_decode_chain(s, st, sub_bytes, nblocks_cap, nchunks_cap, nsub_cap, wc, hc);
+        CK(cudaGetLastError());
+    }
+    h->kernels += 9 + dec_rounds();
     CK(cudaMemcpyAsync(s->h_decst, s->d_decst, sizeof(DecState), cudaMemcpyDeviceToHost, st));
     s->job.dec_nblocks = (unsigned int)nblocks;
     return ICB_OK;
@@ -2203,6 +2288,7 @@ int icb_jpg_decode(icb_handle *h, const uint8_t *file, size_t n, int fmt, uint8_
     if (hgt) *hgt = hd.h;
     if (dpitch < hd.w * 3 || dst_cap < (size_t)dpitch * (hd.h - 1) + (size_t)hd.w * 3) return fail(h, ICB_ERR_CAPACITY, "dst too small");
     Slot *s = acquire_slot(h);
+    if (!s) return ICB_BUSY_INTERNAL;
     const int dp = dev_pitch(hd.w, 3);
     if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "cudaSetDevice");
     s->job = Job();
@@ -2254,6 +2340,7 @@ int icb_submit_jpg_file_fit(icb_handle *h, const uint8_t *file, size_t n, float 
     if (hgt) *hgt = fh;
     const auto ta = std::chrono::steady_clock::now();
     Slot *s = acquire_slot(h);
+    if (!s) return ICB_BUSY_INTERNAL;
     g_acquire_ns += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - ta).count();
     if (cudaSetDevice(h->devs[s->devi].dev) != cudaSuccess) rc = fail(h, ICB_ERR_CUDA, "cudaSetDevice");
     s->job = Job();

@@ -85,13 +85,15 @@ struct DecParams {
     int w, h, mcu_cols, mcu_rows;
     unsigned int nblocks;
     unsigned int nsub_max;                  // subsequences the file could hold at most
+    int nchunks;                            // DEC_CHUNK-byte pieces of the file from scan_off on
     const DecTables *tab;
     DecState *st;
 };
 
 // ---- entropy-coded segment: stuffed zeros out, first marker found ----------------------------------------
-__global__ void __launch_bounds__(256) k_dec_scan(const DecParams p)
+__global__ void __launch_bounds__(256) k_dec_scan(const DecParams *pp)
 {
+    const DecParams p = *pp;
     __shared__ unsigned int s_cnt;
     if (threadIdx.x == 0) s_cnt = 0;
     __syncthreads();
@@ -115,8 +117,10 @@ __global__ void __launch_bounds__(256) k_dec_scan(const DecParams p)
     if (threadIdx.x == 0) p.chunk_drop[blockIdx.x] = s_cnt;
 }
 
-__global__ void __launch_bounds__(1024) k_dec_offsets(const DecParams p, int nchunks)
+__global__ void __launch_bounds__(1024) k_dec_offsets(const DecParams *pp)
 {
+    const DecParams p = *pp;
+    const int nchunks = p.nchunks;
     __shared__ unsigned int s_part[1024];
     const int tid = threadIdx.x;
     const int per = (nchunks + 1023) / 1024;
@@ -135,8 +139,9 @@ __global__ void __launch_bounds__(1024) k_dec_offsets(const DecParams p, int nch
     for (int i = i0; i < i1; i++) { const unsigned int c = p.chunk_drop[i]; p.chunk_drop[i] = run; run += c; }
 }
 
-__global__ void __launch_bounds__(256) k_dec_unstuff(const DecParams p)
+__global__ void __launch_bounds__(256) k_dec_unstuff(const DecParams *pp)
 {
+    const DecParams p = *pp;
     __shared__ unsigned int s_warp[8];
     const unsigned int end = min(p.st->scan_end, p.file_len);
     const unsigned int chunk0 = p.scan_off + blockIdx.x * DEC_CHUNK;
@@ -326,8 +331,9 @@ __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *b
 // start of the scan) differs from the one its record was decoded from decodes its subsequence again and carries on
 // into the following ones -- at most DEC_CARRY of them per round -- until it meets a record that was decoded from
 // exactly the state it arrives with: from there on the records are already what this thread would write.
-__global__ void __launch_bounds__(128) k_dec_sync(const DecParams p, int round)
+__global__ void __launch_bounds__(128) k_dec_sync(const DecParams *pp, int round)
 {
+    const DecParams p = *pp;
     __shared__ DecSmem s;
     const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned int total_bits = p.st->total_bytes * 8u;
@@ -357,8 +363,9 @@ __global__ void __launch_bounds__(128) k_dec_sync(const DecParams p, int round)
 }
 
 // blocks in front of every subsequence (exclusive prefix of the per-subsequence block counts), one CTA
-__global__ void __launch_bounds__(1024) k_dec_blocks(const DecParams p)
+__global__ void __launch_bounds__(1024) k_dec_blocks(const DecParams *pp)
 {
+    const DecParams p = *pp;
     __shared__ unsigned int s_part[1024];
     const int tid = threadIdx.x;
     const unsigned int total_bits = p.st->total_bytes * 8u;
@@ -380,8 +387,9 @@ __global__ void __launch_bounds__(1024) k_dec_blocks(const DecParams p)
     if (tid == 1023) p.st->blocks_found = s_part[1023];
 }
 
-__global__ void __launch_bounds__(128) k_dec_write(const DecParams p)
+__global__ void __launch_bounds__(128) k_dec_write(const DecParams *pp)
 {
+    const DecParams p = *pp;
     __shared__ DecSmem s;
     dec_load_tables(s, p.tab);
     const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -401,8 +409,9 @@ __global__ void __launch_bounds__(128) k_dec_write(const DecParams p)
 // differences of the blocks in front of its own inside the MCU.
 constexpr int DEC_DC_THREADS = 256;
 
-__global__ void __launch_bounds__(DEC_DC_THREADS) k_dec_dc_local(const DecParams p)
+__global__ void __launch_bounds__(DEC_DC_THREADS) k_dec_dc_local(const DecParams *pp)
 {
+    const DecParams p = *pp;
     __shared__ int s_w[3][DEC_DC_THREADS / 32];
     const unsigned int nm = p.nblocks / 6;
     const unsigned int m = blockIdx.x * DEC_DC_THREADS + threadIdx.x;
@@ -436,8 +445,10 @@ __global__ void __launch_bounds__(DEC_DC_THREADS) k_dec_dc_local(const DecParams
     }
 }
 
-__global__ void __launch_bounds__(1024) k_dec_dc_cta(const DecParams p, int nctas)
+__global__ void __launch_bounds__(1024) k_dec_dc_cta(const DecParams *pp)
 {
+    const DecParams p = *pp;
+    const int nctas = (int)((p.nblocks / 6 + DEC_DC_THREADS - 1) / DEC_DC_THREADS);
     __shared__ int s_part[3][1024];
     const int tid = threadIdx.x;
     const int per = (nctas + 1023) / 1024;
@@ -493,8 +504,9 @@ __device__ __forceinline__ unsigned int dec_range_limit(int x)     // jdmaster.c
 }
 
 // one thread = one block: 64 coefficients (natural order) -> 8 x 8 samples of the block's plane
-__global__ void __launch_bounds__(128) k_dec_idct(const DecParams p)
+__global__ void __launch_bounds__(128) k_dec_idct(const DecParams *pp)
 {
+    const DecParams p = *pp;
     __shared__ short s_qt[3][64];
     for (int i = threadIdx.x; i < 192; i += blockDim.x) (&s_qt[0][0])[i] = (short)(&p.tab->qt[0][0])[i];
     __syncthreads();
@@ -558,8 +570,9 @@ __global__ void __launch_bounds__(128) k_dec_idct(const DecParams p)
 }
 
 // ---- jdsample.c h2v2_fancy_upsample + jdcolor.c ycc_rgb_convert: one thread = 8 pixels of a row ----------
-__global__ void __launch_bounds__(256) k_dec_color(const DecParams p)
+__global__ void __launch_bounds__(256) k_dec_color(const DecParams *pp)
 {
+    const DecParams p = *pp;
     const int x0 = (blockIdx.x * 32 + (threadIdx.x & 31)) * 8;
     const int y = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (x0 >= p.w || y >= p.h) return;

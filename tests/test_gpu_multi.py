@@ -59,3 +59,24 @@ def test_resident_images_run_on_the_gpu_that_holds_them(multi, oracle):
         assert (r.status, r.best_q, r.scale) == (rc, rq, rs)
         if rc == 0:
             assert bytes(out[:r.out_len]) == ref
+
+
+def test_native_executor_with_resident_images_on_every_gpu_never_waits_while_holding_tickets(multi, oracle):
+    """Four workers, three tickets each, items bound to the GPU that holds their image: the pattern that left every
+    worker waiting for a slot another waiting worker held (bench.py one_process_all_gpus, r02)."""
+    n_dev = multi.device_count
+    img = synth.natural_image(960, 640, 480)
+    rc, ref, rq, rs, _, _ = oracle.jpg_fit(img, 0.25, 16000)
+    handles = [multi.upload_image(img, d) for d in range(n_dev)]
+    n = 40 * n_dev
+    outs = [np.empty(16000, np.uint8) for _ in range(n)]
+    items = multi.make_items([dict(kind="jpg_fit_image", image=handles[i % n_dev], init_q=0.25, target=16000, out=outs[i])
+                              for i in range(n)])
+    for _ in range(5):
+        multi.run_list(items, threads=4, inflight=3)
+    for r, o in zip(items.results(), outs):
+        assert (r.status, r.best_q, r.scale) == (rc, rq, rs)
+        if rc == 0:
+            assert bytes(o[: r.out_len]) == ref
+    for hnd in handles:
+        multi.free_image(hnd)
