@@ -633,7 +633,9 @@ int enqueue_resize(icb_handle *h, Slot *s, const unsigned char *d_src, int w, in
     // (tw - 1) source steps plus the two outer taps, rounded out to 16-byte vectors -- fits the staging rows
     const int bpp = bpp_of(fmt);
     const double step = (double)w / dw;
-    int tl = 7;
+    static const int tl_max = [] { const char *e = getenv("ICB_RS_TL"); const int v = e ? atoi(e) : 7; return v >= 2 && v <= 7 ? v : 7; }();   // A/B knob
+    static const int cps_max = [] { const char *e = getenv("ICB_RS_CPS"); const int v = e ? atoi(e) : 6; return v >= 1 && v <= 8 ? v : 6; }();
+    int tl = tl_max;
     size_t seg = 0;
     for (; tl >= 2; tl--) {
         seg = round_up((size_t)(((1 << tl) - 1) * step + 3.0) * bpp + 32, 16);
@@ -662,7 +664,7 @@ int enqueue_resize(icb_handle *h, Slot *s, const unsigned char *d_src, int w, in
     rp.ntiles = rp.tiles_x * ((dh + RS_ROWS - 1) / RS_ROWS);
     const size_t smem = (size_t)resize_smem_bytes(rp.seg_bytes, tw, bpp);
     // persistent CTAs: as many as fit an SM by shared memory (at most 6), one wave
-    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(6, ((size_t)220 << 10) / smem));
+    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>((size_t)cps_max, ((size_t)220 << 10) / smem));
     const dim3 grid((unsigned)std::min(rp.ntiles, h->devs[s->devi].sms * per_sm));
     switch (fmt) {
     case ICB_FMT_RGBA8: case ICB_FMT_ARGB32: k_resize<4, 3><<<grid, RS_THREADS, smem, s->stream>>>(rp); break;

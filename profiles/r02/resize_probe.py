@@ -19,3 +19,10 @@ with pkg.Engine(devices=[0], slots_per_gpu=2) as eng:
             out["resize_plus_png_us"] = round(eng.profile_resize_series(hnd, dw, dh, 10, with_png=True) * 1e3, 1)
         print(json.dumps(out), flush=True)
         eng.free_image(hnd)
+        if c == 4:       # the same shape with an opaque alpha plane (photographs saved as RGBA): no premultiply / divide
+            img2 = img.copy(); img2[:, :, 3] = 255
+            hnd = eng.upload_image(img2, 0)
+            ms2 = eng.profile_resize_series(hnd, dw, dh, 30)
+            print(json.dumps({"src": [w, h, c], "dst": [dw, dh], "alpha": "opaque", "resize_us": round(ms2 * 1e3, 2),
+                              "gbs": round(touched / ms2 / 1e6, 1), "frac_of_measured_peak": round(touched / ms2 / 1e6 / peak, 3)}), flush=True)
+            eng.free_image(hnd)
