@@ -93,7 +93,22 @@ def _check_fit(fit, g):
             assert (best_q, scale) == (lq, ls)
 
 
+def _check_decode(decode, g):
+    if "decode" not in g:
+        pytest.xfail("jdk_golden.json predates the decode section: decoded-pixel parity unpinned")
+    for rec in g["decode"]:
+        data = bytes.fromhex(rec["file"])
+        px = decode(data)
+        assert px.shape == (rec["h"], rec["w"], 3)
+        assert _sha(px.tobytes()) == rec["sha256"], ("decoded raster differs from ImageIO's", rec["kind"], rec["w"], rec["h"], rec["k"])
+
+
 # ---- the oracle against the JDK (CPU suite) -------------------------------------------------------
+def test_oracle_decode_equals_imageio(oracle):
+    """core/ImageCompression.java:119-155: the reader the reference gets from ImageIO, on the JDK's own files"""
+    _check_decode(lambda data: oracle.jpeg_decode(data), _golden())
+
+
 def test_oracle_jpeg_bytes_equal_imageio(oracle):
     _check_jpeg(lambda img, q: oracle.encode(img, q), _golden())
 
@@ -133,3 +148,8 @@ def test_gpu_fit_equals_the_reference_loop(engine):
         r = engine.jpg_fit(img, q, target)
         return r.status, r.data, r.best_q, r.scale
     _check_fit(fit, _golden())
+
+
+@pytest.mark.gpu
+def test_gpu_decode_equals_imageio(engine):
+    _check_decode(lambda data: engine.jpg_decode(data), _golden())

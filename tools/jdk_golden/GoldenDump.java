@@ -175,6 +175,36 @@ public final class GoldenDump {
                     px.length <= 200000 ? "\"" + hex(px, px.length) + "\"" : "null"));
         }
         js.append("\n ],\n");
+        // ---- decode (SURVEY 8 f2): the files above read back the way core/ImageCompression.java:119-155 reads them
+        js.append(" \"decode\": [\n");
+        first = true;
+        String readerClass = "?";
+        for (String[] c : JPEG_CASES) {
+            int w = Integer.parseInt(c[1]), h = Integer.parseInt(c[2]);
+            BufferedImage img = image(c[0], w, h, 3);
+            for (int k : new int[] {32, 96, 118}) {
+                byte[] file = encode(img, k / 128.0f);
+                BufferedImage dec;
+                try (javax.imageio.stream.ImageInputStream in = ImageIO.createImageInputStream(new java.io.ByteArrayInputStream(file))) {
+                    javax.imageio.ImageReader reader = ImageIO.getImageReaders(in).next();
+                    readerClass = reader.getClass().getName();
+                    reader.setInput(in, true, true);
+                    dec = reader.read(0, reader.getDefaultReadParam());
+                    reader.dispose();
+                }
+                byte[] rgb = new byte[w * h * 3];
+                for (int y = 0, o = 0; y < h; y++)
+                    for (int x = 0; x < w; x++) {
+                        int p = dec.getRGB(x, y);
+                        rgb[o++] = (byte) (p >> 16); rgb[o++] = (byte) (p >> 8); rgb[o++] = (byte) p;
+                    }
+                if (!first) js.append(",\n");
+                first = false;
+                js.append(String.format("  {\"kind\": \"%s\", \"w\": %d, \"h\": %d, \"k\": %d, \"image_type\": %d, \"file\": \"%s\", \"sha256\": \"%s\"}",
+                        c[0], w, h, k, dec.getType(), hex(file, file.length), sha256(rgb)));
+            }
+        }
+        js.append("\n ],\n");
         // ---- the reference's own loop, when its jar is on the classpath
         js.append(" \"fit\": [\n");
         first = true;
@@ -213,8 +243,8 @@ public final class GoldenDump {
             // only the JDK-level vectors are written
         }
         js.append("\n ],\n");
-        js.append(String.format(" \"env\": {\"java_version\": \"%s\", \"java_vendor\": \"%s\", \"writer_class\": \"%s\", \"fit\": \"%s\"}\n}\n",
-                System.getProperty("java.version"), System.getProperty("java.vendor"), writerClass, fitNote));
+        js.append(String.format(" \"env\": {\"java_version\": \"%s\", \"java_vendor\": \"%s\", \"writer_class\": \"%s\", \"reader_class\": \"%s\", \"fit\": \"%s\"}\n}\n",
+                System.getProperty("java.version"), System.getProperty("java.vendor"), writerClass, readerClass, fitNote));
         try (PrintWriter pw = new PrintWriter(Files.newBufferedWriter(out, StandardCharsets.UTF_8))) {
             pw.print(js);
         }
