@@ -366,6 +366,37 @@ def leg_jpg(eng, pool, name, threads, inflight, peak_gbs):
                    "h2d_bytes_per_step": (st1["h2d_bytes"] - st0["h2d_bytes"]) / (steps_e + 1),
                    "d2h_bytes_per_step": (st1["d2h_bytes"] - st0["d2h_bytes"]) / (steps_e + 1)},
            "parity_check": "bit-exact vs oracle on image 0 (%d bytes, q=%.7f, scale=%.4f)" % (len(ref or b""), rq, rs)}
+    try:        # the same leg from JPEG files (decode on the GPU): what "100,000 synthetic 24MP JPGs" start from
+        import io
+        from PIL import Image
+        files = []
+        for im in imgs:
+            bio = io.BytesIO()
+            Image.fromarray(im).save(bio, "JPEG", quality=92, subsampling=2)
+            files.append(np.frombuffer(bio.getvalue(), np.uint8))
+        fpins = []
+        for f in files:
+            a = eng.alloc_pinned((f.size,))
+            a[:] = f
+            fpins.append(a)
+        items_f = eng.make_items([dict(kind="jpg_file_fit", file=fpins[i % len(fpins)], init_q=q, target=target, out=outs[i])
+                                  for i in range(n_e2e)])
+        eng.run_list(items_f, threads, inflight)
+        rf = items_f.results()[0]
+        px = O.jpeg_decode(files[0].tobytes())
+        rc2, ref2, rq2, rs2, _, _ = O.jpg_fit(px, q, target)
+        assert (rf.status, rf.best_q, rf.scale) == (rc2, rq2, rs2) and bytes(outs[0][: rf.out_len]) == ref2, name + " from files: differs from the oracle"
+        sf0 = eng.stats()
+        ms_f, steps_f = steps_for(eng, [0], lambda: eng.run_list(items_f, threads, inflight))
+        sf1 = eng.stats()
+        out["e2e_file"] = {"value": n_e2e / ms_f * 1e3 * mpx, "unit": "MP/s", "images_per_s": n_e2e / ms_f * 1e3,
+                           "h2d_bytes_per_step": (sf1["h2d_bytes"] - sf0["h2d_bytes"]) / (steps_f + 1),
+                           "file_bytes_mean": float(np.mean([f.size for f in files])),
+                           "parity_check": "bit-exact vs oracle decode + fit of file 0 (q=%.7f, scale=%.4f)" % (rq2, rs2)}
+        for a in fpins:
+            eng.free_pinned(a)
+    except Exception as e:
+        out["e2e_file"] = {"error": repr(e)}
     xf_ms, _ = eng.profile_transform_series(res, 3, list_q=q)
     nblocks = 6 * ((w + 15) // 16) * ((h + 15) // 16)
     xb = 3 * w * h + 128 * nblocks
@@ -493,6 +524,48 @@ def leg_mixed(eng, pool, threads, inflight):
            "note": "e2e only: value == e2e (pinned host pixels in, JFIF bytes / resized pixels out)",
            "roofline": None,
            "parity_check": "both cached JPG kinds bit-exact vs oracle (used_cache, bytes); every timed JPG used the cache"}
+    try:        # the same list with the JPG lines as FILES (decode on the GPU); the PNG lines stay decoded pixels
+        import io
+        from PIL import Image
+        fkinds = []
+        for (w, h) in [(4000, 3000), (6000, 4000)]:
+            img = pool[0] if w == 4000 else compose(pool, w, h, 3, 1)
+            bio = io.BytesIO()
+            Image.fromarray(img).save(bio, "JPEG", quality=92, subsampling=2)
+            fbytes = np.frombuffer(bio.getvalue(), np.uint8)
+            r = eng.jpg_file_fit(fbytes, q, target)                      # warm-up search on the decoded pixels
+            assert r.status == 0
+            lp = LearnedParams(r.best_q, r.scale)
+            px = O.jpeg_decode(fbytes.tobytes())
+            rc, ref, rq, rs, uc, _ = O.jpg_fit(px, q, target, cached=(lp.quality, lp.scale))
+            hit = eng.jpg_file_fit(fbytes, q, target, cached=lp)
+            assert (hit.status, hit.used_cache, hit.data) == (rc, bool(uc), ref) and uc, "cached file fit differs from the oracle"
+            fp = eng.alloc_pinned((fbytes.size,))
+            fp[:] = fbytes
+            fkinds.append((fp, lp))
+        lst_f, bytes_in = [], 0
+        for i, d in enumerate(lst):
+            if d["kind"] == "jpg_fit":
+                fp, lp = fkinds[order[i % len(order)]]
+                lst_f.append(dict(kind="jpg_file_fit", file=fp, init_q=q, target=target, cached=lp, out=d["out"]))
+            else:
+                lst_f.append(d)
+        items_f = eng.make_items(lst_f)
+        eng.run_list(items_f, threads, inflight)
+        sf0 = eng.stats()
+        ms_f, steps_f = steps_for(eng, [0], lambda: eng.run_list(items_f, threads, inflight), seconds=1.5)
+        sf1 = eng.stats()
+        rf = items_f.results()
+        assert all(x.status == 0 for x in rf)
+        assert all(x.used_cache for x, d in zip(rf, lst_f) if d["kind"] == "jpg_file_fit"), "a cached file fit fell back to the search"
+        out["e2e_file"] = {"value": mp_step / ms_f * 1e3, "unit": "MP/s", "images_per_s": n / ms_f * 1e3,
+                           "h2d_bytes_per_step": (sf1["h2d_bytes"] - sf0["h2d_bytes"]) / (steps_f + 1),
+                           "parity_check": "both cached JPG kinds from files bit-exact vs oracle decode + cached fit; every timed JPG used the cache",
+                           "note": "JPG lines as JPEG files decoded on the GPU, PNG lines as decoded RGBA pixels"}
+        for fp, _ in fkinds:
+            eng.free_pinned(fp)
+    except Exception as e:
+        out["e2e_file"] = {"error": repr(e)}
     for k in kinds:
         eng.free_pinned(k[1])
     for o in bufs:

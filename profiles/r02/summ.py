@@ -26,6 +26,8 @@ for src in (sys.argv[1:] or ["-"]):
                 print("   %s: value %.1f %s | e2e %.1f %s | roof %s %s | %s | %.1fs" % (
                     k, v["value"], v["unit"], v["e2e"]["value"], v["e2e"]["unit"], r.get("kernel"),
                     r.get("frac") and round(r["frac"], 3), v.get("parity_check", "")[:60], v.get("leg_wall_s", 0)))
+                if "e2e_file" in v:
+                    print("      e2e_file:", {a: (round(b, 1) if isinstance(b, float) else b) for a, b in v["e2e_file"].items()})
                 if "png_file" in v:
                     print("      png_file:", {a: b for a, b in v["png_file"].items() if a != "note"})
         if d.get("one_process"):
