@@ -102,8 +102,11 @@ class WorkItem:
     original file size; decode itself is input staging and stays on the host)."""
     index: int
     kind: str                 # "jpg" | "png"
-    pixels: object            # uint8 ndarray (h, w, 3|4)
+    pixels: object            # uint8 ndarray (h, w, 3|4); may be None for a "jpg" line that carries file_bytes
     original_size: int
+    file_bytes: object = None  # the JPEG file itself (bytes / uint8 ndarray): SURVEY 8 f2 -- lines whose file the GPU
+    #                            reader takes go up as files (core/ImageCompression.java:119-155 on the device) and
+    #                            need no host decode; every other line is decoded on the host into `pixels` as before
 
 
 class _Cursor:
@@ -201,6 +204,26 @@ def _run_queued(engine, lines, cursor, params, cache, on_output, inflight: int) 
         if len(pending) == inflight:
             finish()
         try:
+            if it.kind == "jpg" and it.file_bytes is not None and hasattr(engine, "submit_jpg_file_fit"):
+                from .api import jpg_file_info, subsample_factor
+                try:
+                    fw, fh = jpg_file_info(it.file_bytes)
+                except IcbError:
+                    fw = 0                                          # another kind of JPEG: the pixel path below
+                if fw:
+                    sf = subsample_factor(fw, fh)                   # decode rule :140-153 -> the dims the cache key sees
+                    key = create_key((fw + sf - 1) // sf, (fh + sf - 1) // sf, it.original_size)
+                    slot = free_outs.pop()
+                    try:
+                        t = engine.submit_jpg_file_fit(it.file_bytes, params.quality, target, jpg_outs[slot], cached=cache.get(key))
+                    except Exception:
+                        free_outs.append(slot)
+                        raise
+                    pending.append((it, "jpg", t, jpg_outs[slot], (key, slot)))
+                    continue
+                if it.pixels is None:
+                    c.add(FAILED_UNSUPPORTED_FORMAT, it.original_size, it.original_size)
+                    continue
             h, w = it.pixels.shape[:2]
             if it.kind == "jpg":
                 key = create_key(w, h, it.original_size)

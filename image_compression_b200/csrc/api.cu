@@ -108,7 +108,7 @@ struct Slot {
     DecJob *d_decjob = nullptr;         DecJob *h_decjob = nullptr;         // h_*: pinned
     DecState *d_decst = nullptr;        DecState *h_decst = nullptr;
     size_t dec_scan_cap = 0; int dec_w_cap = 0, dec_h_cap = 0;              // what the slot's decode graph is sized for
-    cudaGraphExec_t dec_graph = nullptr; uint64_t dec_graph_key = 0;
+    cudaGraphExec_t dec_graph = nullptr; uint64_t dec_graph_key = 0; bool dec_graph_broken = false;
     Geom geom{};
     bool busy = false;
     bool lone = false;                      // the job in flight found no other slot of its GPU busy (enqueue_transform)
@@ -2155,11 +2155,11 @@ void launch_decode_chain(Slot *s, cudaStream_t st, size_t sub_bytes_cap, size_t 
     k_dec_scan<<<nchunks_cap, 256, 0, st>>>(pp);
     k_dec_offsets<<<1, 1024, 0, st>>>(pp);
     k_dec_unstuff<<<nchunks_cap, 256, 0, st>>>(pp);
-    const unsigned int sgrid = (nsub_cap + 127) / 128;
+    const unsigned int sgrid = (nsub_cap + DEC_THREADS - 1) / DEC_THREADS;
     const int nrounds = dec_rounds();
-    for (int r = 0; r < nrounds; r++) k_dec_sync<<<sgrid, 128, 0, st>>>(pp, r == 0 ? 0 : DEC_ROUNDS - nrounds + r);
+    for (int r = 0; r < nrounds; r++) k_dec_sync<<<sgrid, DEC_THREADS, 0, st>>>(pp, r == 0 ? 0 : DEC_ROUNDS - nrounds + r);
     k_dec_blocks<<<1, 1024, 0, st>>>(pp);
-    k_dec_write<<<sgrid, 128, 0, st>>>(pp);
+    k_dec_write<<<sgrid, DEC_THREADS, 0, st>>>(pp);
     const size_t ndc = (nblocks_cap / 6 + DEC_DC_THREADS - 1) / DEC_DC_THREADS;
     k_dec_dc_local<<<(unsigned int)ndc, DEC_DC_THREADS, 0, st>>>(pp);
     k_dec_dc_cta<<<1, 1024, 0, st>>>(pp);
@@ -2235,7 +2235,7 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     rc = upload(h, s, s->d_file_in, (int)std::min<size_t>(n, 0x7fffffff), file, (int)n, 1, (int)n, 1);
     if (rc) return rc;
 
-    if (use_graph) {
+    if (use_graph && !s->dec_graph_broken) {
         // the graph stands for these buffers and capacities; anything else: capture again
         const uint64_t key = ((uint64_t)(uintptr_t)s->d_coef * 0x9E3779B97F4A7C15ull) ^ ((uint64_t)(uintptr_t)s->d_sub * 0xC2B2AE3D27D4EB4Full) ^
                              ((uint64_t)(uintptr_t)s->d_decst << 7) ^ ((uint64_t)scan_cap << 3) ^ ((uint64_t)wc << 40) ^ ((uint64_t)hc << 20) ^
@@ -2246,12 +2246,19 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
             CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
             launch_decode_chain(s, st, sub_bytes, nblocks_cap, nchunks_cap, nsub_cap, wc, hc);
             cudaError_t e = cudaStreamEndCapture(st, &g);
-            if (e != cudaSuccess || !g) return fail(h, ICB_ERR_CUDA, "decode graph capture", e);
-            e = cudaGraphInstantiate(&s->dec_graph, g, 0);
-            cudaGraphDestroy(g);
-            if (e != cudaSuccess) { s->dec_graph = nullptr; return fail(h, ICB_ERR_CUDA, "decode graph instantiate", e); }
+            if (e == cudaSuccess && g) {
+                e = cudaGraphInstantiate(&s->dec_graph, g, 0);
+                cudaGraphDestroy(g);
+            }
+            if (e != cudaSuccess || !s->dec_graph) {         // a driver that cannot capture this: plain launches from now on
+                cudaGetLastError();
+                s->dec_graph = nullptr;
+                s->dec_graph_broken = true;
+            }
             s->dec_graph_key = key;
         }
+    }
+    if (use_graph && !s->dec_graph_broken && s->dec_graph) {
         CK(cudaGraphLaunch(s->dec_graph, st));
     } else {
         launch_decode_chain(s, st, sub_bytes, nblocks_cap, nchunks_cap, nsub_cap, wc, hc);

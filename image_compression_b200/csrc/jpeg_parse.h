@@ -122,16 +122,16 @@ inline void jpeg_build_tables(const JpegHeader &hd, DecTables &t)
         for (int l = 1; l <= 16; l++) {
             t.valoff[tb][l] = k - code;
             for (int i = 0; i < hd.bits[tb][l - 1]; i++, k++, code++) {
-                const unsigned short ent = (unsigned short)((l << 8) | hd.vals[tb][k]);
+                const unsigned int ent = dec_entry(tb >> 1, (unsigned int)l, hd.vals[tb][k]);
                 if (l <= DEC_LUT_BITS) {
                     const int lo = code << (DEC_LUT_BITS - l), cnt = 1 << (DEC_LUT_BITS - l);
                     for (int j = 0; j < cnt && lo + j < (1 << DEC_LUT_BITS); j++) t.lut[tb][lo + j] = ent;
                 } else {
                     const int pre = code >> (l - DEC_LUT_BITS);
                     if (pre >= (1 << DEC_LUT_BITS)) continue;                     // an over-subscribed table: the loop's business
-                    unsigned short &slot = t.lut[tb][pre];
-                    if (slot == 0 && n2 < DEC_LUT2) slot = (unsigned short)(0xF000 | n2++);
-                    if (slot < 0xF000) continue;                                  // no second-level table left: the loop decodes it
+                    unsigned int &slot = t.lut[tb][pre];
+                    if (slot == 0 && n2 < DEC_LUT2) slot = 0x80000000u | (unsigned int)n2++;
+                    if (!(slot & 0x80000000u)) continue;                          // no second-level table left: the loop decodes it
                     const int sub = (code << (16 - l)) & 63, cnt = 1 << (16 - l);
                     for (int j = 0; j < cnt && sub + j < 64; j++) t.lut2[tb][slot & 0xff][sub + j] = ent;
                 }

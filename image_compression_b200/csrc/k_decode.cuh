@@ -40,15 +40,27 @@ constexpr int DEC_ROUNDS = 10;              // synchronisation rounds queued per
 constexpr int DEC_CARRY = 4;                // subsequences a thread carries on through per round
 constexpr int DEC_CHUNK = 4096;             // file bytes per CTA of the scan / unstuff kernels
 constexpr int DEC_LUT_BITS = 10;
+constexpr int DEC_THREADS = 256;            // threads (= subsequences) per CTA of the decode kernels: they share 34 KB of tables
 
-// Huffman decode tables of one file, built on the host (api.cu build_dec_tables): per table t = class * 2 + id
-// (0, 1 DC; 2, 3 AC) a look-up by the next DEC_LUT_BITS bits -> (length << 8) | symbol; 0xF000 | k = a longer code whose
-// next six bits index second-level table k; 0 = not in either (more than DEC_LUT2 long prefixes, or no such code):
-// jdhuff.c's maxcode / valoffset / huffval loop settles those.
 constexpr int DEC_LUT2 = 16;                // second-level tables per Huffman table (distinct 10-bit prefixes of long codes)
-struct DecTables {
-    unsigned short lut[4][1 << DEC_LUT_BITS];
-    unsigned short lut2[4][DEC_LUT2][64];   // codes of 11..16 bits: lut = 0xF000 | index, then the next six bits -> (length << 8) | symbol
+
+// One look-up entry says everything the decode loop needs about the symbol at the head of the window:
+//   [5:0]  bits to skip = code length + value bits      [12:6] how far the zigzag index moves: 1 for a DC symbol,
+//   [16:13] value bits (size)   [21:17] code length      run + 1 for a coefficient, 16 for ZRL, 64 for end of block
+// 0 = not in the table; 0x80000000 | k = a code longer than DEC_LUT_BITS whose next six bits index second-level table k.
+__host__ __device__ inline unsigned int dec_entry(int cls, unsigned int len, unsigned int sym)
+{
+    const unsigned int sz = sym & 15u, r = cls ? sym >> 4 : 0u;
+    const unsigned int zadv = cls == 0 ? 1u : (sz ? r + 1u : (r == 15u ? 16u : 64u));
+    return (len + sz) | (zadv << 6) | (sz << 13) | (len << 17);
+}
+
+// Huffman decode tables of one file, built on the host (jpeg_parse.h jpeg_build_tables): per table t = class * 2 + id
+// (0, 1 DC; 2, 3 AC) a look-up by the next DEC_LUT_BITS bits, second-level tables for the longer codes, and jdhuff.c's
+// maxcode / valoffset / huffval for whatever is in neither (more than DEC_LUT2 long prefixes, or no such code).
+struct alignas(16) DecTables {
+    unsigned int lut[4][1 << DEC_LUT_BITS];
+    unsigned int lut2[4][DEC_LUT2][64];
     int maxcode[4][18];
     int valoff[4][18];
     unsigned char huffval[4][256];
@@ -237,9 +249,9 @@ __constant__ unsigned char c_dec_zz[64] = {
     0, 1, 8, 16, 9, 2, 3, 10, 17, 24, 32, 25, 18, 11, 4, 5, 12, 19, 26, 33, 40, 48, 41, 34, 27, 20, 13, 6, 7, 14, 21, 28,
     35, 42, 49, 56, 57, 50, 43, 36, 29, 22, 15, 23, 30, 37, 44, 51, 58, 59, 52, 45, 38, 31, 39, 46, 53, 60, 61, 54, 47, 55, 62, 63};
 
-struct DecSmem {
-    unsigned short lut[4][1 << DEC_LUT_BITS];
-    unsigned short lut2[4][DEC_LUT2][64];
+struct alignas(16) DecSmem {
+    unsigned int lut[4][1 << DEC_LUT_BITS];
+    unsigned int lut2[4][DEC_LUT2][64];
     int maxcode[4][18];
     int valoff[4][18];
     unsigned char huffval[4][256];
@@ -249,14 +261,10 @@ struct DecSmem {
 
 __device__ __forceinline__ void dec_load_tables(DecSmem &s, const DecTables *t)
 {
-    const unsigned int *src = reinterpret_cast<const unsigned int *>(t->lut);
-    unsigned int *dst = reinterpret_cast<unsigned int *>(s.lut);
-    for (int i = threadIdx.x; i < 4 * (1 << DEC_LUT_BITS) / 2; i += blockDim.x) dst[i] = src[i];
-    {
-        const unsigned int *src2 = reinterpret_cast<const unsigned int *>(t->lut2);
-        unsigned int *dst2 = reinterpret_cast<unsigned int *>(s.lut2);
-        for (int i = threadIdx.x; i < 4 * DEC_LUT2 * 64 / 2; i += blockDim.x) dst2[i] = src2[i];
-    }
+    const uint4 *src = reinterpret_cast<const uint4 *>(t->lut);             // lut and lut2 are contiguous in both structs
+    uint4 *dst = reinterpret_cast<uint4 *>(s.lut);
+    constexpr int nvec = (4 * (1 << DEC_LUT_BITS) + 4 * DEC_LUT2 * 64) / 4;
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) dst[i] = src[i];
     for (int i = threadIdx.x; i < 4 * 18; i += blockDim.x) {
         (&s.maxcode[0][0])[i] = (&t->maxcode[0][0])[i];
         (&s.valoff[0][0])[i] = (&t->valoff[0][0])[i];
@@ -267,18 +275,17 @@ __device__ __forceinline__ void dec_load_tables(DecSmem &s, const DecTables *t)
     __syncthreads();
 }
 
-// one Huffman symbol of table tb at the head of `peek` (jdhuff.c jpeg_huff_decode): -> symbol, code length in len
-__device__ __forceinline__ unsigned int dec_symbol(const DecSmem &s, int tb, unsigned int peek, unsigned int &len)
+// the entry (dec_entry) of the symbol at the head of `peek` in table tb (jdhuff.c jpeg_huff_decode)
+__device__ __forceinline__ unsigned int dec_lookup(const DecSmem &s, unsigned int tb, unsigned int peek)
 {
     unsigned int e = s.lut[tb][peek >> (32 - DEC_LUT_BITS)];
-    if (e >= 0xF000u) e = s.lut2[tb][e & 0xffu][(peek >> (32 - DEC_LUT_BITS - 6)) & 63u];
-    if (e) { len = e >> 8; return e & 0xffu; }
+    if (e & 0x80000000u) e = s.lut2[tb][e & 0xffu][(peek >> (32 - DEC_LUT_BITS - 6)) & 63u];
+    if (e) return e;
     for (int l = DEC_LUT_BITS + 1; l <= 16; l++) {
         const int code = (int)(peek >> (32 - l));
-        if (code <= s.maxcode[tb][l]) { len = (unsigned int)l; return s.huffval[tb][(code + s.valoff[tb][l]) & 255]; }
+        if (code <= s.maxcode[tb][l]) return dec_entry((int)(tb >> 1), (unsigned int)l, s.huffval[tb][(code + s.valoff[tb][l]) & 255]);
     }
-    len = 16;                                                   // not a code: corrupt data, decoded as a zero like IJG
-    return 0;
+    return dec_entry((int)(tb >> 1), 16u, 0u);                  // not a code: corrupt data, decoded as a zero like IJG
 }
 
 // Decodes from state (pbit, bz = block-of-MCU * 64 + zigzag index) until a symbol starts at or after end_bit.
@@ -289,35 +296,29 @@ __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *b
                                         unsigned int nblocks, DecState *st)
 {
     unsigned int b = bz >> 6, z = bz & 63u;
+    unsigned int tdc = s.tab_dc[b], tac = s.tab_ac[b];          // the block's two tables (change once per block)
     DecBits br;
     br.open(bits, pbit);
     while (br.pos < end_bit) {
         if (WRITE && blk >= nblocks) break;
         const unsigned int peek = br.peek();
-        unsigned int len;
-        const bool dc = z == 0;
-        const unsigned int rs = dec_symbol(s, dc ? s.tab_dc[b] : s.tab_ac[b], peek, len);
-        const unsigned int sz = rs & 15u, r = dc ? 0u : rs >> 4;
-        // the value bits follow the code inside the same 32-bit window (jdhuff.c HUFF_EXTEND)
-        int v = 0;
-        if (WRITE && sz) {
-            const unsigned int rb = (peek << len) >> (32u - sz);
-            v = rb < (1u << (sz - 1)) ? (int)rb - (int)(1u << sz) + 1 : (int)rb;
+        const unsigned int e = dec_lookup(s, z == 0 ? tdc : tac, peek);
+        const unsigned int zadv = (e >> 6) & 127u;
+        if (WRITE) {
+            const unsigned int sz = (e >> 13) & 15u, at = z + zadv - 1u;     // (a DC symbol: z = 0, zadv = 1 -> 0)
+            if (sz && at < 64u) {
+                // the value bits follow the code inside the same 32-bit window (jdhuff.c HUFF_EXTEND)
+                const unsigned int rb = (peek << ((e >> 17) & 31u)) >> (32u - sz);
+                const int v = rb < (1u << (sz - 1)) ? (int)rb - (int)(1u << sz) + 1 : (int)rb;
+                coef[(size_t)blk * 64 + s.zz[at]] = (int16_t)v;
+            }
         }
-        br.skip(len + sz);
-        if (dc) {
-            if (WRITE) coef[(size_t)blk * 64] = (int16_t)v;
-            z = 1;
-        } else if (sz) {
-            z += r;
-            if (WRITE && z < 64) coef[(size_t)blk * 64 + s.zz[z]] = (int16_t)v;
-            z++;
-        } else {
-            z = r == 15u ? z + 16 : 64;                         // ZRL or end of block
-        }
-        if (z >= 64) {                                          // block complete
+        br.skip(e & 63u);
+        z += zadv;                                               // coefficient / ZRL / end of block (64) alike
+        if (z >= 64u) {                                          // block complete
             z = 0;
             b = b == 5 ? 0 : b + 1;
+            tdc = s.tab_dc[b]; tac = s.tab_ac[b];
             nblk++;
             blk++;
             if (WRITE && blk == nblocks) st->end_bit = br.pos;
@@ -331,7 +332,7 @@ __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *b
 // start of the scan) differs from the one its record was decoded from decodes its subsequence again and carries on
 // into the following ones -- at most DEC_CARRY of them per round -- until it meets a record that was decoded from
 // exactly the state it arrives with: from there on the records are already what this thread would write.
-__global__ void __launch_bounds__(128) k_dec_sync(const DecParams *pp, int round)
+__global__ void __launch_bounds__(DEC_THREADS) k_dec_sync(const DecParams *pp, int round)
 {
     const DecParams p = *pp;
     __shared__ DecSmem s;
@@ -387,7 +388,7 @@ __global__ void __launch_bounds__(1024) k_dec_blocks(const DecParams *pp)
     if (tid == 1023) p.st->blocks_found = s_part[1023];
 }
 
-__global__ void __launch_bounds__(128) k_dec_write(const DecParams *pp)
+__global__ void __launch_bounds__(DEC_THREADS) k_dec_write(const DecParams *pp)
 {
     const DecParams p = *pp;
     __shared__ DecSmem s;

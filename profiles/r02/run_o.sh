@@ -1,4 +1,4 @@
-# r02 call O: after the straight-line decode loop and the register-only colour kernel
+# r02 call O: decode tests, instruction counts per kernel of one file job, rate with 24 slots
 export ICB_POOL_CACHE=/tmp/icb_pool
 mkdir -p gpurun_out
 timeout 600 python -m pytest tests/test_gpu_decode.py -m gpu -x -q 2>&1 | tail -3
@@ -17,4 +17,4 @@ jobs = 3
 for k, d in agg.items():
     print("%-28s launches/job %5.1f  us/job %8.1f  Mwarp-inst/job %7.2f" % (k, d["n"] / jobs, d["ns"] / jobs / 1000, d["inst"] / jobs / 1e6))
 PY
-PROBE_SLOTS=24 timeout 600 python profiles/r02/decode_probe2.py 2>&1 | sed -n 2,3p
+PROBE_SLOTS=24 timeout 600 python profiles/r02/decode_probe2.py 2>&1 | sed -n 2,4p

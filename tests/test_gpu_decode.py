@@ -100,3 +100,28 @@ def test_file_items_in_the_native_executor(engine, oracle):
         assert (r.status, r.best_q, r.scale) == (rc, rq, rs) and (dw, dh) == (px.shape[1], px.shape[0])
         if rc == 0:
             assert bytes(o[: r.out_len]) == ref
+
+
+def test_run_shard_takes_file_lines_and_falls_back_to_pixels(engine, oracle):
+    """batch.run_shard (the CompressionBatch mirror): JPG lines that carry their file go up as files; a line whose file
+    is of another kind (here: 4:4:4) runs on its host-decoded pixels; results and learned cache equal the oracle's."""
+    from image_compression_b200 import batch
+    params = pkg.CompressionParams(0.25, 0, 100, 100, 30000)
+    items, expect = [], {}
+    for i in range(8):
+        img = synth.natural_image(700 + i, 800 + 32 * i, 600)
+        data = oracle.encode(img, 0.9)
+        px = oracle.jpeg_decode(data)
+        items.append(batch.WorkItem(i, "jpg", None, 102400 * (i + 2), file_bytes=data))
+        expect[i] = (px, 102400 * (i + 2))
+    px444 = synth.natural_image(720, 640, 480)
+    items.append(batch.WorkItem(8, "jpg", px444, 999999, file_bytes=Z["unsup_s444"].tobytes()))
+    expect[8] = (px444, 999999)
+    cache, outputs = {}, {}
+    c = batch.run_shard(engine, items, params, cache, threads=2, inflight_per_thread=2,
+                        on_output=lambda it, out: outputs.__setitem__(it.index, bytes(out)))
+    assert c.counts[batch.COMPRESSED_SUCCESS] == len(items)
+    for i, (px, size) in expect.items():
+        rc, ref, rq, rs, _, _ = oracle.jpg_fit(px, params.quality, params.target_max_size_bytes)
+        assert rc == 0 and outputs[i] == ref
+        assert cache[pkg.create_key(px.shape[1], px.shape[0], size)] == pkg.LearnedParams(rq, rs)
