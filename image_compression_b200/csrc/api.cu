@@ -107,7 +107,7 @@ struct Slot {
     unsigned char *d_dec = nullptr;     size_t dec_cap = 0;     // decoded raster when the decode rule subsamples it
     DecJob *d_decjob = nullptr;         DecJob *h_decjob = nullptr;         // h_*: pinned
     DecState *d_decst = nullptr;        DecState *h_decst = nullptr;
-    size_t dec_scan_cap = 0; int dec_w_cap = 0, dec_h_cap = 0;              // what the slot's decode graph is sized for
+    size_t dec_scan_cap = 0, dec_blocks_cap = 0; int dec_w_cap = 0, dec_h_cap = 0;              // what the slot's decode graph is sized for
     cudaGraphExec_t dec_graph = nullptr; uint64_t dec_graph_key = 0; bool dec_graph_broken = false;
     Geom geom{};
     bool busy = false;
@@ -2127,7 +2127,7 @@ int map_parse(icb_handle *h, int jp)
 {
     if (jp == JP_OK) return ICB_OK;
     if (jp == JP_UNSUPPORTED)
-        return fail(h, ICB_ERR_UNSUPPORTED, "JPEG reader takes baseline 8-bit YCbCr 4:2:0, one scan, no restart interval");
+        return fail(h, ICB_ERR_UNSUPPORTED, "JPEG reader takes baseline 8-bit YCbCr 4:2:0 / 4:2:2 / 4:4:4, one scan, no restart interval");
     return fail(h, ICB_ERR_INVALID, "not a JPEG file / truncated header");
 }
 
@@ -2144,7 +2144,7 @@ int dec_rounds()
 }
 
 void launch_decode_chain(Slot *s, cudaStream_t st, size_t sub_bytes_cap, size_t nblocks_cap, int nchunks_cap, unsigned int nsub_cap,
-                         int w_cap, int h_cap)
+                         int w_cap, int h_cap, int hs, int vs)
 {
     const DecParams *pp = &s->d_decjob->p;
     // state: everything zero, the scan ends at the end of the file unless a marker turns up earlier; no record yet
@@ -2160,11 +2160,14 @@ void launch_decode_chain(Slot *s, cudaStream_t st, size_t sub_bytes_cap, size_t 
     for (int r = 0; r < nrounds; r++) k_dec_sync<<<sgrid, DEC_THREADS, 0, st>>>(pp, r == 0 ? 0 : DEC_ROUNDS - nrounds + r);
     k_dec_blocks<<<1, 1024, 0, st>>>(pp);
     k_dec_write<<<sgrid, DEC_THREADS, 0, st>>>(pp);
-    const size_t ndc = (nblocks_cap / 6 + DEC_DC_THREADS - 1) / DEC_DC_THREADS;
+    const size_t ndc = (nblocks_cap / 3 + DEC_DC_THREADS - 1) / DEC_DC_THREADS;          // (an MCU has at least 3 blocks)
     k_dec_dc_local<<<(unsigned int)ndc, DEC_DC_THREADS, 0, st>>>(pp);
     k_dec_dc_cta<<<1, 1024, 0, st>>>(pp);
     k_dec_idct<<<(unsigned int)((nblocks_cap + 127) / 128), 128, 0, st>>>(pp);
-    k_dec_color<<<dim3((w_cap + 255) / 256, (h_cap + 7) / 8), 256, 0, st>>>(pp);
+    const dim3 cgrid((w_cap + 255) / 256, (h_cap + 7) / 8);
+    if (hs == 2 && vs == 2) k_dec_color<2, 2><<<cgrid, 256, 0, st>>>(pp);
+    else if (hs == 2) k_dec_color<2, 1><<<cgrid, 256, 0, st>>>(pp);
+    else k_dec_color<1, 1><<<cgrid, 256, 0, st>>>(pp);
 }
 
 // file bytes (host) -> decoded raster in d_out (pitch out_pitch, RGB8 or BGR8), all queued on the slot's stream
@@ -2172,8 +2175,9 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
                    int out_pitch, bool bgr)
 {
     cudaStream_t st = s->stream;
-    const int mcu_cols = (hd.w + 15) / 16, mcu_rows = (hd.h + 15) / 16;
-    const size_t nblocks = (size_t)mcu_cols * mcu_rows * 6;
+    const int nbm = hd.hs * hd.vs + 2;                                          // blocks per MCU
+    const int mcu_cols = (hd.w + 8 * hd.hs - 1) / (8 * hd.hs), mcu_rows = (hd.h + 8 * hd.vs - 1) / (8 * hd.vs);
+    const size_t nblocks = (size_t)mcu_cols * mcu_rows * nbm;
     const size_t scan_bytes = n - hd.scan_off;
     static const unsigned int sub_bits = [] {
         const char *e = getenv("ICB_DEC_SUB");
@@ -2187,7 +2191,8 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     // capacities of the slot: they only grow, in steps (1 MB of scan, 256 blocks of 16 pixels), so that slots settle
     const size_t scan_cap = std::max(s->dec_scan_cap, round_up(scan_bytes, (size_t)1 << 20));
     const int wc = std::max(s->dec_w_cap, (int)round_up((size_t)hd.w, 256)), hc = std::max(s->dec_h_cap, (int)round_up((size_t)hd.h, 256));
-    const size_t nblocks_cap = (size_t)((wc + 15) / 16) * ((hc + 15) / 16) * 6;
+    const size_t nblocks_cap = std::max(s->dec_blocks_cap,
+                                        (size_t)((wc + 8 * hd.hs - 1) / (8 * hd.hs)) * ((hc + 8 * hd.vs - 1) / (8 * hd.vs)) * nbm);
     const unsigned int nsub_cap = (unsigned int)std::min<size_t>((scan_cap * 8 + sub_bits - 1) / sub_bits, (1u << 17) - 1);
     const int nchunks_cap = (int)((scan_cap + DEC_CHUNK - 1) / DEC_CHUNK);
     if (!s->d_decjob) {
@@ -2200,14 +2205,14 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     int rc = ensure(h, s->d_file_in, s->file_in_cap, round_up(n, (size_t)1 << 20) + 256);
     if (!rc) rc = ensure(h, s->d_bits, s->bits_cap, scan_cap + 512);
     const size_t sub_bytes = round_up((size_t)nsub_cap * 8, 256);
-    const size_t nmcu_cap = nblocks_cap / 6, ndc_cap = (nmcu_cap + DEC_DC_THREADS - 1) / DEC_DC_THREADS;
+    const size_t nmcu_cap = nblocks_cap / 3, ndc_cap = (nmcu_cap + DEC_DC_THREADS - 1) / DEC_DC_THREADS;
     const size_t o_base = sub_bytes, o_chunk = o_base + round_up((size_t)nsub_cap * 4, 256);
     const size_t o_mcu = o_chunk + round_up((size_t)(nchunks_cap + 1) * 4, 256), o_cta = o_mcu + round_up(nmcu_cap * 12, 256);
     if (!rc) rc = ensure(h, s->d_sub, s->sub_cap, o_cta + round_up(ndc_cap * 12, 256));
     if (!rc) rc = ensure(h, s->d_planes, s->planes_cap, nblocks_cap * 64 + 256);
     if (!rc) rc = ensure(h, s->d_coef, s->coef_cap, nblocks_cap * 128);
     if (rc) return rc;
-    s->dec_scan_cap = scan_cap; s->dec_w_cap = wc; s->dec_h_cap = hc;
+    s->dec_scan_cap = scan_cap; s->dec_w_cap = wc; s->dec_h_cap = hc; s->dec_blocks_cap = nblocks_cap;
 
     DecJob &job = *s->h_decjob;
     jpeg_build_tables(hd, job.t);
@@ -2226,6 +2231,7 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     dp.planes = s->d_planes;
     dp.rgb = d_out; dp.rgb_pitch = out_pitch; dp.bgr = bgr ? 1 : 0;
     dp.w = hd.w; dp.h = hd.h; dp.mcu_cols = mcu_cols; dp.mcu_rows = mcu_rows;
+    dp.hs = hd.hs; dp.vs = hd.vs; dp.nb = nbm;
     dp.nblocks = (unsigned int)nblocks;
     dp.nsub_max = (unsigned int)((scan_bytes * 8 + sub_bits - 1) / sub_bits);
     dp.nchunks = (int)((scan_bytes + DEC_CHUNK - 1) / DEC_CHUNK);
@@ -2239,12 +2245,12 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
         // the graph stands for these buffers and capacities; anything else: capture again
         const uint64_t key = ((uint64_t)(uintptr_t)s->d_coef * 0x9E3779B97F4A7C15ull) ^ ((uint64_t)(uintptr_t)s->d_sub * 0xC2B2AE3D27D4EB4Full) ^
                              ((uint64_t)(uintptr_t)s->d_decst << 7) ^ ((uint64_t)scan_cap << 3) ^ ((uint64_t)wc << 40) ^ ((uint64_t)hc << 20) ^
-                             (uint64_t)dec_rounds();
+                             (uint64_t)dec_rounds() ^ ((uint64_t)(hd.hs * 4 + hd.vs) << 60) ^ ((uint64_t)nblocks_cap << 9);
         if (!s->dec_graph || s->dec_graph_key != key) {
             if (s->dec_graph) { cudaGraphExecDestroy(s->dec_graph); s->dec_graph = nullptr; }
             cudaGraph_t g = nullptr;
             CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
-            launch_decode_chain(s, st, sub_bytes, nblocks_cap, nchunks_cap, nsub_cap, wc, hc);
+            launch_decode_chain(s, st, sub_bytes, nblocks_cap, nchunks_cap, nsub_cap, wc, hc, hd.hs, hd.vs);
             cudaError_t e = cudaStreamEndCapture(st, &g);
             if (e == cudaSuccess && g) {
                 e = cudaGraphInstantiate(&s->dec_graph, g, 0);
@@ -2261,7 +2267,7 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     if (use_graph && !s->dec_graph_broken && s->dec_graph) {
         CK(cudaGraphLaunch(s->dec_graph, st));
     } else {
-        launch_decode_chain(s, st, sub_bytes, nblocks_cap, nchunks_cap, nsub_cap, wc, hc);
+        launch_decode_chain(s, st, sub_bytes, nblocks_cap, nchunks_cap, nsub_cap, wc, hc, hd.hs, hd.vs);
         CK(cudaGetLastError());
     }
     h->kernels += 9 + dec_rounds();

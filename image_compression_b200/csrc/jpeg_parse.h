@@ -1,6 +1,6 @@
 // jpeg_parse.h -- host side of the GPU JPEG reader (k_decode.cuh): marker parse of a JFIF file (jdmarker.c's
 // part of what core/ImageCompression.java:119-155 has ImageIO do) and the decode tables the kernels use.
-// Takes exactly what the kernels decode -- SOF0, 8 bit, three components sampled 2x2 / 1x1 / 1x1, 8-bit
+// Takes exactly what the kernels decode -- SOF0, 8 bit, three components, luma sampled 2x2 / 2x1 / 1x1 over 1x1 chroma, 8-bit
 // quantisation tables, one interleaved scan over the full spectrum, no restart interval -- and says
 // "unsupported" for everything else, so that the caller keeps the stock host decode for such files.
 #pragma once
@@ -17,6 +17,7 @@ enum { JP_OK = 0, JP_UNSUPPORTED = 1, JP_CORRUPT = 2 };
 
 struct JpegHeader {
     int w = 0, h = 0;
+    int hs = 2, vs = 2;                     // luma sampling factors: 2x2 (4:2:0), 2x1 (4:2:2) or 1x1 (4:4:4); chroma 1x1
     size_t scan_off = 0;                    // first entropy-coded byte
     int comp_tq[3] = {0, 0, 0}, comp_td[3] = {0, 0, 0}, comp_ta[3] = {0, 0, 0};
     unsigned char qt[4][64];                // zigzag order as stored in the file
@@ -78,7 +79,11 @@ inline int jpeg_parse(const uint8_t *f, size_t n, JpegHeader &hd)
             if (hd.w < 1 || hd.h < 1) return JP_UNSUPPORTED;
             for (int c = 0; c < 3; c++) {
                 comp_id[c] = s[6 + 3 * c];
-                if (s[7 + 3 * c] != (c == 0 ? 0x22 : 0x11)) return JP_UNSUPPORTED;     // 4:2:0 only
+                const int hv = s[7 + 3 * c];
+                if (c == 0) {
+                    if (hv != 0x22 && hv != 0x21 && hv != 0x11) return JP_UNSUPPORTED;     // 4:2:0, 4:2:2, 4:4:4
+                    hd.hs = hv >> 4; hd.vs = hv & 15;
+                } else if (hv != 0x11) return JP_UNSUPPORTED;
                 hd.comp_tq[c] = s[8 + 3 * c] & 3;
             }
             have_sof = true;
@@ -144,8 +149,9 @@ inline void jpeg_build_tables(const JpegHeader &hd, DecTables &t)
     }
     for (int c = 0; c < 3; c++)
         for (int i = 0; i < 64; i++) t.qt[c][zz[i]] = hd.qt[hd.comp_tq[c]][i];
-    for (int k = 0; k < 6; k++) {
-        const int c = k < 4 ? 0 : k - 3;
+    const int ny = hd.hs * hd.vs;
+    for (int k = 0; k < ny + 2; k++) {
+        const int c = k < ny ? 0 : k - ny + 1;
         t.tab_dc[k] = (unsigned char)hd.comp_td[c];
         t.tab_ac[k] = (unsigned char)(2 + hd.comp_ta[c]);
     }

@@ -1,7 +1,7 @@
 // k_decode.cuh -- SURVEY section 8 row f2 (input staging): the JPEG reader in front of the JPG seam, on the GPU.
 //
 // Replaces reader.read(0, param) of core/ImageCompression.java:119-155 for the files that make up the reference's
-// workload (baseline SOF0, 8 bit, YCbCr 4:2:0, one interleaved scan, no restart interval): the caller uploads the
+// workload (baseline SOF0, 8 bit, YCbCr 4:2:0 -- also 4:2:2 and 4:4:4 --, one interleaved scan, no restart interval): the caller uploads the
 // FILE (a few MB) instead of the decoded raster (36 MB for 12 MP), which is what bounds the end-to-end rate on a
 // PCIe link.  Anything else is refused on the host (ICB_ERR_UNSUPPORTED: the caller keeps the stock ImageIO decode).
 // Arithmetic = the JDK reader's libjavajpeg = IJG libjpeg 6b with its defaults [JDK-mem], restated in
@@ -91,10 +91,11 @@ struct DecParams {
     int *mcu_pref;                          // [mcus][3] DC differences in front of each MCU inside its CTA of k_dec_dc_local
     int *cta_pref;                          // [ceil(mcus / DEC_DC_THREADS)][3] ... and in front of that CTA
     int16_t *coef;                          // [nblocks][64] natural order
-    unsigned char *planes;                  // Y [mcu_rows * 16][mcu_cols * 16], then Cb, Cr [mcu_rows * 8][mcu_cols * 8]
+    unsigned char *planes;                  // Y [mcu_rows * 8 vs][mcu_cols * 8 hs], then Cb, Cr [mcu_rows * 8][mcu_cols * 8]
     unsigned char *rgb;                     // decoded raster
     int rgb_pitch, bgr;
     int w, h, mcu_cols, mcu_rows;
+    int hs, vs, nb;                         // luma sampling (2x2 4:2:0, 2x1 4:2:2, 1x1 4:4:4) and blocks per MCU = hs * vs + 2
     unsigned int nblocks;
     unsigned int nsub_max;                  // subsequences the file could hold at most
     int nchunks;                            // DEC_CHUNK-byte pieces of the file from scan_off on
@@ -293,7 +294,7 @@ __device__ __forceinline__ unsigned int dec_lookup(const DecSmem &s, unsigned in
 template <bool WRITE>
 __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *bits, unsigned int &pbit, unsigned int &bz,
                                         unsigned int &nblk, unsigned int end_bit, int16_t *coef, unsigned int blk,
-                                        unsigned int nblocks, DecState *st)
+                                        unsigned int nblocks, DecState *st, unsigned int last_b)
 {
     unsigned int b = bz >> 6, z = bz & 63u;
     unsigned int tdc = s.tab_dc[b], tac = s.tab_ac[b];          // the block's two tables (change once per block)
@@ -317,7 +318,7 @@ __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *b
         z += zadv;                                               // coefficient / ZRL / end of block (64) alike
         if (z >= 64u) {                                          // block complete
             z = 0;
-            b = b == 5 ? 0 : b + 1;
+            b = b == last_b ? 0 : b + 1;
             tdc = s.tab_dc[b]; tac = s.tab_ac[b];
             nblk++;
             blk++;
@@ -356,7 +357,7 @@ __global__ void __launch_bounds__(DEC_THREADS) k_dec_sync(const DecParams *pp, i
         if (k > i && dec_rec_entry(p.rec[k]) == entry) break;   // joined what is already recorded
         const unsigned int start = k * S, end = min(start + S, total_bits);
         unsigned int pbit = start + (entry >> 9), bz = entry & 0x1ffu, nblk = 0;
-        dec_run<false>(s, p.bits, pbit, bz, nblk, end, nullptr, 0, 0, nullptr);
+        dec_run<false>(s, p.bits, pbit, bz, nblk, end, nullptr, 0, 0, nullptr, (unsigned int)p.nb - 1u);
         const unsigned int exit_ = (min(pbit - end, 63u) << 9) | bz;
         atomicMin(&p.rec[k], dec_rec(round, i, entry, exit_, nblk));
         entry = exit_;
@@ -401,7 +402,7 @@ __global__ void __launch_bounds__(DEC_THREADS) k_dec_write(const DecParams *pp)
     const unsigned int entry = dec_rec_entry(p.rec[i]);
     unsigned int pbit = start + (entry >> 9), bz = entry & 0x1ffu, nblk = 0;
     const unsigned int end = min(start + S, total_bits);
-    dec_run<true>(s, p.bits, pbit, bz, nblk, end, p.coef, p.blk_base[i], p.nblocks, p.st);
+    dec_run<true>(s, p.bits, pbit, bz, nblk, end, p.coef, p.blk_base[i], p.nblocks, p.st, (unsigned int)p.nb - 1u);
 }
 
 // ---- DC differences -> DC values (jdhuff.c last_dc_val): per component a prefix over the MCUs --------------
@@ -414,15 +415,16 @@ __global__ void __launch_bounds__(DEC_DC_THREADS) k_dec_dc_local(const DecParams
 {
     const DecParams p = *pp;
     __shared__ int s_w[3][DEC_DC_THREADS / 32];
-    const unsigned int nm = p.nblocks / 6;
+    const unsigned int nm = p.nblocks / (unsigned int)p.nb;
     const unsigned int m = blockIdx.x * DEC_DC_THREADS + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ny = p.nb - 2;
     int v[3] = {0, 0, 0};
     if (m < nm) {
-        const int16_t *c = p.coef + (size_t)m * 6 * 64;
-        v[0] = c[0] + c[64] + c[128] + c[192];
-        v[1] = c[256];
-        v[2] = c[320];
+        const int16_t *c = p.coef + (size_t)m * p.nb * 64;
+        for (int j = 0; j < ny; j++) v[0] += c[64 * j];
+        v[1] = c[64 * ny];
+        v[2] = c[64 * ny + 64];
     }
     int incl[3];
 #pragma unroll
@@ -449,7 +451,7 @@ __global__ void __launch_bounds__(DEC_DC_THREADS) k_dec_dc_local(const DecParams
 __global__ void __launch_bounds__(1024) k_dec_dc_cta(const DecParams *pp)
 {
     const DecParams p = *pp;
-    const int nctas = (int)((p.nblocks / 6 + DEC_DC_THREADS - 1) / DEC_DC_THREADS);
+    const int nctas = (int)((p.nblocks / (unsigned int)p.nb + DEC_DC_THREADS - 1) / DEC_DC_THREADS);
     __shared__ int s_part[3][1024];
     const int tid = threadIdx.x;
     const int per = (nctas + 1023) / 1024;
@@ -513,18 +515,20 @@ __global__ void __launch_bounds__(128) k_dec_idct(const DecParams *pp)
     __syncthreads();
     const unsigned int blk = blockIdx.x * blockDim.x + threadIdx.x;
     if (blk >= p.nblocks) return;
-    const unsigned int m = blk / 6, k = blk - m * 6;
+    const unsigned int nbm = (unsigned int)p.nb, ny = nbm - 2u;
+    const unsigned int m = blk / nbm, k = blk - m * nbm;
     const int mx = (int)(m % (unsigned int)p.mcu_cols), my = (int)(m / (unsigned int)p.mcu_cols);
-    const int comp = k < 4 ? 0 : (int)k - 3;
-    const int yw = p.mcu_cols * 16, cw = p.mcu_cols * 8;
+    const int comp = k < ny ? 0 : (int)(k - ny) + 1;
+    const int yw = p.mcu_cols * 8 * p.hs, cw = p.mcu_cols * 8;
     unsigned char *dst;
     int pitch;
-    if (k < 4) {
-        dst = p.planes + (size_t)(my * 16 + (int)(k >> 1) * 8) * yw + mx * 16 + (int)(k & 1) * 8;
+    if (k < ny) {
+        const int ky = p.hs == 2 ? (int)(k >> 1) : (int)k, kx = p.hs == 2 ? (int)(k & 1u) : 0;     // (hs == 1: one block column)
+        dst = p.planes + (size_t)(my * 8 * p.vs + (p.vs == 2 ? ky : 0) * 8) * yw + mx * 8 * p.hs + kx * 8;
         pitch = yw;
     } else {
-        const size_t ysz = (size_t)yw * p.mcu_rows * 16, csz = (size_t)cw * p.mcu_rows * 8;
-        dst = p.planes + ysz + (k == 5 ? csz : 0) + (size_t)(my * 8) * cw + mx * 8;
+        const size_t ysz = (size_t)yw * p.mcu_rows * 8 * p.vs, csz = (size_t)cw * p.mcu_rows * 8;
+        dst = p.planes + ysz + (k == ny + 1u ? csz : 0) + (size_t)(my * 8) * cw + mx * 8;
         pitch = cw;
     }
     const uint4 *src = reinterpret_cast<const uint4 *>(p.coef + (size_t)blk * 64);
@@ -543,8 +547,8 @@ __global__ void __launch_bounds__(128) k_dec_idct(const DecParams *pp)
     }
     {   // DC value = differences of every earlier block of the component + its own (stored back as the JCOEF short)
         int dc = p.cta_pref[(size_t)(m / DEC_DC_THREADS) * 3 + comp] + p.mcu_pref[(size_t)m * 3 + comp];
-        const int16_t *mc = p.coef + (size_t)m * 6 * 64;
-        if (k < 4) { for (unsigned int j = 0; j <= k; j++) dc += mc[64 * j]; }
+        const int16_t *mc = p.coef + (size_t)m * nbm * 64;
+        if (k < ny) { for (unsigned int j = 0; j <= k; j++) dc += mc[64 * j]; }
         else dc += mc[64 * k];
         cf[0] = (short)dc;
     }
@@ -571,30 +575,47 @@ __global__ void __launch_bounds__(128) k_dec_idct(const DecParams *pp)
 }
 
 // ---- jdsample.c h2v2_fancy_upsample + jdcolor.c ycc_rgb_convert: one thread = 8 pixels of a row ----------
+// HS, VS = luma sampling: 2,2 h2v2 fancy (context rows); 2,1 h2v1 fancy; 1,1 no upsampling (fullsize_upsample)
+template <int HS, int VS>
 __global__ void __launch_bounds__(256) k_dec_color(const DecParams *pp)
 {
     const DecParams p = *pp;
     const int x0 = (blockIdx.x * 32 + (threadIdx.x & 31)) * 8;
     const int y = blockIdx.y * 8 + (threadIdx.x >> 5);
     if (x0 >= p.w || y >= p.h) return;
-    const int yw = p.mcu_cols * 16, cw = p.mcu_cols * 8;
-    const size_t ysz = (size_t)yw * p.mcu_rows * 16, csz = (size_t)cw * p.mcu_rows * 8;
+    const int yw = p.mcu_cols * 8 * HS, cw = p.mcu_cols * 8;
+    const size_t ysz = (size_t)yw * p.mcu_rows * 8 * VS, csz = (size_t)cw * p.mcu_rows * 8;
     const unsigned char *Y = p.planes + (size_t)y * yw + x0;
-    const int dsw = (p.w + 1) >> 1, dsh = (p.h + 1) >> 1;
-    const int cy = y >> 1;
+    const int dsw = (p.w + HS - 1) / HS, dsh = (p.h + VS - 1) / VS;
+    const int cy = VS == 2 ? y >> 1 : y;
     int cn = (y & 1) ? cy + 1 : cy - 1;                      // jdmainct.c context rows: clamped to the real rows
     cn = max(0, min(cn, dsh - 1));
     const bool fancy = dsw > 2;
-    const int cx0 = x0 >> 1;
+    const int cx0 = HS == 2 ? x0 >> 1 : x0;
     int cb[8], cr[8];
 #pragma unroll
     for (int pl = 0; pl < 2; pl++) {
         const unsigned char *P = p.planes + ysz + (pl ? csz : 0);
         const unsigned char *r0 = P + (size_t)cy * cw, *r1 = P + (size_t)cn * cw;
         int *res = pl ? cr : cb;
-        if (!fancy) {
+        if (HS == 1) {
+#pragma unroll
+            for (int i = 0; i < 8; i++) res[i] = r0[min(cx0 + i, cw - 1)];
+        } else if (!fancy) {
 #pragma unroll
             for (int i = 0; i < 8; i++) res[i] = r0[min(cx0 + (i >> 1), cw - 1)];
+        } else if (VS == 1) {
+            // jdsample.c h2v1_fancy_upsample: 3/4 of the nearer sample + 1/4 of the further one, rounding 1 towards the left
+            // neighbour and 2 towards the right; the first and the last output column copy their sample
+            int sv[6];
+#pragma unroll
+            for (int j = 0; j < 6; j++) sv[j] = r0[min(max(cx0 - 1 + j, 0), cw - 1)];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int cx = cx0 + j, cur = sv[j + 1];
+                res[2 * j] = cx == 0 ? cur : (3 * cur + sv[j] + 1) >> 2;
+                res[2 * j + 1] = cx == dsw - 1 ? cur : (3 * cur + sv[j + 2] + 2) >> 2;
+            }
         } else {
             int sum[6];                                       // 3 * cur + near for columns cx0 - 1 .. cx0 + 4
 #pragma unroll

@@ -16,7 +16,8 @@
  * files written at several sizes and qualities, tests/golden/jpeg_decode.npz (tests/golden/make_golden_decode.py).
  * Against a real JDK the decoded pixels are "parity unpinned" like every other [JDK-mem] fact.
  *
- * Scope = what the CUDA decoder takes: SOF0, 8 bits, 3 components sampled 2x2 / 1x1 / 1x1, one
+ * Scope = what the CUDA decoder takes: SOF0, 8 bits, 3 components, luma sampled 2x2 (4:2:0), 2x1 (4:2:2) or 1x1
+ * (4:4:4) with 1x1 chroma, one
  * interleaved scan, no restart interval.  Everything else returns ORC_DEC_UNSUPPORTED: the caller keeps
  * the stock host decode for such files.
  */
@@ -28,6 +29,7 @@
 typedef struct {
     int w, h;
     int mcu_cols, mcu_rows;
+    int hs, vs;                         /* luma sampling factors: 2x2 (4:2:0), 2x1 (4:2:2), 1x1 (4:4:4) */
     unsigned short qt[4][64];           /* natural order */
     int qt_set[4];
     /* jdhuff.c derived tables */
@@ -109,7 +111,10 @@ static int parse_headers(const uint8_t *f, size_t n, dec_t *d)
             for (int c = 0; c < 3; c++) {
                 comp_id[c] = s[6 + 3 * c];
                 const int hv = s[7 + 3 * c];
-                if (hv != (c == 0 ? 0x22 : 0x11)) return ORC_DEC_UNSUPPORTED;
+                if (c == 0) {
+                    if (hv != 0x22 && hv != 0x21 && hv != 0x11) return ORC_DEC_UNSUPPORTED;
+                    d->hs = hv >> 4; d->vs = hv & 15;
+                } else if (hv != 0x11) return ORC_DEC_UNSUPPORTED;
                 d->comp_tq[c] = s[8 + 3 * c] & 3;
             }
             have_sof = 1;
@@ -131,8 +136,8 @@ static int parse_headers(const uint8_t *f, size_t n, dec_t *d)
             }
             if (s[7] != 0 || s[8] != 63 || s[9] != 0) return ORC_DEC_UNSUPPORTED;
             d->scan_off = p + len;
-            d->mcu_cols = (d->w + 15) / 16;
-            d->mcu_rows = (d->h + 15) / 16;
+            d->mcu_cols = (d->w + 8 * d->hs - 1) / (8 * d->hs);
+            d->mcu_rows = (d->h + 8 * d->vs - 1) / (8 * d->vs);
             return ORC_DEC_OK;
         }
         p += len;
@@ -279,7 +284,8 @@ int orc_jpeg_info(const uint8_t *file, size_t n, int *w, int *h)
 }
 
 /* Coefficients as the Huffman decoder leaves them (DC prediction undone, NOT dequantised): MCU-interleaved
- * block order Y00 Y01 Y10 Y11 Cb Cr, 64 int16 per block in NATURAL order.  out holds 64 * 6 * mcus entries. */
+ * block order (4:2:0: Y00 Y01 Y10 Y11 Cb Cr; 4:2:2: Y0 Y1 Cb Cr; 4:4:4: Y Cb Cr), 64 int16 per block in NATURAL
+ * order.  out holds 64 * blocks-per-MCU * mcus entries. */
 int orc_jpeg_decode_coefficients(const uint8_t *file, size_t n, int16_t *out)
 {
     dec_t d;
@@ -288,11 +294,22 @@ int orc_jpeg_decode_coefficients(const uint8_t *file, size_t n, int16_t *out)
     bits_t b = {file, n, d.scan_off, 0, 0, 0};
     int last_dc[3] = {0, 0, 0};
     const long nm = (long)d.mcu_cols * d.mcu_rows;
+    const int ny = d.hs * d.vs, nb = ny + 2;
     for (long m = 0; m < nm; m++)
-        for (int k = 0; k < 6; k++) {
-            const int comp = k < 4 ? 0 : k - 3;
-            decode_block(&b, &d, comp, &last_dc[comp], out + (m * 6 + k) * 64);
+        for (int k = 0; k < nb; k++) {
+            const int comp = k < ny ? 0 : k - ny + 1;
+            decode_block(&b, &d, comp, &last_dc[comp], out + (m * nb + k) * 64);
         }
+    return ORC_DEC_OK;
+}
+
+int orc_jpeg_sampling(const uint8_t *file, size_t n, int *hs, int *vs)
+{
+    dec_t d;
+    const int rc = parse_headers(file, n, &d);
+    if (rc) return rc;
+    if (hs) *hs = d.hs;
+    if (vs) *vs = d.vs;
     return ORC_DEC_OK;
 }
 
@@ -302,35 +319,49 @@ int orc_jpeg_decode(const uint8_t *file, size_t n, int fmt, uint8_t *dst, int dp
     int rc = parse_headers(file, n, &d);
     if (rc) return rc;
     if (fmt != ORC_FMT_RGB8 && fmt != ORC_FMT_BGR8) return ORC_DEC_UNSUPPORTED;
-    const int yw = d.mcu_cols * 16, yh = d.mcu_rows * 16, cw = d.mcu_cols * 8, ch = d.mcu_rows * 8;
+    const int yw = d.mcu_cols * 8 * d.hs, yh = d.mcu_rows * 8 * d.vs, cw = d.mcu_cols * 8, ch = d.mcu_rows * 8;
     const long nm = (long)d.mcu_cols * d.mcu_rows;
-    int16_t *coef = (int16_t *)malloc((size_t)nm * 6 * 64 * sizeof(int16_t));
+    const int ny = d.hs * d.vs, nb = ny + 2;
+    int16_t *coef = (int16_t *)malloc((size_t)nm * nb * 64 * sizeof(int16_t));
     unsigned char *Y = (unsigned char *)malloc((size_t)yw * yh), *Cb = (unsigned char *)malloc((size_t)cw * ch),
                   *Cr = (unsigned char *)malloc((size_t)cw * ch);
     if (!coef || !Y || !Cb || !Cr) { free(coef); free(Y); free(Cb); free(Cr); return ORC_DEC_CORRUPT; }
     rc = orc_jpeg_decode_coefficients(file, n, coef);
     for (long m = 0; m < nm && !rc; m++) {
         const int mx = (int)(m % d.mcu_cols), my = (int)(m / d.mcu_cols);
-        for (int k = 0; k < 4; k++)
-            idct_islow(coef + (m * 6 + k) * 64, d.qt[d.comp_tq[0]], Y + (size_t)(my * 16 + (k >> 1) * 8) * yw + mx * 16 + (k & 1) * 8, yw);
-        idct_islow(coef + (m * 6 + 4) * 64, d.qt[d.comp_tq[1]], Cb + (size_t)(my * 8) * cw + mx * 8, cw);
-        idct_islow(coef + (m * 6 + 5) * 64, d.qt[d.comp_tq[2]], Cr + (size_t)(my * 8) * cw + mx * 8, cw);
+        for (int k = 0; k < ny; k++)
+            idct_islow(coef + (m * nb + k) * 64, d.qt[d.comp_tq[0]],
+                       Y + (size_t)(my * 8 * d.vs + (k / d.hs) * 8) * yw + mx * 8 * d.hs + (k % d.hs) * 8, yw);
+        idct_islow(coef + (m * nb + ny) * 64, d.qt[d.comp_tq[1]], Cb + (size_t)(my * 8) * cw + mx * 8, cw);
+        idct_islow(coef + (m * nb + ny + 1) * 64, d.qt[d.comp_tq[2]], Cr + (size_t)(my * 8) * cw + mx * 8, cw);
     }
-    /* jdsample.c: fancy h2v2 only when the downsampled width exceeds 2, else pixel replication (h2v2_upsample) */
-    const int dsw = (d.w + 1) / 2, dsh = (d.h + 1) / 2;
+    /* jdsample.c jinit_upsampler: h2v2 / h2v1 fancy only when the downsampled width exceeds 2, else pixel
+     * replication (h2v2_upsample / h2v1_upsample); 1x1: fullsize_upsample */
+    const int dsw = (d.w + d.hs - 1) / d.hs, dsh = (d.h + d.vs - 1) / d.vs;
     const int fancy = dsw > 2;
     for (int y = 0; y < d.h && !rc; y++) {
-        const int cy = y >> 1;
-        /* jdmainct.c context rows: above the first / below the last real row = that row */
+        const int cy = d.vs == 2 ? y >> 1 : y;
+        /* h2v2: jdmainct.c context rows: above the first / below the last real row = that row */
         int cn = (y & 1) ? cy + 1 : cy - 1;
         if (cn < 0) cn = 0;
         if (cn > dsh - 1) cn = dsh - 1;
         for (int x = 0; x < d.w; x++) {
-            const int cx = x >> 1;
+            const int cx = d.hs == 2 ? x >> 1 : x;
             int cbv, crv;
-            if (!fancy) {
+            if (d.hs == 1 || !fancy) {
                 cbv = Cb[(size_t)cy * cw + cx];
                 crv = Cr[(size_t)cy * cw + cx];
+            } else if (d.vs == 1) {
+                /* h2v1_fancy_upsample: 3/4 nearer + 1/4 further sample, rounding 1 (left neighbour) / 2 (right);
+                 * the first and the last output column copy their sample */
+                const unsigned char *planes[2] = {Cb, Cr};
+                int res[2];
+                for (int pl = 0; pl < 2; pl++) {
+                    const unsigned char *r0 = planes[pl] + (size_t)cy * cw;
+                    if (!(x & 1)) res[pl] = cx == 0 ? r0[0] : (3 * r0[cx] + r0[cx - 1] + 1) >> 2;
+                    else res[pl] = cx == dsw - 1 ? r0[cx] : (3 * r0[cx] + r0[cx + 1] + 2) >> 2;
+                }
+                cbv = res[0]; crv = res[1];
             } else {
                 const unsigned char *planes[2] = {Cb, Cr};
                 int res[2];

@@ -109,10 +109,11 @@ int orc_subsample(const uint8_t *src, int w, int h, int pitch, int bpp, int s,
                   uint8_t *dst, int dpitch);
 
 /* f2 (input staging): the JPEG reader of core/ImageCompression.java:119-155 for the files the CUDA decoder
- * takes (baseline SOF0, 8 bit, YCbCr 4:2:0, one scan, no restart interval) -- jpeg_decode_oracle.c. */
+ * takes (baseline SOF0, 8 bit, YCbCr 4:2:0 / 4:2:2 / 4:4:4, one scan, no restart interval) -- jpeg_decode_oracle.c. */
 enum { ORC_DEC_OK = 0, ORC_DEC_UNSUPPORTED = -4, ORC_DEC_CORRUPT = -1 };
 int orc_jpeg_info(const uint8_t *file, size_t n, int *w, int *h);
 int orc_jpeg_decode_coefficients(const uint8_t *file, size_t n, int16_t *out);
+int orc_jpeg_sampling(const uint8_t *file, size_t n, int *hs, int *vs);
 int orc_jpeg_decode(const uint8_t *file, size_t n, int fmt, uint8_t *dst, int dpitch);
 
 /* a7: ImageCompressionPng.java:49-61.  Returns 0 and the new dims when a resize

@@ -93,6 +93,7 @@ def lib():
         L.orc_jpeg_info.argtypes = [u8p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]
         L.orc_jpeg_decode_coefficients.argtypes = [u8p, C.c_size_t, i16p]
         L.orc_jpeg_decode.argtypes = [u8p, C.c_size_t, C.c_int, u8p, C.c_int]
+        L.orc_jpeg_sampling.argtypes = [u8p, C.c_size_t, C.POINTER(C.c_int), C.POINTER(C.c_int)]
     return _lib
 
 
@@ -250,7 +251,9 @@ def jpeg_decode_coefficients(data: bytes) -> np.ndarray:
     """Huffman-decoded coefficients, [6 * mcus][64] int16, natural order, DC prediction undone, not dequantised."""
     w, h = jpeg_info(data)
     buf = np.frombuffer(data, np.uint8)
-    nb = 6 * ((w + 15) // 16) * ((h + 15) // 16)
+    hs, vs = C.c_int(0), C.c_int(0)
+    lib().orc_jpeg_sampling(_u8(buf), buf.size, C.byref(hs), C.byref(vs))
+    nb = (hs.value * vs.value + 2) * ((w + 8 * hs.value - 1) // (8 * hs.value)) * ((h + 8 * vs.value - 1) // (8 * vs.value))
     out = np.empty((nb, 64), np.int16)
     rc = lib().orc_jpeg_decode_coefficients(_u8(buf), buf.size, out.ctypes.data_as(C.POINTER(C.c_int16)))
     if rc:

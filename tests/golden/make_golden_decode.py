@@ -17,6 +17,12 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
 from image_compression_b200 import synth  # noqa: E402
 
+# (seed, w, h, quality, kind, Pillow subsampling: 2 = 4:2:0, 1 = 4:2:2, 0 = 4:4:4)
+CASES_OTHER = [(53, 97, 61, 92, "natural", 1), (54, 200, 133, 75, "natural", 1), (55, 16, 8, 95, "noise", 1), (56, 5, 7, 92, "natural", 1),
+               (57, 3, 3, 92, "natural", 1), (58, 333, 100, 50, "natural", 1),
+               (59, 97, 61, 92, "natural", 0), (60, 200, 133, 75, "natural", 0), (61, 8, 8, 98, "noise", 0), (62, 5, 7, 92, "natural", 0),
+               (63, 131, 77, 30, "natural", 0)]
+
 CASES = [  # (seed, w, h, quality, kind)
     (41, 64, 48, 92, "natural"), (42, 101, 75, 92, "natural"), (43, 200, 133, 75, "natural"),
     (44, 17, 9, 92, "natural"), (45, 333, 251, 50, "natural"), (46, 16, 16, 98, "noise"),
@@ -42,10 +48,18 @@ def main():
         assert dec.shape == (h, w, 3)
         out[f"file_{i}"] = np.frombuffer(data, np.uint8)
         out[f"pixels_{i}"] = dec
-    # files the decoder must refuse (the caller keeps the stock host decode): progressive, 4:4:4, restart interval, gray
+    for j, (seed, w, h, q, kind, sub) in enumerate(CASES_OTHER):
+        img = make(seed, w, h, kind)
+        bio = io.BytesIO()
+        Image.fromarray(img).save(bio, "JPEG", quality=q, subsampling=sub, optimize=(j % 2 == 1))
+        data = bio.getvalue()
+        dec = np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))
+        out[f"file_{len(CASES) + j}"] = np.frombuffer(data, np.uint8)
+        out[f"pixels_{len(CASES) + j}"] = dec
+    # files the decoder must refuse (the caller keeps the stock host decode): progressive, restart interval, gray
     img = make(60, 48, 32, "natural")
-    for name, kw in (("progressive", dict(progressive=True, subsampling=2)), ("s444", dict(subsampling=0)),
-                     ("s422", dict(subsampling=1)), ("restart", dict(subsampling=2, restart_marker_rows=1))):
+    for name, kw in (("progressive", dict(progressive=True, subsampling=2)),
+                     ("restart", dict(subsampling=2, restart_marker_rows=1))):
         bio = io.BytesIO()
         Image.fromarray(img).save(bio, "JPEG", quality=90, **kw)
         out["unsup_" + name] = np.frombuffer(bio.getvalue(), np.uint8)
@@ -53,7 +67,7 @@ def main():
     Image.fromarray(img[:, :, 0]).save(bio, "JPEG", quality=90)
     out["unsup_gray"] = np.frombuffer(bio.getvalue(), np.uint8)
     np.savez_compressed(os.path.join(HERE, "jpeg_decode.npz"), **out)
-    print("wrote", len(CASES), "cases")
+    print("wrote", len(CASES) + len(CASES_OTHER), "cases")
 
 
 if __name__ == "__main__":
