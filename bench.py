@@ -622,7 +622,7 @@ def leg_files(eng, pool, w, h, q, target, batch, args, dist, local, rank, local_
         Image.fromarray(im).save(bio, "JPEG", quality=92, subsampling=2)
         files.append(np.frombuffer(bio.getvalue(), np.uint8))
     fslots = max(args.slots, 24)                     # the decode kernels are latency bound: more jobs in flight
-    T = args.threads
+    T = max(args.threads, 3)                         # (r02 probes: 3 workers x 8 jobs is steadier than 2 x 12)
     inflight = max(1, fslots // T)
     engf = pkg.Engine(devices=[local_dev], slots_per_gpu=fslots, max_w=w, max_h=h)
     try:

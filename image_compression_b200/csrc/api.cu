@@ -75,7 +75,7 @@ struct Job {
     int passes = 0;
     bool xf_this_phase = false;             // the phase in flight ran the transform (its kernel clock is fresh)
     bool from_file = false;                 // the pixels come out of the GPU JPEG reader: its verdict counts
-    unsigned int dec_nblocks = 0;
+    unsigned int dec_nblocks = 0, dec_nrst = 0;
     icb_result res{};
 };
 
@@ -1230,6 +1230,7 @@ int decode_verdict(icb_handle *h, Slot *s)
     }
     if (ds.active[DEC_ROUNDS - 1]) return fail(h, ICB_ERR_UNSUPPORTED, "JPEG reader: no fixed point within the synchronisation rounds");
     if (ds.blocks_found < s->job.dec_nblocks) return fail(h, ICB_ERR_INVALID, "JPEG reader: entropy-coded data ends early");
+    if (ds.n_rst != s->job.dec_nrst) return fail(h, ICB_ERR_INVALID, "JPEG reader: restart markers do not match the restart interval");
     const unsigned int total_bits = ds.total_bytes * 8u;
     if (ds.end_bit > total_bits || total_bits - ds.end_bit >= 16u)
         return fail(h, ICB_ERR_INVALID, "JPEG reader: data left over after the last block");
@@ -2127,7 +2128,7 @@ int map_parse(icb_handle *h, int jp)
 {
     if (jp == JP_OK) return ICB_OK;
     if (jp == JP_UNSUPPORTED)
-        return fail(h, ICB_ERR_UNSUPPORTED, "JPEG reader takes baseline 8-bit YCbCr 4:2:0 / 4:2:2 / 4:4:4, one scan, no restart interval");
+        return fail(h, ICB_ERR_UNSUPPORTED, "JPEG reader takes baseline 8-bit YCbCr 4:2:0 / 4:2:2 / 4:4:4 in one scan");
     return fail(h, ICB_ERR_INVALID, "not a JPEG file / truncated header");
 }
 
@@ -2208,7 +2209,8 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     const size_t nmcu_cap = nblocks_cap / 3, ndc_cap = (nmcu_cap + DEC_DC_THREADS - 1) / DEC_DC_THREADS;
     const size_t o_base = sub_bytes, o_chunk = o_base + round_up((size_t)nsub_cap * 4, 256);
     const size_t o_mcu = o_chunk + round_up((size_t)(nchunks_cap + 1) * 4, 256), o_cta = o_mcu + round_up(nmcu_cap * 12, 256);
-    if (!rc) rc = ensure(h, s->d_sub, s->sub_cap, o_cta + round_up(ndc_cap * 12, 256));
+    const size_t o_crst = o_cta + round_up(ndc_cap * 12, 256), o_rst = o_crst + round_up((size_t)(nchunks_cap + 1) * 4, 256);
+    if (!rc) rc = ensure(h, s->d_sub, s->sub_cap, o_rst + round_up(nmcu_cap * 4, 256));
     if (!rc) rc = ensure(h, s->d_planes, s->planes_cap, nblocks_cap * 64 + 256);
     if (!rc) rc = ensure(h, s->d_coef, s->coef_cap, nblocks_cap * 128);
     if (rc) return rc;
@@ -2227,6 +2229,10 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     dp.chunk_drop = reinterpret_cast<unsigned int *>(s->d_sub + o_chunk);
     dp.mcu_pref = reinterpret_cast<int *>(s->d_sub + o_mcu);
     dp.cta_pref = reinterpret_cast<int *>(s->d_sub + o_cta);
+    dp.chunk_rst = reinterpret_cast<unsigned int *>(s->d_sub + o_crst);
+    dp.rst_pos = reinterpret_cast<unsigned int *>(s->d_sub + o_rst);
+    dp.rst_cap = (unsigned int)nmcu_cap;
+    dp.ri = hd.ri;
     dp.coef = s->d_coef;
     dp.planes = s->d_planes;
     dp.rgb = d_out; dp.rgb_pitch = out_pitch; dp.bgr = bgr ? 1 : 0;
@@ -2273,6 +2279,7 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     h->kernels += 9 + dec_rounds();
     CK(cudaMemcpyAsync(s->h_decst, s->d_decst, sizeof(DecState), cudaMemcpyDeviceToHost, st));
     s->job.dec_nblocks = (unsigned int)nblocks;
+    s->job.dec_nrst = hd.ri > 0 ? (unsigned int)(((size_t)mcu_cols * mcu_rows + hd.ri - 1) / hd.ri - 1) : 0u;
     return ICB_OK;
 }
 
@@ -2375,10 +2382,12 @@ int icb_submit_jpg_file_fit(icb_handle *h, const uint8_t *file, size_t n, float 
         }
     }
     nblk = s->job.dec_nblocks;
+    const unsigned int nrst = s->job.dec_nrst;
     if (!rc) rc = start_fit(h, s, s->d_rgb, fw, fh, fp, ICB_FMT_RGB8, init_q, target, has_cached, cached_q, cached_scale, out, out_cap);
     if (rc) { cudaStreamSynchronize(s->stream); release_slot(h, s); return rc; }
     s->job.from_file = true;
     s->job.dec_nblocks = nblk;
+    s->job.dec_nrst = nrst;
     *ticket = make_ticket(s);
     return ICB_OK;
 }

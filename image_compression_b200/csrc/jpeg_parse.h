@@ -1,7 +1,7 @@
 // jpeg_parse.h -- host side of the GPU JPEG reader (k_decode.cuh): marker parse of a JFIF file (jdmarker.c's
 // part of what core/ImageCompression.java:119-155 has ImageIO do) and the decode tables the kernels use.
 // Takes exactly what the kernels decode -- SOF0, 8 bit, three components, luma sampled 2x2 / 2x1 / 1x1 over 1x1 chroma, 8-bit
-// quantisation tables, one interleaved scan over the full spectrum, no restart interval -- and says
+// quantisation tables, one interleaved scan over the full spectrum, with or without restart intervals -- and says
 // "unsupported" for everything else, so that the caller keeps the stock host decode for such files.
 #pragma once
 
@@ -17,6 +17,7 @@ enum { JP_OK = 0, JP_UNSUPPORTED = 1, JP_CORRUPT = 2 };
 
 struct JpegHeader {
     int w = 0, h = 0;
+    int ri = 0;                             // restart interval in MCUs (DRI); 0 = none
     int hs = 2, vs = 2;                     // luma sampling factors: 2x2 (4:2:0), 2x1 (4:2:2) or 1x1 (4:4:4); chroma 1x1
     size_t scan_off = 0;                    // first entropy-coded byte
     int comp_tq[3] = {0, 0, 0}, comp_td[3] = {0, 0, 0}, comp_ta[3] = {0, 0, 0};
@@ -90,7 +91,7 @@ inline int jpeg_parse(const uint8_t *f, size_t n, JpegHeader &hd)
             break;
         case 0xDD:
             if (sl < 2) return JP_CORRUPT;
-            if (s[0] | s[1]) return JP_UNSUPPORTED;                             // restart intervals
+            hd.ri = (s[0] << 8) | s[1];
             break;
         case 0xDA:
             if (!have_sof) return JP_CORRUPT;

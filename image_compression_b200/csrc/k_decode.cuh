@@ -1,7 +1,7 @@
 // k_decode.cuh -- SURVEY section 8 row f2 (input staging): the JPEG reader in front of the JPG seam, on the GPU.
 //
 // Replaces reader.read(0, param) of core/ImageCompression.java:119-155 for the files that make up the reference's
-// workload (baseline SOF0, 8 bit, YCbCr 4:2:0 -- also 4:2:2 and 4:4:4 --, one interleaved scan, no restart interval): the caller uploads the
+// workload (baseline SOF0, 8 bit, YCbCr 4:2:0 -- also 4:2:2 and 4:4:4 --, one interleaved scan, restart intervals or not): the caller uploads the
 // FILE (a few MB) instead of the decoded raster (36 MB for 12 MP), which is what bounds the end-to-end rate on a
 // PCIe link.  Anything else is refused on the host (ICB_ERR_UNSUPPORTED: the caller keeps the stock ImageIO decode).
 // Arithmetic = the JDK reader's libjavajpeg = IJG libjpeg 6b with its defaults [JDK-mem], restated in
@@ -20,9 +20,9 @@
 // a job that has not reached it after DEC_ROUNDS rounds reports ICB_ERR_UNSUPPORTED (host decode).  Then: block counts -> prefix -> a last
 // decode that writes the coefficients, DC prediction as a scan over MCUs, IDCT into planes, upsample + colour.
 // Kernels, all on the job's stream:
-//   k_dec_scan     per 4 KB of file: stuffed-zero count, position of the first marker
+//   k_dec_scan     per 4 KB of file: stuffed zeros and RSTn markers counted, position of the first other marker
 //   k_dec_offsets  prefix of those counts (one CTA)
-//   k_dec_unstuff  the entropy-coded bytes without the stuffed zeros, zero padded
+//   k_dec_unstuff  the entropy-coded bytes without stuffed zeros and restart markers, zero padded; where each restart interval starts
 //   k_dec_sync     one synchronisation round (DEC_ROUNDS launches, no-ops once nothing changes)
 //   k_dec_blocks   blocks in front of every subsequence (one CTA)
 //   k_dec_write    coefficients (quantised, natural order, DC as differences) into the block array
@@ -75,6 +75,7 @@ struct DecState {
     unsigned int active[DEC_ROUNDS];        // subsequences re-decoded in round r
     unsigned int end_bit;                   // bit position at which the last block of the image ended
     unsigned int blocks_found;              // blocks the whole stream holds
+    unsigned int n_rst;                     // RSTn markers in the scan
     int error;                              // != 0: not decodable here
     int pad;
 };
@@ -99,96 +100,131 @@ struct DecParams {
     unsigned int nblocks;
     unsigned int nsub_max;                  // subsequences the file could hold at most
     int nchunks;                            // DEC_CHUNK-byte pieces of the file from scan_off on
+    int ri;                                 // restart interval in MCUs (DRI), 0 = none
+    unsigned int *chunk_rst;                // [nchunks + 1] RSTn markers per chunk, then their exclusive prefix
+    unsigned int *rst_pos;                  // [rst_cap] byte offset in `bits` at which the interval after marker k starts
+    unsigned int rst_cap;
     const DecTables *tab;
     DecState *st;
 };
 
-// ---- entropy-coded segment: stuffed zeros out, first marker found ----------------------------------------
+// ---- entropy-coded segment: stuffed zeros and restart markers out, first other marker found -----------------
+// What happens to byte i of the scan (prev / next = its neighbours): a zero after 0xFF is stuffing and goes; with a
+// restart interval, 0xFF 0xD0..0xD7 is an RSTn marker and both bytes go; 0xFF followed by anything else ends the scan.
+__device__ __forceinline__ bool dec_is_rst(unsigned int b, int ri) { return ri > 0 && b >= 0xD0u && b <= 0xD7u; }
+__device__ __forceinline__ bool dec_keep(unsigned int prev, unsigned int b, unsigned int next, int ri)
+{
+    if (prev == 0xFFu && (b == 0u || dec_is_rst(b, ri))) return false;
+    if (b == 0xFFu && dec_is_rst(next, ri)) return false;
+    return true;
+}
+
 __global__ void __launch_bounds__(256) k_dec_scan(const DecParams *pp)
 {
     const DecParams p = *pp;
-    __shared__ unsigned int s_cnt;
-    if (threadIdx.x == 0) s_cnt = 0;
+    __shared__ unsigned int s_cnt[2];
+    if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
     __syncthreads();
     const unsigned int base = p.scan_off + blockIdx.x * DEC_CHUNK + threadIdx.x * 16;
-    unsigned int drops = 0;
+    unsigned int drops = 0, rsts = 0;
     if (base < p.file_len) {
-        unsigned int prev = base > 0 ? p.file[base - 1] : 0;
+        unsigned int prev = base > p.scan_off ? p.file[base - 1] : 0;
         const unsigned int n = min(16u, p.file_len - base);
+        unsigned int b = p.file[base];
         for (unsigned int i = 0; i < n; i++) {
-            const unsigned int b = p.file[base + i];
-            if (prev == 0xFFu && base + i > p.scan_off) {
-                if (b == 0u) drops++;
-                else if (b != 0xFFu) atomicMin(&p.st->scan_end, base + i - 1);      // a marker: the scan ends here
+            const unsigned int next = base + i + 1 < p.file_len ? p.file[base + i + 1] : 0u;
+            if (!dec_keep(prev, b, next, p.ri)) drops++;
+            if (prev == 0xFFu) {
+                if (dec_is_rst(b, p.ri)) rsts++;
+                else if (b != 0u && b != 0xFFu) atomicMin(&p.st->scan_end, base + i - 1);      // a marker: the scan ends here
             }
             prev = b;
+            b = next;
         }
     }
     drops = __reduce_add_sync(0xffffffffu, drops);
-    if ((threadIdx.x & 31) == 0 && drops) atomicAdd(&s_cnt, drops);
+    rsts = __reduce_add_sync(0xffffffffu, rsts);
+    if ((threadIdx.x & 31) == 0) { if (drops) atomicAdd(&s_cnt[0], drops); if (rsts) atomicAdd(&s_cnt[1], rsts); }
     __syncthreads();
-    if (threadIdx.x == 0) p.chunk_drop[blockIdx.x] = s_cnt;
+    if (threadIdx.x == 0) { p.chunk_drop[blockIdx.x] = s_cnt[0]; p.chunk_rst[blockIdx.x] = s_cnt[1]; }
 }
 
 __global__ void __launch_bounds__(1024) k_dec_offsets(const DecParams *pp)
 {
     const DecParams p = *pp;
     const int nchunks = p.nchunks;
-    __shared__ unsigned int s_part[1024];
+    __shared__ unsigned int s_part[2][1024];
     const int tid = threadIdx.x;
     const int per = (nchunks + 1023) / 1024;
     const int i0 = min(nchunks, tid * per), i1 = min(nchunks, i0 + per);
-    unsigned int mine = 0;
-    for (int i = i0; i < i1; i++) mine += p.chunk_drop[i];
-    s_part[tid] = mine;
+    unsigned int mine[2] = {0, 0};
+    for (int i = i0; i < i1; i++) { mine[0] += p.chunk_drop[i]; mine[1] += p.chunk_rst[i]; }
+    s_part[0][tid] = mine[0]; s_part[1][tid] = mine[1];
     __syncthreads();
     for (int o = 1; o < 1024; o <<= 1) {
-        const unsigned int t = tid >= o ? s_part[tid - o] : 0u;
+        unsigned int t0 = 0, t1 = 0;
+        if (tid >= o) { t0 = s_part[0][tid - o]; t1 = s_part[1][tid - o]; }
         __syncthreads();
-        s_part[tid] += t;
+        s_part[0][tid] += t0; s_part[1][tid] += t1;
         __syncthreads();
     }
-    unsigned int run = s_part[tid] - mine;
-    for (int i = i0; i < i1; i++) { const unsigned int c = p.chunk_drop[i]; p.chunk_drop[i] = run; run += c; }
+    unsigned int run0 = s_part[0][tid] - mine[0], run1 = s_part[1][tid] - mine[1];
+    for (int i = i0; i < i1; i++) {
+        const unsigned int c0 = p.chunk_drop[i], c1 = p.chunk_rst[i];
+        p.chunk_drop[i] = run0; p.chunk_rst[i] = run1;
+        run0 += c0; run1 += c1;
+    }
 }
 
+// Two sweeps over a thread's 16 bytes (the second hits L1): count what stays and the restart markers, prefix both over
+// the CTA, then write the bytes and, per marker, where the interval behind it starts.
 __global__ void __launch_bounds__(256) k_dec_unstuff(const DecParams *pp)
 {
     const DecParams p = *pp;
-    __shared__ unsigned int s_warp[8];
+    __shared__ unsigned int s_warp[2][8];
     const unsigned int end = min(p.st->scan_end, p.file_len);
     const unsigned int chunk0 = p.scan_off + blockIdx.x * DEC_CHUNK;
     if (chunk0 >= end) return;
     const unsigned int base = chunk0 + threadIdx.x * 16;
-    unsigned int keep = 0, bytes[16];
-    unsigned int n = 0;
+    unsigned int keep = 0, rsts = 0, n = 0;
     if (base < end) {
         n = min(16u, end - base);
-        unsigned int prev = base > p.scan_off ? p.file[base - 1] : 0;
+        unsigned int prev = base > p.scan_off ? p.file[base - 1] : 0, b = p.file[base];
         for (unsigned int i = 0; i < n; i++) {
-            const unsigned int b = p.file[base + i];
-            if (!(prev == 0xFFu && b == 0u && base + i > p.scan_off)) bytes[keep++] = b;
+            const unsigned int next = base + i + 1 < end ? p.file[base + i + 1] : 0u;
+            keep += dec_keep(prev, b, next, p.ri) ? 1u : 0u;
+            rsts += (prev == 0xFFu && dec_is_rst(b, p.ri)) ? 1u : 0u;
             prev = b;
+            b = next;
         }
     }
-    // exclusive prefix of keep over the CTA
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned int incl = keep;
+    unsigned int ik = keep, ir = rsts;
 #pragma unroll
     for (int o = 1; o < 32; o <<= 1) {
-        const unsigned int t = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += t;
+        const unsigned int t = __shfl_up_sync(0xffffffffu, ik, o), u = __shfl_up_sync(0xffffffffu, ir, o);
+        if (lane >= o) { ik += t; ir += u; }
     }
-    if (lane == 31) s_warp[warp] = incl;
+    if (lane == 31) { s_warp[0][warp] = ik; s_warp[1][warp] = ir; }
     __syncthreads();
-    unsigned int off = incl - keep;
-    for (int w = 0; w < warp; w++) off += s_warp[w];
-    const unsigned int out0 = (chunk0 - p.scan_off) - p.chunk_drop[blockIdx.x] + off;
-    for (unsigned int i = 0; i < keep; i++) p.bits[out0 + i] = (unsigned char)bytes[i];
-    if (n && base + n == end) {                                  // the thread that holds the last byte of the scan
-        const unsigned int total = out0 + keep;
-        p.st->total_bytes = total;
-        for (unsigned int i = 0; i < 64; i++) p.bits[total + i] = 0;
+    unsigned int off = ik - keep, roff = ir - rsts;
+    for (int w = 0; w < warp; w++) { off += s_warp[0][w]; roff += s_warp[1][w]; }
+    unsigned int out = (chunk0 - p.scan_off) - p.chunk_drop[blockIdx.x] + off;
+    unsigned int rk = p.chunk_rst[blockIdx.x] + roff;
+    if (n) {
+        unsigned int prev = base > p.scan_off ? p.file[base - 1] : 0, b = p.file[base];
+        for (unsigned int i = 0; i < n; i++) {
+            const unsigned int next = base + i + 1 < end ? p.file[base + i + 1] : 0u;
+            if (dec_keep(prev, b, next, p.ri)) p.bits[out++] = (unsigned char)b;
+            if (prev == 0xFFu && dec_is_rst(b, p.ri)) { if (rk < p.rst_cap) p.rst_pos[rk] = out; rk++; }
+            prev = b;
+            b = next;
+        }
+        if (base + n == end) {                                  // the thread that holds the last byte of the scan
+            p.st->total_bytes = out;
+            p.st->n_rst = rk;
+            for (unsigned int i = 0; i < 64; i++) p.bits[out + i] = 0;
+        }
     }
 }
 
@@ -291,17 +327,40 @@ __device__ __forceinline__ unsigned int dec_lookup(const DecSmem &s, unsigned in
 
 // Decodes from state (pbit, bz = block-of-MCU * 64 + zigzag index) until a symbol starts at or after end_bit.
 // WRITE: coefficients go to coef (block index blk counts from the caller's base; blocks >= nblocks are dropped).
+__device__ __forceinline__ unsigned int st_n_rst(const DecParams &p) { return p.st->n_rst; }
+
 template <bool WRITE>
 __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *bits, unsigned int &pbit, unsigned int &bz,
                                         unsigned int &nblk, unsigned int end_bit, int16_t *coef, unsigned int blk,
-                                        unsigned int nblocks, DecState *st, unsigned int last_b)
+                                        unsigned int nblocks, DecState *st, unsigned int last_b, const DecParams &p)
 {
     unsigned int b = bz >> 6, z = bz & 63u;
     unsigned int tdc = s.tab_dc[b], tac = s.tab_ac[b];          // the block's two tables (change once per block)
     DecBits br;
     br.open(bits, pbit);
+    // Restart intervals (DRI): the interval behind marker k starts at byte rst_pos[k], byte aligned, with the first
+    // block of an MCU; the exact decoder ends the interval before it inside the last byte in front (padding).  A
+    // decoder that stands there between two MCUs, or finds itself past the boundary, restarts AT the boundary -- which
+    // also makes every boundary a point where a wrong chain becomes exact.
+    unsigned int rk = 0, rnext = 0xffffffffu;
+    const unsigned int n_rst = p.ri > 0 ? min(st_n_rst(p), p.rst_cap) : 0u;
+    if (n_rst) {
+        unsigned int lo = 0, hi = n_rst;                         // first k with rst_pos[k] * 8 > pbit
+        while (lo < hi) { const unsigned int mid = (lo + hi) >> 1; if (p.rst_pos[mid] * 8u > pbit) hi = mid; else lo = mid + 1; }
+        rk = lo;
+        if (rk < n_rst) rnext = p.rst_pos[rk] * 8u;
+    }
     while (br.pos < end_bit) {
         if (WRITE && blk >= nblocks) break;
+        if (br.pos + 7u >= rnext && (br.pos >= rnext || (z == 0 && b == 0))) {
+            br.open(bits, rnext);
+            z = 0; b = 0;
+            tdc = s.tab_dc[0]; tac = s.tab_ac[0];
+            rk++;
+            if (WRITE) blk = rk * (unsigned int)p.ri * (last_b + 1u);
+            rnext = rk < n_rst ? p.rst_pos[rk] * 8u : 0xffffffffu;
+            continue;
+        }
         const unsigned int peek = br.peek();
         const unsigned int e = dec_lookup(s, z == 0 ? tdc : tac, peek);
         const unsigned int zadv = (e >> 6) & 127u;
@@ -357,7 +416,7 @@ __global__ void __launch_bounds__(DEC_THREADS) k_dec_sync(const DecParams *pp, i
         if (k > i && dec_rec_entry(p.rec[k]) == entry) break;   // joined what is already recorded
         const unsigned int start = k * S, end = min(start + S, total_bits);
         unsigned int pbit = start + (entry >> 9), bz = entry & 0x1ffu, nblk = 0;
-        dec_run<false>(s, p.bits, pbit, bz, nblk, end, nullptr, 0, 0, nullptr, (unsigned int)p.nb - 1u);
+        dec_run<false>(s, p.bits, pbit, bz, nblk, end, nullptr, 0, 0, nullptr, (unsigned int)p.nb - 1u, p);
         const unsigned int exit_ = (min(pbit - end, 63u) << 9) | bz;
         atomicMin(&p.rec[k], dec_rec(round, i, entry, exit_, nblk));
         entry = exit_;
@@ -402,7 +461,7 @@ __global__ void __launch_bounds__(DEC_THREADS) k_dec_write(const DecParams *pp)
     const unsigned int entry = dec_rec_entry(p.rec[i]);
     unsigned int pbit = start + (entry >> 9), bz = entry & 0x1ffu, nblk = 0;
     const unsigned int end = min(start + S, total_bits);
-    dec_run<true>(s, p.bits, pbit, bz, nblk, end, p.coef, p.blk_base[i], p.nblocks, p.st, (unsigned int)p.nb - 1u);
+    dec_run<true>(s, p.bits, pbit, bz, nblk, end, p.coef, p.blk_base[i], p.nblocks, p.st, (unsigned int)p.nb - 1u, p);
 }
 
 // ---- DC differences -> DC values (jdhuff.c last_dc_val): per component a prefix over the MCUs --------------
@@ -547,6 +606,10 @@ __global__ void __launch_bounds__(128) k_dec_idct(const DecParams *pp)
     }
     {   // DC value = differences of every earlier block of the component + its own (stored back as the JCOEF short)
         int dc = p.cta_pref[(size_t)(m / DEC_DC_THREADS) * 3 + comp] + p.mcu_pref[(size_t)m * 3 + comp];
+        if (p.ri > 0) {                                     // the predictions start again at every restart interval
+            const unsigned int hm = m / (unsigned int)p.ri * (unsigned int)p.ri;
+            dc -= p.cta_pref[(size_t)(hm / DEC_DC_THREADS) * 3 + comp] + p.mcu_pref[(size_t)hm * 3 + comp];
+        }
         const int16_t *mc = p.coef + (size_t)m * nbm * 64;
         if (k < ny) { for (unsigned int j = 0; j <= k; j++) dc += mc[64 * j]; }
         else dc += mc[64 * k];

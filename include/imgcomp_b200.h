@@ -240,10 +240,9 @@ int icb_submit_png_compress(icb_handle *h, const uint8_t *src, int w, int hgt, i
 
 /* SURVEY 8 f2 (input staging) -- core/ImageCompression.java:119-155 decodeImageWithSubsampling on the GPU:
  * reader.read(0, param) of the ImageIO JPEG reader (libjavajpeg = IJG 6b: sequential Huffman decode, islow inverse
- * DCT, fancy h2v2 upsampling (h2v2 / h2v1), YCbCr -> RGB) for baseline 8-bit YCbCr 4:2:0, 4:2:2 and 4:4:4 files with one scan and no restart
- * interval, so that the caller uploads the FILE instead of the decoded raster (12 MP: ~6 MB instead of 36 MB over
- * PCIe).  ICB_ERR_UNSUPPORTED = any other kind of JPEG (progressive, gray, CMYK, restart markers, 12 bit,
- * other sampling factors) or a stream the parallel decoder did not resolve: the caller decodes on the host as before and calls the
+ * DCT, fancy upsampling (h2v2 / h2v1), YCbCr -> RGB) for baseline 8-bit YCbCr 4:2:0, 4:2:2 and 4:4:4 files with one scan (restart
+ * intervals included), so that the caller uploads the FILE instead of the decoded raster (12 MP: ~6 MB instead of 36 MB over
+ * PCIe).  ICB_ERR_UNSUPPORTED = any other kind of JPEG (progressive, gray, CMYK, 12 bit, other sampling factors) or a stream the parallel decoder did not resolve: the caller decodes on the host as before and calls the
  * pixel entry points.  ICB_ERR_INVALID = not a JPEG / truncated.
  *   icb_jpg_file_info   header parse on the host (:128-129 reader.getWidth / getHeight), no device needed
  *   icb_jpg_decode      the decoded raster (RGB8 or BGR8 = TYPE_3BYTE_BGR) back on the host: test / parity entry

@@ -16,7 +16,7 @@ import java.util.Map;
  * The reference decodes every file on the host ({@code ImageCompression.decodeImageWithSubsampling},
  * core/ImageCompression.java:107-165) and hands the 36 MB raster of a 12 MP image to
  * {@code compressJpgWithTargetSize}.  For the files that make up its workload -- baseline 8-bit YCbCr 4:2:0 / 4:2:2 / 4:4:4, one
- * scan, no restart markers -- the library decodes the FILE on the GPU instead (include/imgcomp_b200.h
+ * scan -- the library decodes the FILE on the GPU instead (include/imgcomp_b200.h
  * icb_jpg_file_fit): only the file crosses PCIe, the decode rule of :140-153 (source subsampling above 4096 px) is
  * applied on the device, and the fit is the same icb_jpg_fit.
  *

@@ -202,7 +202,7 @@ public final class Icb {
 
     /**
      * Dimensions of a JPEG file the GPU reader takes (core/ImageCompression.java:128-129), or null when the file is of
-     * another kind (progressive, gray, CMYK, restart markers): the caller then decodes with ImageIO as before.
+     * another kind (progressive, gray, CMYK): the caller then decodes with ImageIO as before.
      */
     public static int[] jpgFileInfo(byte[] file) throws IOException {
         try (Arena a = Arena.ofConfined()) {

@@ -17,8 +17,8 @@
  * Against a real JDK the decoded pixels are "parity unpinned" like every other [JDK-mem] fact.
  *
  * Scope = what the CUDA decoder takes: SOF0, 8 bits, 3 components, luma sampled 2x2 (4:2:0), 2x1 (4:2:2) or 1x1
- * (4:4:4) with 1x1 chroma, one
- * interleaved scan, no restart interval.  Everything else returns ORC_DEC_UNSUPPORTED: the caller keeps
+ * (4:4:4) with 1x1 chroma, restart intervals (DRI / RSTn), one
+ * interleaved scan.  Everything else returns ORC_DEC_UNSUPPORTED: the caller keeps
  * the stock host decode for such files.
  */
 #include <stdlib.h>
@@ -29,6 +29,7 @@
 typedef struct {
     int w, h;
     int mcu_cols, mcu_rows;
+    int ri;                             /* restart interval in MCUs (DRI), 0 = none */
     int hs, vs;                         /* luma sampling factors: 2x2 (4:2:0), 2x1 (4:2:2), 1x1 (4:4:4) */
     unsigned short qt[4][64];           /* natural order */
     int qt_set[4];
@@ -122,7 +123,7 @@ static int parse_headers(const uint8_t *f, size_t n, dec_t *d)
             return ORC_DEC_UNSUPPORTED;                       /* extended, progressive, lossless, arithmetic */
         } else if (m == 0xDD) {                               /* DRI */
             if (sl < 2) return ORC_DEC_CORRUPT;
-            if ((s[0] << 8) | s[1]) return ORC_DEC_UNSUPPORTED;
+            d->ri = (s[0] << 8) | s[1];
         } else if (m == 0xDA) {                               /* SOS */
             if (!have_sof) return ORC_DEC_CORRUPT;
             if (sl < 1 + 6 + 3 || s[0] != 3) return ORC_DEC_UNSUPPORTED;
@@ -295,11 +296,23 @@ int orc_jpeg_decode_coefficients(const uint8_t *file, size_t n, int16_t *out)
     int last_dc[3] = {0, 0, 0};
     const long nm = (long)d.mcu_cols * d.mcu_rows;
     const int ny = d.hs * d.vs, nb = ny + 2;
-    for (long m = 0; m < nm; m++)
+    for (long m = 0; m < nm; m++) {
+        if (d.ri && m && m % d.ri == 0) {
+            /* jdhuff.c process_restart: drop the padding bits, read the RSTn marker, reset the DC predictions */
+            b.acc = 0; b.nbits = 0;
+            if (b.hit_marker) b.p++;                          /* fill() stopped on the 0xFF: p stands on the marker code */
+            else {
+                while (b.p + 1 < b.n && !(b.f[b.p] == 0xFF && b.f[b.p + 1] >= 0xD0 && b.f[b.p + 1] <= 0xD7)) b.p++;
+                b.p += 2;
+            }
+            b.hit_marker = 0;
+            last_dc[0] = last_dc[1] = last_dc[2] = 0;
+        }
         for (int k = 0; k < nb; k++) {
             const int comp = k < ny ? 0 : k - ny + 1;
             decode_block(&b, &d, comp, &last_dc[comp], out + (m * nb + k) * 64);
         }
+    }
     return ORC_DEC_OK;
 }
 

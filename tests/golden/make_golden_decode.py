@@ -56,10 +56,22 @@ def main():
         dec = np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))
         out[f"file_{len(CASES) + j}"] = np.frombuffer(data, np.uint8)
         out[f"pixels_{len(CASES) + j}"] = dec
-    # files the decoder must refuse (the caller keeps the stock host decode): progressive, restart interval, gray
+    # restart intervals (DRI + RSTn markers): whole MCU rows and a few MCUs, with and without a tail, three samplings
+    base = len(CASES) + len(CASES_OTHER)
+    for j, (seed, w, h, q, sub, kw) in enumerate([(70, 200, 133, 90, 2, dict(restart_marker_rows=1)), (71, 333, 251, 75, 2, dict(restart_marker_blocks=5)),
+                                                   (72, 64, 48, 95, 2, dict(restart_marker_blocks=1)), (73, 97, 61, 92, 1, dict(restart_marker_rows=2)),
+                                                   (74, 131, 77, 60, 0, dict(restart_marker_blocks=7)), (75, 130, 66, 100, 2, dict(restart_marker_blocks=3))]):
+        img = make(seed, w, h, "noise" if seed == 75 else "natural")
+        bio = io.BytesIO()
+        Image.fromarray(img).save(bio, "JPEG", quality=q, subsampling=sub, **kw)
+        data = bio.getvalue()
+        assert b"\xff\xdd" in data
+        dec = np.asarray(Image.open(io.BytesIO(data)).convert("RGB"))
+        out[f"file_{base + j}"] = np.frombuffer(data, np.uint8)
+        out[f"pixels_{base + j}"] = dec
+    # files the decoder must refuse (the caller keeps the stock host decode): progressive, gray
     img = make(60, 48, 32, "natural")
-    for name, kw in (("progressive", dict(progressive=True, subsampling=2)),
-                     ("restart", dict(subsampling=2, restart_marker_rows=1))):
+    for name, kw in (("progressive", dict(progressive=True, subsampling=2)),):
         bio = io.BytesIO()
         Image.fromarray(img).save(bio, "JPEG", quality=90, **kw)
         out["unsup_" + name] = np.frombuffer(bio.getvalue(), np.uint8)
@@ -67,7 +79,7 @@ def main():
     Image.fromarray(img[:, :, 0]).save(bio, "JPEG", quality=90)
     out["unsup_gray"] = np.frombuffer(bio.getvalue(), np.uint8)
     np.savez_compressed(os.path.join(HERE, "jpeg_decode.npz"), **out)
-    print("wrote", len(CASES) + len(CASES_OTHER), "cases")
+    print("wrote", len([k for k in out if k.startswith("file_")]), "cases")
 
 
 if __name__ == "__main__":

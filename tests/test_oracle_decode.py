@@ -40,7 +40,7 @@ def test_coefficients_round_trip_through_the_forward_oracle(oracle):
         assert np.array_equal(q, got[b].astype(np.int64)), b
 
 
-@pytest.mark.parametrize("name", ["progressive", "restart", "gray"])
+@pytest.mark.parametrize("name", ["progressive", "gray"])
 def test_oracle_refuses_what_the_gpu_decoder_does_not_take(oracle, name):
     with pytest.raises(ValueError) as ei:
         oracle.jpeg_info(Z["unsup_" + name].tobytes())
