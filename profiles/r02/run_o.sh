@@ -1,4 +1,3 @@
-# r02 call O: decode tests incl. 4:2:2 / 4:4:4, rate check
+# r02 call O: decode tests
 export ICB_POOL_CACHE=/tmp/icb_pool
 timeout 900 python -m pytest tests/test_gpu_decode.py -m gpu -x -q 2>&1 | tail -8
-PROBE_SLOTS=24 timeout 600 python profiles/r02/decode_probe2.py 2>&1 | sed -n 2,3p

@@ -157,3 +157,15 @@ def test_files_with_restart_intervals(engine, oracle, w, h, sub, kw):
     assert b"\xff\xdd" in data
     want = oracle.jpeg_decode(data)
     assert np.array_equal(engine.jpg_decode(data), want)
+
+
+@pytest.mark.parametrize("variant", ["extra_segments", "merged_tables", "fill_and_tail"])
+def test_rewrapped_files_decode_alike(engine, variant):
+    """what camera files look like: Exif / comment segments, one DHT / DQT segment for all tables, fill bytes in front
+    of markers, bytes behind EOI (tests/jpeg_mangle.py) -- same pixels as the plain file"""
+    import sys
+    sys.path.insert(0, HERE)
+    import jpeg_mangle
+    for i in (2, 13, 19, 24):
+        data = jpeg_mangle.VARIANTS[variant](Z[f"file_{i}"].tobytes())
+        assert np.array_equal(engine.jpg_decode(np.frombuffer(data, np.uint8)), Z[f"pixels_{i}"]), (variant, i)

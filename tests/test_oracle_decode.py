@@ -63,3 +63,14 @@ def test_truncated_and_garbage_files_do_not_crash(oracle):
             oracle.jpeg_decode(bytes(junk))
         except ValueError:
             pass
+
+
+@pytest.mark.parametrize("variant", ["extra_segments", "merged_tables", "fill_and_tail"])
+def test_rewrapped_files_decode_alike(oracle, variant):
+    """Exif / comment segments, merged table segments, fill bytes, bytes behind EOI (tests/jpeg_mangle.py)"""
+    import sys
+    sys.path.insert(0, HERE)
+    import jpeg_mangle
+    for i in (2, 13, 19, 24):                                   # 4:2:0, 4:2:2, 4:4:4, restart intervals
+        data = jpeg_mangle.VARIANTS[variant](Z[f"file_{i}"].tobytes())
+        assert np.array_equal(oracle.jpeg_decode(data), Z[f"pixels_{i}"]), (variant, i)
