@@ -559,10 +559,12 @@ __device__ __forceinline__ void dec_idct_1d(const int (&in)[8], int (&out)[8], i
     out[3] = (tmp13 + tmp0 + rnd) >> shift; out[4] = (tmp13 - tmp0 + rnd) >> shift;
 }
 
-__device__ __forceinline__ unsigned int dec_range_limit(int x)     // jdmaster.c range-limit table at index x & RANGE_MASK
+// jdmaster.c range-limit table at index x & RANGE_MASK (1023): with y = the low ten bits of x read as a SIGNED number
+// (-512 .. 511) the table is clamp(y + 128, 0, 255) -- 0..127 -> +128, 128..511 -> 255, -512..-129 -> 0, -128..-1 -> +128
+__device__ __forceinline__ unsigned int dec_range_limit(int x)
 {
-    const int v = x & 1023;
-    return (unsigned int)(v < 128 ? v + 128 : (v < 512 ? 255 : (v < 896 ? 0 : v - 896)));
+    const int y = (x << 22) >> 22;
+    return (unsigned int)min(max(y + 128, 0), 255);
 }
 
 // one thread = one block: 64 coefficients (natural order) -> 8 x 8 samples of the block's plane
