@@ -38,7 +38,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
            "-o", LIB] + [os.path.join(CSRC, s) for s in SOURCES]
     if os.environ.get("ICB_TIMING"):
         cmd.insert(1, "-DICB_TIMING")
-    for knob in ("ICB_TILE_MCUS", "ICB_XF_CTAS", "ICB_XF_STAGES", "ICB_PASS_LDG", "ICB_NO_KCLK", "ICB_PASS_BITS_ONLY", "ICB_XF_ROWMAJOR", "ICB_XF_DBG", "ICB_XF_COLEXPANDED", "ICB_PASS_OR_BRANCH"):        # A/B builds of the transform kernel
+    for knob in ("ICB_TILE_MCUS", "ICB_XF_CTAS", "ICB_XF_STAGES", "ICB_PASS_LDG", "ICB_NO_KCLK", "ICB_PASS_BITS_ONLY", "ICB_XF_ROWMAJOR", "ICB_XF_DBG", "ICB_XF_COLEXPANDED", "ICB_PASS_OR_BRANCH", "ICB_DEC_THREADS"):        # A/B builds of the transform kernel
         if os.environ.get(knob):
             cmd.insert(1, "-D%s=%s" % (knob, os.environ[knob]))
     if os.environ.get("ICB_LIB_SUFFIX"):

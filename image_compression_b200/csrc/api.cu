@@ -2124,6 +2124,9 @@ extern "C" int icb_png_encode_device_noalloc(icb_handle *h, const uint8_t *d_px,
 // ======================================================================
 namespace {
 
+static std::atomic<uint64_t> g_submit_ns{0}, g_submit_n{0}, g_acquire_ns{0}, g_graph_ns{0}, g_fit_ns{0}, g_dec_ns{0}, g_t1{0}, g_t2{0}, g_t3{0}, g_t4{0};
+static inline uint64_t now_ns() { return (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+
 int map_parse(icb_handle *h, int jp)
 {
     if (jp == JP_OK) return ICB_OK;
@@ -2151,7 +2154,9 @@ void launch_decode_chain(Slot *s, cudaStream_t st, size_t sub_bytes_cap, size_t 
     // state: everything zero, the scan ends at the end of the file unless a marker turns up earlier; no record yet
     cudaMemsetAsync(s->d_decst, 0, sizeof(DecState), st);
     cudaMemsetAsync(&s->d_decst->scan_end, 0xff, 4, st);
-    cudaMemsetAsync(s->d_coef, 0, nblocks_cap * 128, st);
+    static const bool zero_by_memset = [] { const char *e = getenv("ICB_DEC_MEMSET"); return e && e[0] == '1'; }();     // A/B knob
+    if (zero_by_memset) cudaMemsetAsync(s->d_coef, 0, nblocks_cap * 128, st);
+    else k_dec_zero<<<1184, 256, 0, st>>>(reinterpret_cast<uint4 *>(s->d_coef), nblocks_cap * 8);
     cudaMemsetAsync(s->d_sub, 0xff, sub_bytes_cap, st);
     k_dec_scan<<<nchunks_cap, 256, 0, st>>>(pp);
     k_dec_offsets<<<1, 1024, 0, st>>>(pp);
@@ -2216,8 +2221,10 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     if (rc) return rc;
     s->dec_scan_cap = scan_cap; s->dec_w_cap = wc; s->dec_h_cap = hc; s->dec_blocks_cap = nblocks_cap;
 
+    const uint64_t ta = now_ns();
     DecJob &job = *s->h_decjob;
     jpeg_build_tables(hd, job.t);
+    g_t1 += now_ns() - ta;
     DecParams &dp = job.p;
     dp = DecParams{};
     dp.file = s->d_file_in; dp.file_len = (unsigned int)n; dp.scan_off = (unsigned int)hd.scan_off;
@@ -2243,9 +2250,13 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     dp.nchunks = (int)((scan_bytes + DEC_CHUNK - 1) / DEC_CHUNK);
     dp.tab = &s->d_decjob->t;
     dp.st = s->d_decst;
+    const uint64_t tb = now_ns();
     CK(cudaMemcpyAsync(s->d_decjob, s->h_decjob, sizeof(DecJob), cudaMemcpyHostToDevice, st));
+    const uint64_t tc = now_ns();
+    g_t2 += tc - tb;
     rc = upload(h, s, s->d_file_in, (int)std::min<size_t>(n, 0x7fffffff), file, (int)n, 1, (int)n, 1);
     if (rc) return rc;
+    g_t3 += now_ns() - tc;
 
     if (use_graph && !s->dec_graph_broken) {
         // the graph stands for these buffers and capacities; anything else: capture again
@@ -2271,13 +2282,17 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
         }
     }
     if (use_graph && !s->dec_graph_broken && s->dec_graph) {
+        const uint64_t tg = now_ns();
         CK(cudaGraphLaunch(s->dec_graph, st));
+        g_graph_ns += now_ns() - tg;
     } else {
         launch_decode_chain(s, st, sub_bytes, nblocks_cap, nchunks_cap, nsub_cap, wc, hc, hd.hs, hd.vs);
         CK(cudaGetLastError());
     }
     h->kernels += 9 + dec_rounds();
+    const uint64_t te = now_ns();
     CK(cudaMemcpyAsync(s->h_decst, s->d_decst, sizeof(DecState), cudaMemcpyDeviceToHost, st));
+    g_t4 += now_ns() - te;
     s->job.dec_nblocks = (unsigned int)nblocks;
     s->job.dec_nrst = hd.ri > 0 ? (unsigned int)(((size_t)mcu_cols * mcu_rows + hd.ri - 1) / hd.ri - 1) : 0u;
     return ICB_OK;
@@ -2330,16 +2345,19 @@ int icb_jpg_decode(icb_handle *h, const uint8_t *file, size_t n, int fmt, uint8_
     return rc;
 }
 
-static std::atomic<uint64_t> g_submit_ns{0}, g_submit_n{0}, g_acquire_ns{0};
 struct SubmitTimer {
     std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
     ~SubmitTimer()
     {
         g_submit_ns += (uint64_t)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t0).count();
         const uint64_t k = ++g_submit_n;
-        if (getenv("ICB_DEC_DEBUG") && k % 256 == 0)
-            fprintf(stderr, "icb submit_jpg_file_fit: %.1f us per call on the host (%.1f us of it waiting for a slot)\n",
-                    g_submit_ns.load() / 1e3 / k, g_acquire_ns.load() / 1e3 / k);
+        if (getenv("ICB_DEC_DEBUG") && k % 256 == 0) {
+            fprintf(stderr, "icb submit_jpg_file_fit: %.1f us per call on the host (%.1f us of it waiting for a slot; decode enqueue %.1f of which "
+                    "graph launch %.1f; fit enqueue %.1f)\n", g_submit_ns.load() / 1e3 / k, g_acquire_ns.load() / 1e3 / k,
+                    g_dec_ns.load() / 1e3 / k, g_graph_ns.load() / 1e3 / k, g_fit_ns.load() / 1e3 / k);
+            fprintf(stderr, "   tables %.1f, block upload %.1f, file upload %.1f, state download %.1f us\n", g_t1.load() / 1e3 / k,
+                    g_t2.load() / 1e3 / k, g_t3.load() / 1e3 / k, g_t4.load() / 1e3 / k);
+        }
     }
 };
 
@@ -2369,6 +2387,7 @@ int icb_submit_jpg_file_fit(icb_handle *h, const uint8_t *file, size_t n, float 
     const int fp = dev_pitch(fw, 3);
     if (!rc) rc = ensure(h, s->d_rgb, s->rgb_cap, (size_t)fp * fh + 16);
     unsigned int nblk = 0;
+    const uint64_t td = now_ns();
     if (!rc && sf == 1) {
         rc = enqueue_decode(h, s, file, n, hd, s->d_rgb, fp, false);
     } else if (!rc) {
@@ -2383,7 +2402,17 @@ int icb_submit_jpg_file_fit(icb_handle *h, const uint8_t *file, size_t n, float 
     }
     nblk = s->job.dec_nblocks;
     const unsigned int nrst = s->job.dec_nrst;
+    const uint64_t tf = now_ns();
+    g_dec_ns += tf - td;
+    static const bool dec_only = [] { const char *e = getenv("ICB_DEC_ONLY"); return e && e[0] == '1'; }();     // A/B: the reader alone
+    if (dec_only && !rc) {
+        s->job.phase = PH_RESIZE;                   // (a job with nothing to collect: drive_job just waits for the stream)
+        s->job.from_file = false;
+        *ticket = make_ticket(s);
+        return ICB_OK;
+    }
     if (!rc) rc = start_fit(h, s, s->d_rgb, fw, fh, fp, ICB_FMT_RGB8, init_q, target, has_cached, cached_q, cached_scale, out, out_cap);
+    g_fit_ns += now_ns() - tf;
     if (rc) { cudaStreamSynchronize(s->stream); release_slot(h, s); return rc; }
     s->job.from_file = true;
     s->job.dec_nblocks = nblk;

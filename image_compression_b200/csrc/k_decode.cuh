@@ -40,7 +40,10 @@ constexpr int DEC_ROUNDS = 10;              // synchronisation rounds queued per
 constexpr int DEC_CARRY = 4;                // subsequences a thread carries on through per round
 constexpr int DEC_CHUNK = 4096;             // file bytes per CTA of the scan / unstuff kernels
 constexpr int DEC_LUT_BITS = 10;
-constexpr int DEC_THREADS = 256;            // threads (= subsequences) per CTA of the decode kernels: they share 34 KB of tables
+#ifndef ICB_DEC_THREADS
+#define ICB_DEC_THREADS 256
+#endif
+constexpr int DEC_THREADS = ICB_DEC_THREADS;            // threads (= subsequences) per CTA of the decode kernels: they share 34 KB of tables
 
 constexpr int DEC_LUT2 = 16;                // second-level tables per Huffman table (distinct 10-bit prefixes of long codes)
 
@@ -107,6 +110,14 @@ struct DecParams {
     const DecTables *tab;
     DecState *st;
 };
+
+// The coefficient array starts at zero (the decoder only stores non-zero values).  A kernel, not a memset node: how a
+// memset of 36 MB is carried out is the driver's choice, and every job of every slot needs one.
+__global__ void __launch_bounds__(256) k_dec_zero(uint4 *dst, size_t nvec)
+{
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    for (size_t i = (size_t)blockIdx.x * 256 + threadIdx.x; i < nvec; i += (size_t)gridDim.x * 256) dst[i] = z;
+}
 
 // ---- entropy-coded segment: stuffed zeros and restart markers out, first other marker found -----------------
 // What happens to byte i of the scan (prev / next = its neighbours): a zero after 0xFF is stuffing and goes; with a
