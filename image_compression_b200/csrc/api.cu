@@ -2163,9 +2163,19 @@ void launch_decode_chain(Slot *s, cudaStream_t st, size_t sub_bytes_cap, size_t 
     k_dec_unstuff<<<nchunks_cap, 256, 0, st>>>(pp);
     const unsigned int sgrid = (nsub_cap + DEC_THREADS - 1) / DEC_THREADS;
     const int nrounds = dec_rounds();
-    for (int r = 0; r < nrounds; r++) k_dec_sync<<<sgrid, DEC_THREADS, 0, st>>>(pp, r == 0 ? 0 : DEC_ROUNDS - nrounds + r);
+    // A/B knob: unused dynamic shared memory per CTA of the two symbol-walking kernels, to cap how many of them an SM takes
+    static const size_t pad = [] { const char *e = getenv("ICB_DEC_PAD_KB"); const int v = e ? atoi(e) : 0; return (size_t)(v > 0 && v <= 150 ? v : 0) << 10; }();
+    static const bool pad_set = [&] {
+        if (pad) {
+            cudaFuncSetAttribute(k_dec_sync, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad);
+            cudaFuncSetAttribute(k_dec_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad);
+        }
+        return true;
+    }();
+    (void)pad_set;
+    for (int r = 0; r < nrounds; r++) k_dec_sync<<<sgrid, DEC_THREADS, pad, st>>>(pp, r == 0 ? 0 : DEC_ROUNDS - nrounds + r);
     k_dec_blocks<<<1, 1024, 0, st>>>(pp);
-    k_dec_write<<<sgrid, DEC_THREADS, 0, st>>>(pp);
+    k_dec_write<<<sgrid, DEC_THREADS, pad, st>>>(pp);
     const size_t ndc = (nblocks_cap / 3 + DEC_DC_THREADS - 1) / DEC_DC_THREADS;          // (an MCU has at least 3 blocks)
     k_dec_dc_local<<<(unsigned int)ndc, DEC_DC_THREADS, 0, st>>>(pp);
     k_dec_dc_cta<<<1, 1024, 0, st>>>(pp);

@@ -266,15 +266,18 @@ __device__ __forceinline__ unsigned int dec_rec_nblk(unsigned long long r) { ret
 struct DecBits {
     const unsigned int *words;
     unsigned long long win;
-    unsigned int pos, have, next;          // next = index of the word that enters the window next
+    unsigned int pos, have, next;          // next = index of the word `pre` holds
+    unsigned int pre;                      // the word that enters the window next, already loaded: with 200 KB of an SM's
+                                           // L1 taken as shared memory by six of these CTAs a refill is an L2 round trip;
+                                           // asked for one refill ahead, it is back before it is needed
 
     __device__ __forceinline__ void open(const unsigned char *bits, unsigned int pbit)
     {
         words = reinterpret_cast<const unsigned int *>(bits);
         pos = pbit;
-        next = pbit >> 5;
-        const unsigned int a = __byte_perm(__ldg(words + next), 0, 0x0123), b = __byte_perm(__ldg(words + next + 1), 0, 0x0123);
-        next += 2;
+        next = (pbit >> 5) + 2;
+        const unsigned int a = __byte_perm(__ldg(words + next - 2), 0, 0x0123), b = __byte_perm(__ldg(words + next - 1), 0, 0x0123);
+        pre = __ldg(words + next);
         win = (((unsigned long long)a << 32) | b) << (pbit & 31u);
         have = 64u - (pbit & 31u);
     }
@@ -285,10 +288,10 @@ struct DecBits {
         pos += n;
         have -= n;
         if (have < 32u) {
-            const unsigned int w = __byte_perm(__ldg(words + next), 0, 0x0123);
-            next++;
-            win |= (unsigned long long)w << (32u - have);
+            win |= (unsigned long long)__byte_perm(pre, 0, 0x0123) << (32u - have);
             have += 32u;
+            next++;
+            pre = __ldg(words + next);
         }
     }
 };
