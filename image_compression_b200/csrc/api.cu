@@ -2151,16 +2151,22 @@ void launch_decode_chain(Slot *s, cudaStream_t st, size_t sub_bytes_cap, size_t 
                          int w_cap, int h_cap, int hs, int vs)
 {
     const DecParams *pp = &s->d_decjob->p;
+    // A/B knob (timing only, results wrong): leave kernels out -- 1 zero, 2 scan/unstuff, 4 sync rounds, 8 write, 16 DC, 32 IDCT, 64 colour
+    static const int skip = [] { const char *e = getenv("ICB_DEC_SKIP"); return e ? atoi(e) : 0; }();
     // state: everything zero, the scan ends at the end of the file unless a marker turns up earlier; no record yet
     cudaMemsetAsync(s->d_decst, 0, sizeof(DecState), st);
     cudaMemsetAsync(&s->d_decst->scan_end, 0xff, 4, st);
     static const bool zero_by_memset = [] { const char *e = getenv("ICB_DEC_MEMSET"); return e && e[0] == '1'; }();     // A/B knob
-    if (zero_by_memset) cudaMemsetAsync(s->d_coef, 0, nblocks_cap * 128, st);
+    static const bool zero_up_front = [] { const char *e = getenv("ICB_DEC_ZERO"); return e && e[0] == '1'; }();      // A/B: the round-2 first form
+    if ((skip & 1) || !zero_up_front) { }
+    else if (zero_by_memset) cudaMemsetAsync(s->d_coef, 0, nblocks_cap * 128, st);
     else k_dec_zero<<<1184, 256, 0, st>>>(reinterpret_cast<uint4 *>(s->d_coef), nblocks_cap * 8);
     cudaMemsetAsync(s->d_sub, 0xff, sub_bytes_cap, st);
-    k_dec_scan<<<nchunks_cap, 256, 0, st>>>(pp);
-    k_dec_offsets<<<1, 1024, 0, st>>>(pp);
-    k_dec_unstuff<<<nchunks_cap, 256, 0, st>>>(pp);
+    if (!(skip & 2)) {
+        k_dec_scan<<<nchunks_cap, 256, 0, st>>>(pp);
+        k_dec_offsets<<<1, 1024, 0, st>>>(pp);
+        k_dec_unstuff<<<nchunks_cap, 256, 0, st>>>(pp);
+    }
     const unsigned int sgrid = (nsub_cap + DEC_THREADS - 1) / DEC_THREADS;
     const int nrounds = dec_rounds();
     // A/B knob: unused dynamic shared memory per CTA of the two symbol-walking kernels, to cap how many of them an SM takes
@@ -2173,15 +2179,18 @@ void launch_decode_chain(Slot *s, cudaStream_t st, size_t sub_bytes_cap, size_t 
         return true;
     }();
     (void)pad_set;
-    for (int r = 0; r < nrounds; r++) k_dec_sync<<<sgrid, DEC_THREADS, pad, st>>>(pp, r == 0 ? 0 : DEC_ROUNDS - nrounds + r);
+    for (int r = 0; r < nrounds && !(skip & 4); r++) k_dec_sync<<<sgrid, DEC_THREADS, pad, st>>>(pp, r == 0 ? 0 : DEC_ROUNDS - nrounds + r);
     k_dec_blocks<<<1, 1024, 0, st>>>(pp);
-    k_dec_write<<<sgrid, DEC_THREADS, pad, st>>>(pp);
+    if (!(skip & 8)) k_dec_write<<<sgrid, DEC_THREADS, pad, st>>>(pp);
     const size_t ndc = (nblocks_cap / 3 + DEC_DC_THREADS - 1) / DEC_DC_THREADS;          // (an MCU has at least 3 blocks)
-    k_dec_dc_local<<<(unsigned int)ndc, DEC_DC_THREADS, 0, st>>>(pp);
-    k_dec_dc_cta<<<1, 1024, 0, st>>>(pp);
-    k_dec_idct<<<(unsigned int)((nblocks_cap + 127) / 128), 128, 0, st>>>(pp);
+    if (!(skip & 16)) {
+        k_dec_dc_local<<<(unsigned int)ndc, DEC_DC_THREADS, 0, st>>>(pp);
+        k_dec_dc_cta<<<1, 1024, 0, st>>>(pp);
+    }
+    if (!(skip & 32)) k_dec_idct<<<(unsigned int)((nblocks_cap + 127) / 128), 128, 0, st>>>(pp);
     const dim3 cgrid((w_cap + 255) / 256, (h_cap + 7) / 8);
-    if (hs == 2 && vs == 2) k_dec_color<2, 2><<<cgrid, 256, 0, st>>>(pp);
+    if (skip & 64) { }
+    else if (hs == 2 && vs == 2) k_dec_color<2, 2><<<cgrid, 256, 0, st>>>(pp);
     else if (hs == 2) k_dec_color<2, 1><<<cgrid, 256, 0, st>>>(pp);
     else k_dec_color<1, 1><<<cgrid, 256, 0, st>>>(pp);
 }

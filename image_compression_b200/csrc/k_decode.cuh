@@ -343,10 +343,19 @@ __device__ __forceinline__ unsigned int dec_lookup(const DecSmem &s, unsigned in
 // WRITE: coefficients go to coef (block index blk counts from the caller's base; blocks >= nblocks are dropped).
 __device__ __forceinline__ unsigned int st_n_rst(const DecParams &p) { return p.st->n_rst; }
 
+__device__ __forceinline__ void dec_zero_block(int16_t *coef, unsigned int blk)
+{
+    uint4 *q = reinterpret_cast<uint4 *>(coef + (size_t)blk * 64);
+    const uint4 z = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int i = 0; i < 8; i++) q[i] = z;
+}
+
 template <bool WRITE>
 __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *bits, unsigned int &pbit, unsigned int &bz,
                                         unsigned int &nblk, unsigned int end_bit, int16_t *coef, unsigned int blk,
-                                        unsigned int nblocks, DecState *st, unsigned int last_b, const DecParams &p)
+                                        unsigned int nblocks, DecState *st, unsigned int last_b, const DecParams &p,
+                                        unsigned int next_base = 0xffffffffu)
 {
     unsigned int b = bz >> 6, z = bz & 63u;
     unsigned int tdc = s.tab_dc[b], tac = s.tab_ac[b];          // the block's two tables (change once per block)
@@ -371,7 +380,11 @@ __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *b
             z = 0; b = 0;
             tdc = s.tab_dc[0]; tac = s.tab_ac[0];
             rk++;
-            if (WRITE) blk = rk * (unsigned int)p.ri * (last_b + 1u);
+            if (WRITE) {
+                const unsigned int nbk = rk * (unsigned int)p.ri * (last_b + 1u);
+                if (nbk != blk && nbk < nblocks && nbk != next_base) dec_zero_block(coef, nbk);     // (only a wrong chain gets here)
+                blk = nbk;
+            }
             rnext = rk < n_rst ? p.rst_pos[rk] * 8u : 0xffffffffu;
             continue;
         }
@@ -395,7 +408,10 @@ __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *b
             tdc = s.tab_dc[b]; tac = s.tab_ac[b];
             nblk++;
             blk++;
-            if (WRITE && blk == nblocks) st->end_bit = br.pos;
+            if (WRITE) {
+                if (blk == nblocks) st->end_bit = br.pos;
+                else if (blk < nblocks && blk != next_base) dec_zero_block(coef, blk);   // (see k_dec_write)
+            }
         }
     }
     pbit = br.pos;
@@ -458,7 +474,12 @@ __global__ void __launch_bounds__(1024) k_dec_blocks(const DecParams *pp)
         __syncthreads();
     }
     unsigned int run = s_part[tid] - mine;
-    for (unsigned int i = i0; i < i1; i++) { p.blk_base[i] = run; run += dec_rec_nblk(p.rec[i]); }
+    for (unsigned int i = i0; i < i1; i++) {
+        p.blk_base[i] = run;
+        // the block in progress where a subsequence starts is shared with the thread to its left: zeroed here, once
+        if (run < p.nblocks && (i == i0 || run != p.blk_base[i - 1])) dec_zero_block(p.coef, run);
+        run += dec_rec_nblk(p.rec[i]);
+    }
     if (tid == 1023) p.st->blocks_found = s_part[1023];
 }
 
@@ -475,7 +496,13 @@ __global__ void __launch_bounds__(DEC_THREADS) k_dec_write(const DecParams *pp)
     const unsigned int entry = dec_rec_entry(p.rec[i]);
     unsigned int pbit = start + (entry >> 9), bz = entry & 0x1ffu, nblk = 0;
     const unsigned int end = min(start + S, total_bits);
-    dec_run<true>(s, p.bits, pbit, bz, nblk, end, p.coef, p.blk_base[i], p.nblocks, p.st, (unsigned int)p.nb - 1u, p);
+    // The coefficient array is not cleared beforehand: a thread clears each block as it STARTS it (eight 16-byte stores:
+    // whole sectors, which then sit in L2 for the 2-byte stores that follow -- with 36 MB cleared up front those stores
+    // each fetched a sector back from DRAM: 76 us of the reader's 216 per image in the steady state), except the block
+    // the next thread is already writing into, which k_dec_blocks cleared.
+    const unsigned int nsub = min(p.nsub_max, (total_bits + S - 1) / S);
+    const unsigned int next_base = i + 1 < nsub ? p.blk_base[i + 1] : 0xffffffffu;
+    dec_run<true>(s, p.bits, pbit, bz, nblk, end, p.coef, p.blk_base[i], p.nblocks, p.st, (unsigned int)p.nb - 1u, p, next_base);
 }
 
 // ---- DC differences -> DC values (jdhuff.c last_dc_val): per component a prefix over the MCUs --------------
