@@ -2174,14 +2174,15 @@ void launch_decode_chain(Slot *s, cudaStream_t st, size_t sub_bytes_cap, size_t 
     static const bool pad_set = [&] {
         if (pad) {
             cudaFuncSetAttribute(k_dec_sync, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad);
-            cudaFuncSetAttribute(k_dec_write, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pad);
         }
         return true;
     }();
     (void)pad_set;
     for (int r = 0; r < nrounds && !(skip & 4); r++) k_dec_sync<<<sgrid, DEC_THREADS, pad, st>>>(pp, r == 0 ? 0 : DEC_ROUNDS - nrounds + r);
     k_dec_blocks<<<1, 1024, 0, st>>>(pp);
-    if (!(skip & 8)) k_dec_write<<<sgrid, DEC_THREADS, pad, st>>>(pp);
+    static const bool wattr = [] { cudaFuncSetAttribute(k_dec_write, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_WBUF_BYTES); return true; }();
+    (void)wattr;
+    if (!(skip & 8)) k_dec_write<<<(nsub_cap + DEC_WTHREADS - 1) / DEC_WTHREADS, DEC_WTHREADS, DEC_WBUF_BYTES, st>>>(pp);
     const size_t ndc = (nblocks_cap / 3 + DEC_DC_THREADS - 1) / DEC_DC_THREADS;          // (an MCU has at least 3 blocks)
     if (!(skip & 16)) {
         k_dec_dc_local<<<(unsigned int)ndc, DEC_DC_THREADS, 0, st>>>(pp);
@@ -2251,6 +2252,8 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     dp.rec = reinterpret_cast<unsigned long long *>(s->d_sub);
     dp.sub_bits = sub_bits;
     dp.carry = carry;
+    static const int wbuf = [] { const char *e = getenv("ICB_DEC_WBUF"); return e && e[0] == '0' ? 0 : 1; }();
+    dp.wbuf = wbuf;
     dp.blk_base = reinterpret_cast<unsigned int *>(s->d_sub + o_base);
     dp.chunk_drop = reinterpret_cast<unsigned int *>(s->d_sub + o_chunk);
     dp.mcu_pref = reinterpret_cast<int *>(s->d_sub + o_mcu);

@@ -91,6 +91,7 @@ struct DecParams {
     unsigned long long *rec;                // [nsub_max] one record per subsequence (dec_rec)
     unsigned int sub_bits;                  // bits per subsequence
     unsigned int carry;                     // subsequences a thread carries on through per round
+    int wbuf;                               // write pass: whole blocks through shared memory (1) or every coefficient straight to HBM (0, A/B)
     unsigned int *blk_base;                 // [nsub_max] blocks in front of each subsequence
     int *mcu_pref;                          // [mcus][3] DC differences in front of each MCU inside its CTA of k_dec_dc_local
     int *cta_pref;                          // [ceil(mcus / DEC_DC_THREADS)][3] ... and in front of that CTA
@@ -355,8 +356,13 @@ template <bool WRITE>
 __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *bits, unsigned int &pbit, unsigned int &bz,
                                         unsigned int &nblk, unsigned int end_bit, int16_t *coef, unsigned int blk,
                                         unsigned int nblocks, DecState *st, unsigned int last_b, const DecParams &p,
-                                        unsigned int next_base = 0xffffffffu)
+                                        unsigned int next_base = 0xffffffffu, int16_t *buf = nullptr)
 {
+    // WRITE with buf: the coefficients of a block this thread decodes from its first symbol to its last are collected
+    // in the thread's 128 bytes of shared memory and leave as eight 16-byte stores (zeros included); only the block the
+    // thread finds half done at its start and the one it leaves half done at its end -- the next thread's first:
+    // next_base -- take 2-byte stores, into memory k_dec_blocks cleared.
+    bool direct = true;
     unsigned int b = bz >> 6, z = bz & 63u;
     unsigned int tdc = s.tab_dc[b], tac = s.tab_ac[b];          // the block's two tables (change once per block)
     DecBits br;
@@ -382,7 +388,10 @@ __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *b
             rk++;
             if (WRITE) {
                 const unsigned int nbk = rk * (unsigned int)p.ri * (last_b + 1u);
-                if (nbk != blk && nbk < nblocks && nbk != next_base) dec_zero_block(coef, nbk);     // (only a wrong chain gets here)
+                if (nbk != blk) {                               // (only a wrong chain gets here)
+                    if (buf) direct = true;                     // whatever it holds is not a whole block: scattered from here on
+                    else if (nbk < nblocks && nbk != next_base) dec_zero_block(coef, nbk);
+                }
                 blk = nbk;
             }
             rnext = rk < n_rst ? p.rst_pos[rk] * 8u : 0xffffffffu;
@@ -397,7 +406,8 @@ __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *b
                 // the value bits follow the code inside the same 32-bit window (jdhuff.c HUFF_EXTEND)
                 const unsigned int rb = (peek << ((e >> 17) & 31u)) >> (32u - sz);
                 const int v = rb < (1u << (sz - 1)) ? (int)rb - (int)(1u << sz) + 1 : (int)rb;
-                coef[(size_t)blk * 64 + s.zz[at]] = (int16_t)v;
+                if (buf && !direct) buf[s.zz[at]] = (int16_t)v;
+                else coef[(size_t)blk * 64 + s.zz[at]] = (int16_t)v;
             }
         }
         br.skip(e & 63u);
@@ -409,8 +419,18 @@ __device__ __forceinline__ void dec_run(const DecSmem &s, const unsigned char *b
             nblk++;
             blk++;
             if (WRITE) {
+                if (buf) {
+                    if (!direct) {                              // a whole block: out it goes, and the buffer is clean again
+                        uint4 *q = reinterpret_cast<uint4 *>(coef + (size_t)(blk - 1) * 64), *bq = reinterpret_cast<uint4 *>(buf);
+                        const uint4 zero4 = make_uint4(0, 0, 0, 0);
+#pragma unroll
+                        for (int k8 = 0; k8 < 8; k8++) { q[k8] = bq[k8]; bq[k8] = zero4; }
+                    }
+                    direct = blk == next_base;
+                } else if (blk < nblocks && blk != next_base) {
+                    dec_zero_block(coef, blk);                  // (unbuffered form: clear each block as it starts)
+                }
                 if (blk == nblocks) st->end_bit = br.pos;
-                else if (blk < nblocks && blk != next_base) dec_zero_block(coef, blk);   // (see k_dec_write)
             }
         }
     }
@@ -483,11 +503,22 @@ __global__ void __launch_bounds__(1024) k_dec_blocks(const DecParams *pp)
     if (tid == 1023) p.st->blocks_found = s_part[1023];
 }
 
-__global__ void __launch_bounds__(DEC_THREADS) k_dec_write(const DecParams *pp)
+constexpr int DEC_WTHREADS = 128;           // threads per CTA of the write pass
+constexpr int DEC_WBUF_STRIDE = 144;        // bytes of block buffer per thread: 128 + 16, so that the 16-byte reads of a warp spread over the banks
+constexpr int DEC_WBUF_BYTES = DEC_WTHREADS * DEC_WBUF_STRIDE;
+
+__global__ void __launch_bounds__(DEC_WTHREADS) k_dec_write(const DecParams *pp)
 {
     const DecParams p = *pp;
     __shared__ DecSmem s;
+    extern __shared__ __align__(16) unsigned char dec_wbuf[];
     dec_load_tables(s, p.tab);
+    int16_t *buf = reinterpret_cast<int16_t *>(dec_wbuf + threadIdx.x * DEC_WBUF_STRIDE);
+    {
+        const uint4 zero4 = make_uint4(0, 0, 0, 0);
+#pragma unroll
+        for (int k8 = 0; k8 < 8; k8++) reinterpret_cast<uint4 *>(buf)[k8] = zero4;
+    }
     const unsigned int i = blockIdx.x * blockDim.x + threadIdx.x;
     const unsigned int total_bits = p.st->total_bytes * 8u;
     const unsigned int S = p.sub_bits;
@@ -496,13 +527,10 @@ __global__ void __launch_bounds__(DEC_THREADS) k_dec_write(const DecParams *pp)
     const unsigned int entry = dec_rec_entry(p.rec[i]);
     unsigned int pbit = start + (entry >> 9), bz = entry & 0x1ffu, nblk = 0;
     const unsigned int end = min(start + S, total_bits);
-    // The coefficient array is not cleared beforehand: a thread clears each block as it STARTS it (eight 16-byte stores:
-    // whole sectors, which then sit in L2 for the 2-byte stores that follow -- with 36 MB cleared up front those stores
-    // each fetched a sector back from DRAM: 76 us of the reader's 216 per image in the steady state), except the block
-    // the next thread is already writing into, which k_dec_blocks cleared.
     const unsigned int nsub = min(p.nsub_max, (total_bits + S - 1) / S);
     const unsigned int next_base = i + 1 < nsub ? p.blk_base[i + 1] : 0xffffffffu;
-    dec_run<true>(s, p.bits, pbit, bz, nblk, end, p.coef, p.blk_base[i], p.nblocks, p.st, (unsigned int)p.nb - 1u, p, next_base);
+    dec_run<true>(s, p.bits, pbit, bz, nblk, end, p.coef, p.blk_base[i], p.nblocks, p.st, (unsigned int)p.nb - 1u, p, next_base,
+                  p.wbuf ? buf : nullptr);
 }
 
 // ---- DC differences -> DC values (jdhuff.c last_dc_val): per component a prefix over the MCUs --------------
