@@ -2220,7 +2220,7 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     const size_t nblocks_cap = std::max(s->dec_blocks_cap,
                                         (size_t)((wc + 8 * hd.hs - 1) / (8 * hd.hs)) * ((hc + 8 * hd.vs - 1) / (8 * hd.vs)) * nbm);
     const unsigned int nsub_cap = (unsigned int)std::min<size_t>((scan_cap * 8 + sub_bits - 1) / sub_bits, (1u << 17) - 1);
-    const int nchunks_cap = (int)((scan_cap + DEC_CHUNK - 1) / DEC_CHUNK);
+    const int nchunks_cap = (int)((scan_cap + DEC_CHUNK - 1) / DEC_CHUNK) + 1;     // (+1: chunks start at scan_off rounded down to 16)
     if (!s->d_decjob) {
         if (cudaMalloc((void **)&s->d_decjob, sizeof(DecJob)) != cudaSuccess ||
             cudaMalloc((void **)&s->d_decst, sizeof(DecState)) != cudaSuccess ||
@@ -2269,7 +2269,7 @@ int enqueue_decode(icb_handle *h, Slot *s, const uint8_t *file, size_t n, const 
     dp.hs = hd.hs; dp.vs = hd.vs; dp.nb = nbm;
     dp.nblocks = (unsigned int)nblocks;
     dp.nsub_max = (unsigned int)((scan_bytes * 8 + sub_bits - 1) / sub_bits);
-    dp.nchunks = (int)((scan_bytes + DEC_CHUNK - 1) / DEC_CHUNK);
+    dp.nchunks = (int)((scan_bytes + (hd.scan_off & 15) + DEC_CHUNK - 1) / DEC_CHUNK);
     dp.tab = &s->d_decjob->t;
     dp.st = s->d_decst;
     const uint64_t tb = now_ns();

@@ -131,27 +131,56 @@ __device__ __forceinline__ bool dec_keep(unsigned int prev, unsigned int b, unsi
     return true;
 }
 
+// A thread takes the 16 file bytes of one ALIGNED group (one 16-byte load; the file buffer is 256-byte aligned and the
+// groups start at scan_off rounded down), plus the byte in front and the byte behind; bytes outside [scan_off, end) do
+// not exist for it.  Chunk c = the 256 groups from group 256 c on.
+struct DecGroup {
+    unsigned int w[4];          // the 16 bytes, little-endian words
+    unsigned int prev, next;    // neighbours (0 outside the scan)
+    unsigned int first, last;   // byte indices (0..16) of the part of the group inside [scan_off, end)
+    unsigned int addr;          // file offset of byte 0
+};
+
+__device__ __forceinline__ DecGroup dec_load_group(const DecParams &p, unsigned int chunk, unsigned int end)
+{
+    DecGroup g;
+    g.addr = (p.scan_off & ~15u) + (chunk * 256u + threadIdx.x) * 16u;
+    g.first = g.addr < p.scan_off ? p.scan_off - g.addr : 0u;
+    g.last = g.addr >= end ? 0u : min(16u, end - g.addr);
+    if (g.first > g.last) g.first = g.last;
+    g.w[0] = g.w[1] = g.w[2] = g.w[3] = 0u;
+    g.prev = g.next = 0u;
+    if (g.last > g.first) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(p.file + g.addr);       // (the buffer is padded to whole groups)
+        g.w[0] = v.x; g.w[1] = v.y; g.w[2] = v.z; g.w[3] = v.w;
+        if (g.addr + g.first > p.scan_off) g.prev = p.file[g.addr + g.first - 1];
+        if (g.addr + 16u < end) g.next = p.file[g.addr + 16u];
+    }
+    return g;
+}
+__device__ __forceinline__ unsigned int dec_group_byte(const DecGroup &g, unsigned int i) { return (g.w[i >> 2] >> (8u * (i & 3u))) & 0xffu; }
+
 __global__ void __launch_bounds__(256) k_dec_scan(const DecParams *pp)
 {
     const DecParams p = *pp;
     __shared__ unsigned int s_cnt[2];
     if (threadIdx.x < 2) s_cnt[threadIdx.x] = 0;
     __syncthreads();
-    const unsigned int base = p.scan_off + blockIdx.x * DEC_CHUNK + threadIdx.x * 16;
+    const DecGroup g = dec_load_group(p, blockIdx.x, p.file_len);
     unsigned int drops = 0, rsts = 0;
-    if (base < p.file_len) {
-        unsigned int prev = base > p.scan_off ? p.file[base - 1] : 0;
-        const unsigned int n = min(16u, p.file_len - base);
-        unsigned int b = p.file[base];
-        for (unsigned int i = 0; i < n; i++) {
-            const unsigned int next = base + i + 1 < p.file_len ? p.file[base + i + 1] : 0u;
+    {
+        unsigned int prev = g.prev;
+#pragma unroll
+        for (unsigned int i = 0; i < 16; i++) {
+            if (i < g.first || i >= g.last) continue;
+            const unsigned int b = dec_group_byte(g, i);
+            const unsigned int next = i + 1 < 16 ? (i + 1 < g.last ? dec_group_byte(g, i + 1) : 0u) : g.next;
             if (!dec_keep(prev, b, next, p.ri)) drops++;
-            if (prev == 0xFFu) {
+            if (prev == 0xFFu && g.addr + i > p.scan_off) {
                 if (dec_is_rst(b, p.ri)) rsts++;
-                else if (b != 0u && b != 0xFFu) atomicMin(&p.st->scan_end, base + i - 1);      // a marker: the scan ends here
+                else if (b != 0u && b != 0xFFu) atomicMin(&p.st->scan_end, g.addr + i - 1);      // a marker: the scan ends here
             }
             prev = b;
-            b = next;
         }
     }
     drops = __reduce_add_sync(0xffffffffu, drops);
@@ -188,26 +217,29 @@ __global__ void __launch_bounds__(1024) k_dec_offsets(const DecParams *pp)
     }
 }
 
-// Two sweeps over a thread's 16 bytes (the second hits L1): count what stays and the restart markers, prefix both over
-// the CTA, then write the bytes and, per marker, where the interval behind it starts.
+// The bytes that stay are first packed into the CTA's shared memory (each thread at its offset inside the chunk's
+// output), then leave as 16-byte vectors: one store per 16 output bytes instead of sixteen.
 __global__ void __launch_bounds__(256) k_dec_unstuff(const DecParams *pp)
 {
     const DecParams p = *pp;
     __shared__ unsigned int s_warp[2][8];
+    __shared__ __align__(16) unsigned char s_out[DEC_CHUNK + 16];
     const unsigned int end = min(p.st->scan_end, p.file_len);
-    const unsigned int chunk0 = p.scan_off + blockIdx.x * DEC_CHUNK;
-    if (chunk0 >= end) return;
-    const unsigned int base = chunk0 + threadIdx.x * 16;
-    unsigned int keep = 0, rsts = 0, n = 0;
-    if (base < end) {
-        n = min(16u, end - base);
-        unsigned int prev = base > p.scan_off ? p.file[base - 1] : 0, b = p.file[base];
-        for (unsigned int i = 0; i < n; i++) {
-            const unsigned int next = base + i + 1 < end ? p.file[base + i + 1] : 0u;
-            keep += dec_keep(prev, b, next, p.ri) ? 1u : 0u;
-            rsts += (prev == 0xFFu && dec_is_rst(b, p.ri)) ? 1u : 0u;
+    const unsigned int chunk_addr = (p.scan_off & ~15u) + blockIdx.x * DEC_CHUNK;
+    if (chunk_addr >= end) return;
+    const DecGroup g = dec_load_group(p, blockIdx.x, end);
+    unsigned int keep = 0, rsts = 0;
+    unsigned int kept_mask = 0, rst_mask = 0;
+    {
+        unsigned int prev = g.prev;
+#pragma unroll
+        for (unsigned int i = 0; i < 16; i++) {
+            if (i < g.first || i >= g.last) continue;
+            const unsigned int b = dec_group_byte(g, i);
+            const unsigned int next = i + 1 < 16 ? (i + 1 < g.last ? dec_group_byte(g, i + 1) : 0u) : g.next;
+            if (dec_keep(prev, b, next, p.ri)) { keep++; kept_mask |= 1u << i; }
+            if (prev == 0xFFu && dec_is_rst(b, p.ri)) { rsts++; rst_mask |= 1u << i; }
             prev = b;
-            b = next;
         }
     }
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -219,24 +251,37 @@ __global__ void __launch_bounds__(256) k_dec_unstuff(const DecParams *pp)
     }
     if (lane == 31) { s_warp[0][warp] = ik; s_warp[1][warp] = ir; }
     __syncthreads();
-    unsigned int off = ik - keep, roff = ir - rsts;
-    for (int w = 0; w < warp; w++) { off += s_warp[0][w]; roff += s_warp[1][w]; }
-    unsigned int out = (chunk0 - p.scan_off) - p.chunk_drop[blockIdx.x] + off;
-    unsigned int rk = p.chunk_rst[blockIdx.x] + roff;
-    if (n) {
-        unsigned int prev = base > p.scan_off ? p.file[base - 1] : 0, b = p.file[base];
-        for (unsigned int i = 0; i < n; i++) {
-            const unsigned int next = base + i + 1 < end ? p.file[base + i + 1] : 0u;
-            if (dec_keep(prev, b, next, p.ri)) p.bits[out++] = (unsigned char)b;
-            if (prev == 0xFFu && dec_is_rst(b, p.ri)) { if (rk < p.rst_cap) p.rst_pos[rk] = out; rk++; }
-            prev = b;
-            b = next;
+    unsigned int off = ik - keep, roff = ir - rsts, cta_keep = 0;
+    for (int w = 0; w < 8; w++) { if (w < warp) { off += s_warp[0][w]; roff += s_warp[1][w]; } cta_keep += s_warp[0][w]; }
+    // output offset of the chunk = bytes of the scan in front of it minus what was dropped there
+    const unsigned int in_front = chunk_addr > p.scan_off ? chunk_addr - p.scan_off : 0u;
+    const unsigned int out0 = in_front - p.chunk_drop[blockIdx.x];
+    const unsigned int shift = out0 & 15u;                      // the chunk's output starts `shift` bytes into a 16-byte vector
+    unsigned int o = off, rk = p.chunk_rst[blockIdx.x] + roff;
+#pragma unroll
+    for (unsigned int i = 0; i < 16; i++) {
+        if (kept_mask & (1u << i)) s_out[shift + o++] = (unsigned char)dec_group_byte(g, i);
+        if (rst_mask & (1u << i)) { if (rk < p.rst_cap) p.rst_pos[rk] = out0 + o; rk++; }
+    }
+    __syncthreads();
+    {
+        // whole vectors from shared memory; the ragged first and last vector of the chunk in bytes (the neighbours own the rest)
+        unsigned char *dst = p.bits + (out0 - shift);
+        const unsigned int nbytes = shift + cta_keep, nvec = (nbytes + 15u) >> 4;
+        for (unsigned int v = threadIdx.x; v < nvec; v += 256) {
+            const unsigned int lo = v * 16u, hi = min(lo + 16u, nbytes);
+            if (lo >= shift && hi == lo + 16u) {
+                reinterpret_cast<uint4 *>(dst)[v] = reinterpret_cast<const uint4 *>(s_out)[v];
+            } else {
+                for (unsigned int k = max(lo, shift); k < hi; k++) dst[k] = s_out[k];
+            }
         }
-        if (base + n == end) {                                  // the thread that holds the last byte of the scan
-            p.st->total_bytes = out;
-            p.st->n_rst = rk;
-            for (unsigned int i = 0; i < 64; i++) p.bits[out + i] = 0;
-        }
+    }
+    if (g.last > g.first && g.addr + g.last == end) {           // the thread that holds the last byte of the scan
+        const unsigned int total = out0 + o;
+        p.st->total_bytes = total;
+        p.st->n_rst = rk;
+        for (unsigned int i = 0; i < 64; i++) p.bits[total + i] = 0;
     }
 }
 
