@@ -24,11 +24,14 @@
 //   k_dec_offsets  prefix of those counts (one CTA)
 //   k_dec_unstuff  the entropy-coded bytes without stuffed zeros and restart markers, zero padded; where each restart interval starts
 //   k_dec_sync     one synchronisation round (DEC_ROUNDS launches, no-ops once nothing changes)
-//   k_dec_blocks   blocks in front of every subsequence (one CTA)
-//   k_dec_write    coefficients (quantised, natural order, DC as differences) into the block array
+//   k_dec_blocks   blocks in front of every subsequence (one CTA); clears the blocks two neighbouring subsequences share
+//   k_dec_write    coefficients (quantised, natural order, DC as differences) into the block array: whole blocks
+//                  through 128 bytes of shared memory per thread as 16-byte vectors, shared blocks by 2-byte stores
 //   k_dec_dc_local / k_dec_dc_cta   per-component prefix of the DC differences over the MCUs
 //   k_dec_idct     DC prediction undone, dequantise + islow inverse DCT, one thread per block -> Y / Cb / Cr planes
-//   k_dec_color    fancy h2v2 upsampling + YCbCr -> RGB, eight pixels per thread -> the decoded raster
+//   k_dec_color    fancy h2v2 / h2v1 upsampling (or none, 4:4:4) + YCbCr -> RGB, eight pixels per thread -> the decoded raster
+// The chain is captured once per slot as a CUDA graph (api.cu enqueue_decode): the kernels read their parameters from
+// a block in device memory, grids follow the slot's capacities.
 #pragma once
 
 #include "common.cuh"
