@@ -301,6 +301,8 @@ int setup_device(icb_handle *h, DeviceCtx &d)
     CK(cudaFuncSetAttribute(k_transform<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_transform<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
     CK(cudaFuncSetAttribute(k_transform<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, XF_SMEM_BYTES));
+    // (function attributes belong to the device: every GPU of the handle needs them, not just the first one used)
+    CK(cudaFuncSetAttribute(k_dec_write, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_WBUF_BYTES));
     return ICB_OK;
 }
 
@@ -2180,8 +2182,6 @@ void launch_decode_chain(Slot *s, cudaStream_t st, size_t sub_bytes_cap, size_t 
     (void)pad_set;
     for (int r = 0; r < nrounds && !(skip & 4); r++) k_dec_sync<<<sgrid, DEC_THREADS, pad, st>>>(pp, r == 0 ? 0 : DEC_ROUNDS - nrounds + r);
     k_dec_blocks<<<1, 1024, 0, st>>>(pp);
-    static const bool wattr = [] { cudaFuncSetAttribute(k_dec_write, cudaFuncAttributeMaxDynamicSharedMemorySize, DEC_WBUF_BYTES); return true; }();
-    (void)wattr;
     if (!(skip & 8)) k_dec_write<<<(nsub_cap + DEC_WTHREADS - 1) / DEC_WTHREADS, DEC_WTHREADS, DEC_WBUF_BYTES, st>>>(pp);
     const size_t ndc = (nblocks_cap / 3 + DEC_DC_THREADS - 1) / DEC_DC_THREADS;          // (an MCU has at least 3 blocks)
     if (!(skip & 16)) {

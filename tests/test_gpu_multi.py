@@ -80,3 +80,23 @@ def test_native_executor_with_resident_images_on_every_gpu_never_waits_while_hol
             assert bytes(o[: r.out_len]) == ref
     for hnd in handles:
         multi.free_image(hnd)
+
+
+def test_file_jobs_on_every_gpu(multi, oracle):
+    """icb_submit_jpg_file_fit through one handle over all GPUs: the reader's kernels (shared-memory opt-in, graphs,
+    arenas) are set up per GPU, and every GPU decodes and fits bit-exactly."""
+    n_dev = multi.device_count
+    img = synth.natural_image(970, 1024, 768)
+    data = oracle.encode(img, 0.9)
+    px = oracle.jpeg_decode(data)
+    rc, ref, rq, rs, _, _ = oracle.jpg_fit(px, 0.25, 30000)
+    n = 8 * n_dev
+    outs = [np.empty(30000, np.uint8) for _ in range(n)]
+    items = multi.make_items([dict(kind="jpg_file_fit", file=data, init_q=0.25, target=30000, out=outs[i]) for i in range(n)])
+    multi.run_list(items, threads=2 * n_dev, inflight=2)
+    seen = set()
+    for r, o in zip(items.results(), outs):
+        assert (r.status, r.best_q, r.scale) == (rc, rq, rs)
+        assert bytes(o[: r.out_len]) == ref
+        seen.add(r.device)
+    assert seen == set(range(n_dev)), sorted(seen)
